@@ -1,0 +1,117 @@
+"""Helpers shared by the oracle and GPU parity tests: load a golden case recorded from the
+unmodified reference (tests/golden/make_golden.py) and replay its epochs through any engine
+exposing `fit(x, y, masks) -> (pred, loss)` and `evaluate(x, y) -> (pred, loss)`."""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+
+import numpy as np
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+CASES = ['tinysys_adam_b32', 'sgd_h64_ragged', 'gelu_h64', 'deep_h64_h48']
+
+
+@dataclass
+class GoldenCase:
+    name: str
+    raw: dict
+
+    @property
+    def dims(self):
+        return [int(d) for d in self.raw['dims']]
+
+    @property
+    def dropout(self):
+        return float(self.raw['dropout'])
+
+    @property
+    def activation(self):
+        return str(self.raw['activation'])
+
+    @property
+    def optimizer(self):
+        return str(self.raw['optimizer'])
+
+    @property
+    def lr(self):
+        return float(self.raw['lr'])
+
+    @property
+    def batch(self):
+        return int(self.raw['batch'])
+
+    @property
+    def epochs(self):
+        return int(self.raw['epochs'])
+
+    def init_params(self):
+        n = 2 * (len(self.dims) - 1)
+        return [self.raw[f'init_{i}'].copy() for i in range(n)]
+
+    def final_params(self):
+        n = 2 * (len(self.dims) - 1)
+        return [self.raw[f'final_{i}'] for i in range(n)]
+
+    def masks(self, fit_call: int):
+        """0/1 uint8 keep masks [B, hidden_l] per hidden layer for the fit_call-th fit."""
+        if self.dropout == 0.0:
+            return None
+        hidden = self.dims[1:-1]
+        return [np.unpackbits(self.raw[f'mask_{fit_call}_{l}'], axis=1)[:, :h].copy() for l, h in enumerate(hidden)]
+
+    def batches(self, split: str):
+        x, y = self.raw[f'x_{split}'], self.raw[f'y_{split}']
+        return [(x[i:i + self.batch], y[i:i + self.batch]) for i in range(0, x.shape[0], self.batch)]
+
+
+def load_case(name: str) -> GoldenCase:
+    with np.load(os.path.join(GOLDEN_DIR, name + '.npz')) as f:
+        return GoldenCase(name, {k: f[k] for k in f.files})
+
+
+def replay(case: GoldenCase, engine, metrics):
+    """Run the recorded epochs (train batches, then validation batches, metrics reset after each
+    phase, as training.py:21-27 does) and return per-batch and per-phase records."""
+    losses, preds, phases = [], [], []
+    fit_call = 0
+    for _ in range(case.epochs):
+        for b, (x, y) in enumerate(case.batches('train'), start=1):
+            p, l = engine.fit(x, y, case.masks(fit_call))
+            fit_call += 1
+            metrics.update(b, l, p, y)
+            losses.append(float(l)); preds.append(np.asarray(p))
+        phases.append(metrics.compute()); metrics.reset()
+        for b, (x, y) in enumerate(case.batches('val'), start=1):
+            p, l = engine.evaluate(x, y)
+            metrics.update(b, l, p, y)
+            losses.append(float(l)); preds.append(np.asarray(p))
+        phases.append(metrics.compute()); metrics.reset()
+    return np.array(losses, dtype=np.float32), np.concatenate(preds), phases
+
+
+def golden_phase_results(case: GoldenCase):
+    names, losses, accs = case.raw['event_name'], case.raw['event_loss'], case.raw['event_accuracy']
+    return [(float(l), float(a)) for n, l, a in zip(names, losses, accs) if str(n) != 'Iterated']
+
+
+def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weights'):
+    """Updated-weight tolerance of the north star (1e-5 relative in fp32 mode, 1e-2 in bf16 mode),
+    applied per element as |got - want| <= tol * (|want| + rms(want)).
+
+    SGD must satisfy it everywhere. Adam divides the step by sqrt(v): an element whose gradient is
+    itself at round-off level (|g| near eps = 1e-8) moves by up to `lr` per step in a direction that
+    depends on summation order, in the reference as much as here. For Adam at most 2e-4 of the
+    elements of a tensor may therefore leave the band, and none by more than lr * steps (the hard
+    bound on any Adam trajectory difference)."""
+    for i, (g, w) in enumerate(zip(got, want)):
+        g = np.asarray(g, dtype=np.float64); w = np.asarray(w, dtype=np.float64)
+        assert g.shape == w.shape, f'{what}[{i}]: shape {g.shape} vs {w.shape}'
+        rms = np.sqrt(np.mean(w * w)) if w.size else 0.0
+        dev = np.abs(g - w)
+        bad = dev > tol * (np.abs(w) + rms) + 1e-9
+        if not adam:
+            assert not bad.any(), f'{what}[{i}]: {bad.sum()} elements off, max |d|={dev.max():.3e}'
+        else:
+            assert bad.mean() <= 2e-4, f'{what}[{i}]: {bad.sum()}/{bad.size} elements off (tol {tol})'
+            assert dev.max() <= lr * steps + 1e-9, f'{what}[{i}]: max |d|={dev.max():.3e} beyond lr*steps'
