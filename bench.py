@@ -1,0 +1,292 @@
+#!/usr/bin/env python
+"""bench.py -- train() samples/sec of the TorchSystem hot path on B200 (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): MLP(784,256,10), dropout 0.1 (in-kernel Philox),
+ReLU, CrossEntropyLoss, SGD(lr=0.01), batch 4096, 1,048,576 synthetic samples per GPU. One STEP is one pass of the
+`train` handler (model.fit + metrics.update per batch, metrics.compute, Trained event) over those 256 batches.
+Weak scaling: every rank owns its own 1,048,576-sample shard, gradients are all-reduced every batch.
+
+* value   whole-job samples/s, inputs resident in HBM (DeviceLoader); device-timed, max over ranks.
+* e2e     same handler, inputs in pinned HOST memory copied host->device every step (PinnedLoader), the
+          phase result read back device->host.
+* roofline / cpu_baseline / clocks / gpu_launches: see DESIGN.md "Measurement".
+* --impl reference  times the reference's CPU path (oracle/ref_torch.py: the same stock-torch call sequence as
+          the reference's Classifier/handlers) on the host cores, on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+DIMS = [784, 256, 10]
+BATCH = 4096
+BATCHES_PER_STEP = 256
+DROPOUT = 0.1
+LR = 0.01
+BYTES_PER_SAMPLE = 784 * 4 + 8 + 8          # x f32 + target i64 + prediction i64
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--precision', default=os.environ.get('TSB_BENCH_PRECISION', 'bf16'), choices=['bf16', 'f32'])
+    ap.add_argument('--optimizer', default='sgd', choices=['sgd', 'adam'])
+    ap.add_argument('--batches', type=int, default=BATCHES_PER_STEP, help='batches of 4096 per step')
+    ap.add_argument('--e2e-steps', type=int, default=2)
+    ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the cpu_baseline leg')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- CPU arm (reference path)
+def cpu_reference_run(steps: int, warmup: int, batches_per_step: int, seconds_cap: float | None, optimizer: str):
+    """The reference's stock-torch CPU path over `batches_per_step` batches of 4096 per step."""
+    import torch
+    from oracle import ref_torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    net = ref_torch.make_layers(DIMS, DROPOUT, 'relu')
+    opt = torch.optim.SGD(net.parameters(), lr=LR) if optimizer == 'sgd' else torch.optim.Adam(net.parameters(), lr=1e-3)
+    model, metrics = ref_torch.CpuClassifier(net, opt), ref_torch.CpuMetrics()
+    g = torch.Generator().manual_seed(1234)
+    n = batches_per_step * BATCH
+    x = torch.randn(n, 1, 28, 28, generator=g)
+    y = torch.randint(0, 10, (n,), generator=g)
+    loader = [(x[i:i + BATCH], y[i:i + BATCH]) for i in range(0, n, BATCH)]
+    for _ in range(warmup):
+        ref_torch.train(model, loader[:2], metrics); metrics.reset()
+    done, t0 = 0, time.perf_counter()
+    for _ in range(steps):
+        ref_torch.train(model, loader, metrics); metrics.reset()
+        done += 1
+        if seconds_cap is not None and time.perf_counter() - t0 > seconds_cap:
+            break
+    dt = time.perf_counter() - t0
+    return {'value': done * n / dt, 'seconds': dt, 'steps_done': done, 'cores': cores,
+            'sample': f'{done} x {batches_per_step} batches of {BATCH} (S model, {optimizer}, dropout {DROPOUT}), torch {torch.__version__} CPU'}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    per_step = 16                       # bounded sample: 16 batches of 4096 = 65,536 samples per step
+    r = cpu_reference_run(args.steps, min(args.warmup, 3), per_step, None, args.optimizer)
+    ms = r['seconds'] / max(r['steps_done'], 1) * 1e3
+    line = {
+        'impl': 'reference', 'metric': 'train_samples_per_sec', 'value': r['value'], 'unit': 'samples/s',
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': f'tinysys train handler, MLP(784,256,10) {args.optimizer} batch {BATCH}; CPU sample of '
+                               f'{per_step} batches per step', 'batch': BATCH, 'samples_per_step': per_step * BATCH},
+        'cpu_baseline': {'value': r['value'], 'unit': 'samples/s', 'cores': r['cores'], 'kind': 'port', 'sample': r['sample']},
+        'e2e': {'value': r['value'], 'unit': 'samples/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index: int):
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', f'--id={index}', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
+                                       '-lms', '100'], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self) -> dict:
+        if self.p is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for row in self.f.read().splitlines():
+            c = [t.strip() for t in row.split(',')]
+            if len(c) < 8:
+                continue
+            try:
+                sm.append(float(c[0])); mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), c[4:8]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+# ----------------------------------------------------------------------------- B200 arm
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    from torch import nn
+    import __graft_entry__ as entry
+    entry.build()
+    from torchsystem_b200 import B200Classifier, B200Metrics, DeviceLoader, PinnedLoader, MLP, training, _lib
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    n = args.batches * BATCH
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    x = torch.randn(n, 1, 28, 28, generator=g, device=dev)
+    teacher = torch.randn(784, 10, generator=torch.Generator(device=dev).manual_seed(99), device=dev)
+    y = torch.argmax(x.flatten(1) @ teacher, dim=1)
+
+    torch.manual_seed(0)
+    net = MLP(DIMS[0], DIMS[1], DIMS[2], dropout=DROPOUT, activation=nn.ReLU())
+    opt = torch.optim.SGD(net.parameters(), lr=LR) if args.optimizer == 'sgd' else torch.optim.Adam(net.parameters(), lr=1e-3)
+    model = B200Classifier(net, nn.CrossEntropyLoss(), opt, precision=args.precision, device=dev, max_batch=BATCH)
+    metrics = B200Metrics(device=dev, log_every=0)
+    training.provider.override(training.device, lambda: dev)
+    results = []
+    consumer = __import__('torchsystem_b200.compat', fromlist=['Consumer']).Consumer()
+
+    def on_trained(e: training.Trained):
+        results.append((e.results['loss'].item(), e.results['accuracy'].item()))     # device->host read of the result
+    on_trained.__annotations__ = {'e': training.Trained}
+    consumer.handler(on_trained)
+    training.producer.consumers.clear()
+    training.producer.register(consumer)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(loader, steps, warmup, sample_clocks=False):
+        for _ in range(warmup):
+            training.service.handle('train', model, loader, metrics); metrics.reset()
+        barrier()
+        clocks = ClockSampler(local) if sample_clocks and rank == 0 else None
+        launches0 = _lib.lib.ts_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            training.service.handle('train', model, loader, metrics); metrics.reset()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = _lib.lib.ts_launch_count() - launches0
+        t = torch.tensor([ms, float(launches)], dtype=torch.float64, device=dev)
+        if world > 1:
+            tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
+            ms, launches = tm[0].item(), int(ts[1].item())
+        return ms, int(launches), (clocks.stop() if clocks else None)
+
+    # ---- value: inputs resident in HBM
+    dev_loader = DeviceLoader(x, y, BATCH, device=dev)
+    ms, launches, clocks = timed(dev_loader, args.steps, args.warmup, sample_clocks=True)
+    value = world * n * args.steps / (ms * 1e-3)
+
+    # ---- roofline: one more identical step with CUDA events around every kernel (on the launching stream)
+    _lib.profile_begin()
+    training.service.handle('train', model, dev_loader, metrics); metrics.reset()
+    prof = _lib.profile_end()
+    total_ms = sum(v[0] for v in prof.values())
+    top = max(prof, key=lambda k: prof[k][0])
+    esz = 2 if args.precision == 'bf16' else 4
+    H, D = DIMS[1], DIMS[0]
+    algo_bytes = {   # per launch: what the kernel must read once + write once (DESIGN.md "Kernels")
+        'cast_bf16': BATCH * D * 6,
+        'fwd_gemm': BATCH * D * esz + H * D * esz + H * 4 + BATCH * H * esz,
+        'head': BATCH * H * esz * 2 + BATCH * (8 + 8 + DIMS[2] * 4) + DIMS[2] * H * 4,
+        'head_wgrad': BATCH * H * esz + BATCH * DIMS[2] * 4,
+        'colsum': BATCH * H * esz,
+        'dw_gemm': BATCH * H * esz + BATCH * D * esz + H * D * 4,
+        'optimizer': sum(DIMS[i] * DIMS[i + 1] + DIMS[i + 1] for i in range(2)) * (12 if args.optimizer == 'sgd' else 28),
+    }
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except OSError:
+        pass
+    peak = float(peaks.get('hbm_gbs', 6650.0))
+    top_ms, top_n = prof[top]
+    achieved = algo_bytes.get(top, 0) / (top_ms / top_n * 1e-3) / 1e9 if top_n else 0.0
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(f'{top}:{args.precision}')
+    except OSError:
+        pass
+    step_bytes = BYTES_PER_SAMPLE * n
+    roofline = {
+        'bound': 'hbm', 'kernel': top, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+        'traffic': traffic, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback 6650 GB/s',
+        'algorithmic_bytes_per_launch': algo_bytes.get(top), 'avg_launch_us': top_ms / max(top_n, 1) * 1e3,
+        'kernel_share_of_step': {k: round(v[0] / total_ms, 4) for k, v in prof.items()},
+        'kernel_avg_us': {k: round(v[0] / v[1] * 1e3, 3) for k, v in prof.items()},
+        'step_streaming_gbs': step_bytes * world / (ms / args.steps * 1e-3) / 1e9 / world,
+        'step_streaming_frac': step_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
+    }
+
+    # ---- e2e: host buffers, H2D every step, result read back
+    pin_loader = PinnedLoader(x.cpu(), y.cpu(), BATCH, device=dev, prefetch=3)
+    pin_loader.h2d_bytes = 0
+    e_ms, _, _ = timed(pin_loader, args.e2e_steps, 1)
+    h2d_per_step = pin_loader.h2d_bytes // (args.e2e_steps + 1)
+    e2e = {'value': world * n * args.e2e_steps / (e_ms * 1e-3), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d_per_step,
+           'd2h_bytes_per_step': 32, 'steps': args.e2e_steps, 'ms_per_step': e_ms / args.e2e_steps,
+           'path': 'training.service.handle("train") over PinnedLoader (pinned host -> device on a copy stream, 3 batches ahead)'}
+
+    # ---- cpu_baseline (rank 0, N=1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = cpu_reference_run(1000, 1, 16, args.cpu_seconds, args.optimizer)
+        cpu = {'value': r['value'], 'unit': 'samples/s', 'cores': r['cores'], 'kind': 'port', 'sample': r['sample']}
+
+    if rank == 0:
+        line = {
+            'metric': 'train_samples_per_sec', 'value': value, 'unit': 'samples/s', 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': args.precision, 'data': 'synthetic',
+            'config': {'workload': f'tinysys train handler: MLP(784,256,10) dropout 0.1 ReLU, CrossEntropyLoss, {args.optimizer}, '
+                                   f'batch {BATCH}, {args.batches} batches per step per GPU (BASELINE.json configs[1])',
+                       'batch': BATCH, 'samples_per_step_per_gpu': n, 'optimizer': args.optimizer, 'precision': args.precision,
+                       'parallelism': f'dp{world}', 'l2': f'inputs of one step ({n * 3136 / 1e9:.2f} GB per GPU) exceed the 126 MB L2',
+                       'last_train_result': results[-1] if results else None},
+            'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline, 'cpu_baseline': cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

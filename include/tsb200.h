@@ -1,0 +1,170 @@
+/*
+ * tsb200.h -- C ABI of the B200-native engine behind TorchSystem's training handlers.
+ *
+ * The reference (mapache-software/torch-system 1.4.0) has no FFI: its hot path is reached through
+ * Python structural protocols (examples/tinysys/tinysys/domain.py:10-40). This header is the
+ * boundary a binding for that path would target: plain pointers and sizes, no torch types.
+ * Each entry point names the reference call it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative TS_E_* code otherwise; ts_last_error()
+ *     returns a thread-local, human-readable message for the last failure on this thread;
+ *   - all data pointers are DEVICE pointers on the device the handle was created for, unless
+ *     marked HOST; `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - nothing here synchronises the stream except where stated; nothing falls back to the CPU;
+ *   - the library never allocates device memory: the caller sizes a workspace with
+ *     ts_mlp_workspace_bytes() and hands it over with ts_mlp_set_workspace().
+ *
+ * Parameter layout: all parameters live in ONE flat fp32 buffer in torch order
+ * (layer0.weight [out,in] row-major, layer0.bias, layer1.weight, ...; examples/tinysys/modules/mlp.py:8-11),
+ * each tensor starting at the element offset reported by ts_mlp_param_layout() (4 KiB aligned).
+ * Gradients and the Adam moments use the same layout in buffers of the same size.
+ */
+#ifndef TSB200_H
+#define TSB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TS_ABI_VERSION 1
+
+/* status codes */
+#define TS_OK 0
+#define TS_E_INVALID (-1)   /* bad argument (NULL, size, enum) */
+#define TS_E_CUDA (-2)      /* a CUDA runtime/driver call failed; message has the CUDA error */
+#define TS_E_STATE (-3)     /* call order: parameters / optimizer / workspace not bound */
+#define TS_E_UNSUPPORTED (-4)
+#define TS_E_TOO_LARGE (-5) /* size beyond a stated maximum */
+
+/* activation of the hidden layers (examples/tinysys/main.py:60 uses ReLU; tests/test_storage.py:38 GELU) */
+#define TS_ACT_RELU 0
+#define TS_ACT_GELU 1
+
+/* arithmetic mode of the dense layers */
+#define TS_PREC_F32 0  /* fp32 SIMT everywhere: matches the CPU reference to 1e-5 */
+#define TS_PREC_BF16 1 /* bf16 operands on tcgen05 tensor cores, fp32 accumulate in TMEM: 1e-2 */
+
+/* element type of the `inputs` buffer */
+#define TS_DT_F32 0
+#define TS_DT_BF16 1
+
+/* optimizer (examples/tinysys/main.py:62 ships Adam(lr=1e-3); SGD is the north-star addition) */
+#define TS_OPT_SGD 0
+#define TS_OPT_ADAM 1
+
+typedef struct ts_mlp ts_mlp; /* opaque aggregate handle */
+
+/* Hyper-parameters, torch.optim semantics (momentum/weight decay/amsgrad not supported: 0). */
+typedef struct ts_opt_hyper {
+    double lr;
+    double beta1, beta2; /* Adam only */
+    double eps;          /* Adam only */
+} ts_opt_hyper;
+
+/* One record per fit/evaluate call, written by the fused head kernel (16 bytes, device memory).
+ * `loss` is the batch-mean cross-entropy that Classifier.fit/evaluate return
+ * (examples/tinysys/tinysys/classifier.py:35,39); `n_correct` is what
+ * MulticlassAccuracy.update would count from (argmax, targets) (tinysys/metrics.py:15). */
+typedef struct ts_batch_record {
+    float loss;
+    int32_t n_correct;
+    int32_t n_rows;
+    int32_t reserved;
+} ts_batch_record;
+
+/* Running metric state (device memory, 32 bytes): torcheval Mean + micro MulticlassAccuracy
+ * (examples/tinysys/tinysys/metrics.py:8-27). */
+typedef struct ts_metrics_state {
+    double loss_sum;   /* sum of per-batch mean losses, fp64 like torcheval.Mean */
+    int64_t n_batches; /* Mean's weight: one per update */
+    int64_t n_correct;
+    int64_t n_total;
+} ts_metrics_state;
+
+int32_t ts_abi_version(void);
+const char *ts_last_error(void);
+
+/* ---- aggregate construction: replaces Classifier.__init__ + .to(device)
+ *      (examples/tinysys/tinysys/classifier.py:10-16, tinysys/services/compilation.py:23-34) ---- */
+
+/* dims[n_dims] = {in, hidden..., classes}: (n_dims-2) x [Linear, Dropout(p), act] then Linear. */
+int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims /*HOST*/, int32_t n_dims, int32_t activation,
+                      float dropout_p, int32_t precision, int32_t device);
+int32_t ts_mlp_destroy(ts_mlp *m);
+
+/* offsets[2*(n_dims-1)] (HOST, in elements) of each parameter tensor in the flat buffers; *total = buffer length. */
+int32_t ts_mlp_param_layout(const ts_mlp *m, int64_t *offsets /*HOST*/, int64_t *total /*HOST*/);
+
+/* Alias the caller's parameter and gradient storage (fp32 master weights stay where torch sees them). */
+int32_t ts_mlp_bind_params(ts_mlp *m, float *params, float *grads);
+
+/* replaces torch.optim.Adam/SGD construction (examples/tinysys/main.py:62); moments may be NULL for SGD.
+ * `step` is the number of optimizer steps already taken (resume). */
+int32_t ts_opt_bind(ts_mlp *m, int32_t kind, const ts_opt_hyper *hyper /*HOST*/, float *exp_avg, float *exp_avg_sq,
+                    int64_t step);
+int64_t ts_opt_step_count(const ts_mlp *m);
+
+int64_t ts_mlp_workspace_bytes(const ts_mlp *m, int64_t max_batch);
+int32_t ts_mlp_set_workspace(ts_mlp *m, void *workspace, int64_t bytes, int64_t max_batch);
+
+/* Re-derive the bf16 shadow weights from the fp32 masters (after load_state_dict / manual edits). */
+int32_t ts_mlp_sync_weights(ts_mlp *m, void *stream);
+
+/* ---- hot path ---- */
+
+/* Classifier.fit (examples/tinysys/tinysys/classifier.py:29-35): zero_grad, forward with dropout,
+ * mean cross-entropy, backward, optimizer step; returns the PRE-update argmax and loss.
+ *   inputs       [B, dims[0]] row-major, dtype `inputs_dtype` (the handler's Flatten is a view)
+ *   targets      [B] int64 in [0, classes)
+ *   masks        HOST array of (n_dims-2) device pointers to uint8 keep-masks [B, hidden_l] (values 0/1), or
+ *                NULL to draw the masks in-kernel from Philox4x32-10 keyed by (`seed`, optimizer step, layer)
+ *   predictions  [B] int64 out
+ *   record       one ts_batch_record out (its .loss is the returned loss tensor)
+ */
+int32_t ts_fit_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                    const uint8_t *const *masks /*HOST*/, uint64_t seed, int64_t *predictions,
+                    ts_batch_record *record, void *stream);
+
+/* Data-parallel split of the same call: ts_fit_backward leaves the local mean gradient in `grads`
+ * (caller all-reduces it), ts_opt_apply consumes `grads * grad_scale` (1/world) and updates. */
+int32_t ts_fit_backward(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                        const uint8_t *const *masks /*HOST*/, uint64_t seed, int64_t *predictions,
+                        ts_batch_record *record, void *stream);
+int32_t ts_opt_apply(ts_mlp *m, float grad_scale, void *stream);
+
+/* Classifier.evaluate (examples/tinysys/tinysys/classifier.py:37-39): dropout off, no state change. */
+int32_t ts_eval_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                     int64_t *predictions, ts_batch_record *record, void *stream);
+
+/* ---- metrics: replaces Metrics.update/compute/reset (examples/tinysys/tinysys/metrics.py:13-27) ---- */
+
+/* Fold `count` records of a ring of `ring_len` records, starting at slot `first`, into `state`
+ * in slot order (fp64 adds, same order as successive Mean.update calls). */
+int32_t ts_metrics_accumulate(ts_metrics_state *state, const ts_batch_record *ring, int64_t ring_len, int64_t first,
+                              int64_t count, void *stream);
+/* Metrics.update for tensors that did not come from this engine: counts predictions == targets on the GPU. */
+int32_t ts_metrics_update_raw(ts_metrics_state *state, const float *loss, const int64_t *predictions,
+                              const int64_t *targets, int64_t batch, void *stream);
+int32_t ts_metrics_reset(ts_metrics_state *state, void *stream);
+/* Copies the state to HOST memory; synchronises `stream`. */
+int32_t ts_metrics_read(const ts_metrics_state *state, ts_metrics_state *out /*HOST*/, void *stream);
+
+/* ---- measurement support (no counterpart in the reference, which ships no profiling hooks) ----
+ * Between ts_profile_begin() and ts_profile_end() every kernel launch is bracketed by CUDA events recorded on
+ * the launching stream; ts_profile_end() synchronises them and returns, per kernel kind, the summed device
+ * time in milliseconds and the launch count (arrays of at least ts_profile_kind_count() entries, HOST). */
+int32_t ts_profile_begin(void);
+int32_t ts_profile_end(double *ms_per_kind /*HOST*/, int64_t *launches_per_kind /*HOST*/, int32_t n_kinds);
+int32_t ts_profile_kind_count(void);
+const char *ts_profile_kind_name(int32_t kind);
+
+/* number of kernels this library has launched on the calling process so far (bench.py's gpu_launches) */
+int64_t ts_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSB200_H */

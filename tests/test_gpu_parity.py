@@ -1,0 +1,271 @@
+"""GPU parity tests (run on the B200 box with -m gpu): the CUDA path, called through the C ABI
+(libtsb200.so via ctypes), against the CPU oracle and the golden vectors recorded from the reference.
+
+Tolerances (BASELINE.json north star): predictions and correct-counts bit-exact; loss and updated weights
+within 1e-5 relative in fp32 mode and 1e-2 in bf16 mode."""
+import numpy as np
+import pytest
+import torch
+from torch import nn
+
+from oracle import mlp_numpy as onp
+from tests.golden_util import CASES, load_case, replay, golden_phase_results, assert_params_close
+
+pytestmark = pytest.mark.gpu
+
+ACT = {'relu': onp.ACT_RELU, 'gelu': onp.ACT_GELU}
+OPT = {'adam': onp.OPT_ADAM, 'sgd': onp.OPT_SGD}
+
+
+def build_model(dims, dropout, activation, optimizer, lr, init, precision, max_batch=4096, seed=42):
+    from torchsystem_b200 import B200Classifier, MLP
+    act = nn.ReLU() if activation == 'relu' else nn.GELU()
+    net = MLP(dims[0], dims[1] if len(dims) == 3 else dims[1:-1], dims[-1], dropout=dropout, activation=act)
+    with torch.no_grad():
+        for p, w in zip([q for lin in net.linears() for q in (lin.weight, lin.bias)], init):
+            p.copy_(torch.from_numpy(np.asarray(w)))
+    opt = torch.optim.Adam(net.parameters(), lr=lr) if optimizer == 'adam' else torch.optim.SGD(net.parameters(), lr=lr)
+    return B200Classifier(net, nn.CrossEntropyLoss(), opt, precision=precision, device='cuda:0', max_batch=max_batch,
+                          dropout_seed=seed), net
+
+
+class EngineAdapter:
+    """Gives B200Classifier the replay() interface (numpy in, numpy out)."""
+
+    def __init__(self, model):
+        self.model = model
+
+    def fit(self, x, y, masks):
+        m = None if masks is None else [torch.from_numpy(k).cuda() for k in masks]
+        p, l = self.model.fit(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), masks=m)
+        return p.cpu().numpy(), l.item()
+
+    def evaluate(self, x, y):
+        p, l = self.model.evaluate(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda())
+        return p.cpu().numpy(), l.item()
+
+
+def net_params(net):
+    return [q.detach().cpu().numpy() for lin in net.linears() for q in (lin.weight, lin.bias)]
+
+
+# ------------------------------------------------------------------ golden vectors from the reference run
+@pytest.mark.parametrize('name', CASES)
+def test_f32_replays_reference_golden(name):
+    case = load_case(name)
+    model, net = build_model(case.dims, case.dropout, case.activation, case.optimizer, case.lr, case.init_params(), 'f32',
+                             max_batch=case.batch)
+    losses, preds, phases = replay(case, EngineAdapter(model), onp.OracleMetrics())
+    assert np.array_equal(preds, case.raw['batch_pred']), 'predictions must be bit-exact'
+    np.testing.assert_allclose(losses, case.raw['batch_loss'], rtol=1e-5, atol=1e-6)
+    steps = case.epochs * len(case.batches('train'))
+    assert_params_close(net_params(net), case.final_params(), 1e-5, lr=case.lr, steps=steps, adam=case.optimizer == 'adam')
+    for got, (loss, acc) in zip(phases, golden_phase_results(case)):
+        assert got['accuracy'] == pytest.approx(acc, abs=1e-7)
+        assert got['loss'] == pytest.approx(loss, rel=1e-5)
+    if case.optimizer == 'adam':
+        assert model.engine.step_count == int(case.raw['opt_step'])
+        st = model.optimizer.state[net.linears()[0].weight]
+        assert_params_close([st['exp_avg'].cpu().numpy(), st['exp_avg_sq'].cpu().numpy()],
+                            [case.raw['exp_avg_0'], case.raw['exp_avg_sq_0']], 1e-3, adam=False, what='adam state')
+
+
+def test_fused_metrics_match_golden_events():
+    """B200Metrics fed by the fused records reproduces the Trained / Validated results of the reference run."""
+    from torchsystem_b200 import B200Metrics
+    case = load_case('tinysys_adam_b32')
+    model, _ = build_model(case.dims, case.dropout, case.activation, case.optimizer, case.lr, case.init_params(), 'f32',
+                           max_batch=case.batch)
+    metrics = B200Metrics(device='cuda:0', log_every=0)
+    got, fit_call = [], 0
+    for _ in range(case.epochs):
+        for b, (x, y) in enumerate(case.batches('train'), 1):
+            yt = torch.from_numpy(y).cuda()
+            m = [torch.from_numpy(k).cuda() for k in case.masks(fit_call)]
+            fit_call += 1
+            p, l = model.fit(torch.from_numpy(x).cuda(), yt, masks=m)
+            metrics.update(b, l, p, yt)
+        got.append(metrics.compute()); metrics.reset()
+        for b, (x, y) in enumerate(case.batches('val'), 1):
+            yt = torch.from_numpy(y).cuda()
+            p, l = model.evaluate(torch.from_numpy(x).cuda(), yt)
+            metrics.update(b, l, p, yt)
+        got.append(metrics.compute()); metrics.reset()
+    for r, (loss, acc) in zip(got, golden_phase_results(case)):
+        assert r['accuracy'].item() == pytest.approx(acc, abs=1e-7)
+        assert r['loss'].item() == pytest.approx(loss, rel=1e-5)
+        assert r['loss'].dtype == torch.float64
+
+
+# ------------------------------------------------------------------ seeded comparisons with the oracle at batch 4096
+def synthetic(n, seed=1234):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, 1, 28, 28, generator=g)
+    teacher = torch.randn(784, 10, generator=g)
+    y = torch.argmax(x.flatten(1) @ teacher, dim=1)
+    return x, y
+
+
+def seeded_init(dims, seed=0, bf16=False):
+    torch.manual_seed(seed)
+    out = []
+    for i, o in zip(dims[:-1], dims[1:]):
+        lin = nn.Linear(i, o)
+        w, b = lin.weight.detach(), lin.bias.detach()
+        if bf16:
+            w = w.bfloat16().float()
+        out += [w.numpy().copy(), b.numpy().copy()]
+    return out
+
+
+def mismatch_report(z_margin_fn, got, want):
+    bad = np.nonzero(got != want)[0]
+    return f'{len(bad)} prediction mismatches at rows {bad[:8]}'
+
+
+@pytest.mark.parametrize('optimizer,lr', [('adam', 1e-3), ('sgd', 1e-2)])
+def test_f32_batch4096_against_oracle(optimizer, lr):
+    dims, p, B, steps = [784, 256, 10], 0.1, 4096, 3
+    x, y = synthetic(B * steps + B)
+    init = seeded_init(dims)
+    model, net = build_model(dims, p, 'relu', optimizer, lr, init, 'f32', max_batch=B)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=OPT[optimizer], lr=lr)
+    g = torch.Generator().manual_seed(42)
+    for s in range(steps):
+        xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
+        mask = (torch.rand(B, dims[1], generator=g) >= p).to(torch.uint8)
+        pr, l = model.fit(xb.cuda(), yb.cuda(), masks=[mask.cuda()])
+        opr, ol = oracle.fit(xb.numpy(), yb.numpy(), [mask.numpy()])
+        assert np.array_equal(pr.cpu().numpy(), opr), mismatch_report(None, pr.cpu().numpy(), opr)
+        assert l.item() == pytest.approx(float(ol), rel=1e-5)
+    xb, yb = x[steps * B:], y[steps * B:]
+    pr, l = model.evaluate(xb.cuda(), yb.cuda())
+    opr, ol = oracle.evaluate(xb.numpy(), yb.numpy())
+    assert np.array_equal(pr.cpu().numpy(), opr)
+    assert l.item() == pytest.approx(float(ol), rel=1e-5)
+    assert_params_close(net_params(net), oracle.parameters(), 1e-5, lr=lr, steps=steps, adam=optimizer == 'adam')
+
+
+def test_f32_deep_net_against_oracle():
+    dims, p, B = [784, 128, 64, 10], 0.1, 512
+    x, y = synthetic(B)
+    init = seeded_init(dims)
+    model, net = build_model(dims, p, 'relu', 'adam', 1e-3, init, 'f32', max_batch=B)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=onp.OPT_ADAM, lr=1e-3)
+    g = torch.Generator().manual_seed(3)
+    for s in range(2):
+        masks = [(torch.rand(B, h, generator=g) >= p).to(torch.uint8) for h in dims[1:-1]]
+        pr, l = model.fit(x.cuda(), y.cuda(), masks=[m.cuda() for m in masks])
+        opr, ol = oracle.fit(x.numpy(), y.numpy(), [m.numpy() for m in masks])
+        assert np.array_equal(pr.cpu().numpy(), opr)
+        assert l.item() == pytest.approx(float(ol), rel=1e-5)
+    assert_params_close(net_params(net), oracle.parameters(), 1e-5, lr=1e-3, steps=2)
+
+
+# ------------------------------------------------------------------ edge cases and size-independent properties
+@pytest.mark.parametrize('B', [1, 7, 33, 257])
+def test_ragged_batch_sizes(B):
+    dims = [784, 64, 10]
+    x, y = synthetic(B, seed=5)
+    init = seeded_init(dims)
+    model, _ = build_model(dims, 0.0, 'relu', 'sgd', 0.05, init, 'f32', max_batch=8)   # forces a workspace regrow
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.05)
+    for _ in range(2):
+        pr, l = model.fit(x.cuda(), y.cuda())
+        opr, ol = oracle.fit(x.numpy(), y.numpy(), None)
+        assert np.array_equal(pr.cpu().numpy(), opr)
+        assert l.item() == pytest.approx(float(ol), rel=1e-5, abs=1e-7)
+
+
+def test_evaluate_is_pure_and_partition_independent():
+    """Idempotence + batch-partition independence: per-sample results do not depend on how samples are batched,
+    and evaluate() changes no state; counts add up (a checksum of checksums)."""
+    from torchsystem_b200 import B200Metrics
+    dims = [784, 256, 10]
+    N = 8192
+    x, y = synthetic(N, seed=9)
+    model, net = build_model(dims, 0.1, 'relu', 'adam', 1e-3, seeded_init(dims), 'f32', max_batch=N)
+    before = [w.copy() for w in net_params(net)]
+    xc, yc = x.cuda(), y.cuda()
+    p_all, l_all = model.evaluate(xc, yc)
+    p_again, l_again = model.evaluate(xc, yc)
+    assert torch.equal(p_all, p_again) and l_all.item() == l_again.item()
+    metrics = B200Metrics(device='cuda:0', log_every=0)
+    parts = []
+    for b, i in enumerate(range(0, N, 1000), 1):       # ragged tail of 192
+        p, l = model.evaluate(xc[i:i + 1000], yc[i:i + 1000])
+        metrics.update(b, l, p, yc[i:i + 1000])
+        parts.append(p)
+    assert torch.equal(torch.cat(parts), p_all)
+    loss_sum, n_batches, n_correct, n_total = metrics.counters()
+    assert n_total == N and n_batches == 9
+    assert n_correct == int((p_all == yc).sum().item())
+    for a, b in zip(before, net_params(net)):
+        assert np.array_equal(a, b)
+
+
+def test_zero_lr_step_changes_nothing_and_grads_are_exposed():
+    dims = [784, 64, 10]
+    x, y = synthetic(64, seed=2)
+    init = seeded_init(dims)
+    model, net = build_model(dims, 0.0, 'relu', 'sgd', 0.0, init, 'f32', max_batch=64)
+    model.fit(x.cuda(), y.cuda())
+    for a, b in zip(init, net_params(net)):
+        assert np.array_equal(a, b)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=1.0)
+    ref = [w.copy() for w in oracle.parameters()]
+    oracle.fit(x.numpy(), y.numpy(), None)
+    grads = [r - w for r, w in zip(ref, oracle.parameters())]          # lr = 1: the gradient itself
+    got = [lin_p.grad.cpu().numpy() for lin in net.linears() for lin_p in (lin.weight, lin.bias)]
+    assert_params_close(got, grads, 1e-4, adam=False, what='grads')
+
+
+def test_philox_dropout_is_deterministic_and_active():
+    dims = [784, 256, 10]
+    x, y = synthetic(512, seed=4)
+    outs = []
+    for seed in (42, 42, 43):
+        model, net = build_model(dims, 0.5, 'relu', 'sgd', 0.1, seeded_init(dims), 'f32', max_batch=512, seed=seed)
+        _, l = model.fit(x.cuda(), y.cuda())
+        outs.append((l.item(), net_params(net)[0].copy()))
+    assert outs[0][0] == outs[1][0] and np.array_equal(outs[0][1], outs[1][1])
+    assert outs[0][0] != outs[2][0]
+    model, _ = build_model(dims, 0.0, 'relu', 'sgd', 0.1, seeded_init(dims), 'f32', max_batch=512)
+    _, l0 = model.fit(x.cuda(), y.cuda())
+    assert abs(l0.item() - outs[0][0]) > 1e-4          # dropout changed the forward pass
+
+
+def test_metrics_raw_path_counts_foreign_tensors():
+    from torchsystem_b200 import B200Metrics
+    m = B200Metrics(device='cuda:0', log_every=0)
+    pred = torch.tensor([1, 2, 3, 4], device='cuda:0')
+    tgt = torch.tensor([1, 0, 3, 0], device='cuda:0')
+    m.update(1, torch.tensor(2.0, device='cuda:0'), pred, tgt)
+    m.update(2, torch.tensor(4.0, device='cuda:0'), pred[:1], tgt[:1])
+    r = m.compute()
+    assert r['loss'].item() == 3.0 and r['accuracy'].item() == pytest.approx(3 / 5)
+    m.reset()
+    assert m.counters() == (0.0, 0, 0, 0)
+
+
+def test_errors_are_loud():
+    from torchsystem_b200 import B200Classifier, MLP
+    dims = [784, 64, 10]
+    model, _ = build_model(dims, 0.0, 'relu', 'sgd', 0.1, seeded_init(dims), 'f32', max_batch=16)
+    x, y = synthetic(16)
+    with pytest.raises(RuntimeError):
+        model.fit(x, y)                                   # host tensors: no silent CPU path
+    with pytest.raises(TypeError):
+        model.fit(x.cuda(), y.cuda().int())
+    with pytest.raises(ValueError):
+        model.fit(x.cuda()[:, :, :14], y.cuda())
+    with pytest.raises(RuntimeError):
+        model(x.cuda())
+    net = MLP(784, 64, 10, dropout=0.0, activation=nn.ReLU())
+    with pytest.raises(TypeError):
+        B200Classifier(net, nn.MSELoss(), torch.optim.SGD(net.parameters(), lr=0.1), device='cuda:0')
+    with pytest.raises(NotImplementedError):
+        B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.1, momentum=0.9), device='cuda:0')
+    with pytest.raises(TypeError):
+        B200Classifier(nn.Sequential(nn.Linear(4, 4), nn.Tanh(), nn.Linear(4, 2)), nn.CrossEntropyLoss(),
+                       torch.optim.SGD(net.parameters(), lr=0.1), device='cuda:0')

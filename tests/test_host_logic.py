@@ -1,0 +1,217 @@
+"""CPU tests of the host side: network inspection, identity hashes, the stand-in orchestration layer against
+the real TorchSystem (when /root/reference is present), handler call sequences, sharding."""
+import os
+import subprocess
+import sys
+import textwrap
+from unittest.mock import MagicMock
+
+import pytest
+import torch
+from torch import nn
+
+import __graft_entry__ as entry
+
+entry.build()
+
+from torchsystem_b200 import MLP, training                      # noqa: E402
+from torchsystem_b200 import compat                             # noqa: E402
+from torchsystem_b200.modules import inspect_mlp                # noqa: E402
+from torchsystem_b200.parallel import shard_bounds              # noqa: E402
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REFERENCE = '/root/reference'
+have_reference = os.path.isdir(os.path.join(REFERENCE, 'torchsystem'))
+
+
+def test_inspect_reference_shaped_mlp():
+    spec = inspect_mlp(MLP(784, 256, 10, dropout=0.1, activation=nn.ReLU()))
+    assert spec.dims == [784, 256, 10] and spec.dropout == 0.1 and spec.activation == 'relu'
+    spec = inspect_mlp(MLP(784, [4096, 4096, 4096, 4096], 10, dropout=0.0, activation=nn.ReLU()))
+    assert spec.dims == [784, 4096, 4096, 4096, 4096, 10]
+    seq = nn.Sequential(nn.Linear(8, 16), nn.Dropout(0.2), nn.GELU(), nn.Linear(16, 4))
+    spec = inspect_mlp(seq)
+    assert spec.dims == [8, 16, 4] and spec.activation == 'gelu' and spec.dropout == 0.2
+
+
+@pytest.mark.parametrize('bad', [
+    nn.Sequential(nn.Linear(8, 16), nn.ReLU(), nn.Dropout(0.2), nn.Linear(16, 4)),     # dropout after activation
+    nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4)),
+    nn.Sequential(nn.Linear(8, 4)),
+    nn.Sequential(nn.Linear(8, 16), nn.ReLU(), nn.Linear(8, 4)),
+    nn.Sequential(nn.Linear(8, 16), nn.GELU(approximate='tanh'), nn.Linear(16, 4)),
+])
+def test_inspect_rejects_what_the_engine_cannot_run(bad):
+    with pytest.raises(TypeError):
+        inspect_mlp(bad)
+
+
+def test_mlp_matches_reference_layout_and_state_dict_names():
+    net = MLP(784, 256, 10, dropout=0.1, activation=nn.ReLU())
+    assert list(net.state_dict()) == ['input_layer.weight', 'input_layer.bias', 'output_layer.weight', 'output_layer.bias']
+    net.eval()
+    x = torch.randn(4, 784)
+    want = net.output_layer(torch.relu(net.input_layer(x)))
+    assert torch.equal(net(x), want)
+
+
+def test_identity_hash_goldens():
+    """examples/tinysys/notebook.ipynb:34 and docs/registry.md:50 (reproduced with the stand-in registry)."""
+    class _MLP(MLP):
+        pass
+    _MLP.__name__ = 'MLP'
+    compat.register(_MLP)
+    relu = type('ReLU', (nn.ReLU,), {})
+    compat.register(relu)
+    assert compat.gethash(_MLP(784, 256, 10, dropout=0.1, activation=relu())) == '302adcec37ba79ed6a33d58956391d20'
+    assert compat.gethash(_MLP(784, 256, 10, dropout=0.5, activation=relu())) == 'af51a51a38f7ad81f9523360fafe7068'
+
+
+def test_shard_bounds_equal_and_disjoint():
+    spans = [shard_bounds(1_048_576 + 123, r, 8, 4096) for r in range(8)]
+    assert all(hi - lo == spans[0][1] - spans[0][0] for lo, hi in spans)
+    assert all((hi - lo) % 4096 == 0 for lo, hi in spans)
+    assert all(spans[i][1] == spans[i + 1][0] for i in range(7))
+
+
+# ------------------------------------------------------------------ stand-in orchestration semantics
+@pytest.mark.skipif(compat.HAVE_TORCHSYSTEM, reason='real torchsystem on the path: stand-ins not in use')
+def test_standin_depends_service_consumer():
+    opened = []
+
+    def dep():
+        opened.append('open'); yield 'resource'; opened.append('close')
+
+    def other():
+        return 'override'
+
+    provider = compat.Provider()
+    service = compat.Service(provider=provider)
+
+    @service.handler
+    def do_thing(a, b=compat.Depends(dep)):
+        return a, b
+
+    assert service.handle('do-thing', 1) == (1, 'resource') and opened == ['open', 'close']
+    provider.override(dep, other)
+    assert do_thing(2) == (2, 'override')
+    assert do_thing(2, 'explicit') == (2, 'explicit')
+    with pytest.raises(KeyError):
+        service.handle('missing')
+
+    @compat.event
+    class ModelTrained:
+        value: int
+
+    @compat.event
+    class ModelValidated:
+        value: int
+
+    seen = []
+    consumer = compat.Consumer()
+
+    @consumer.handler
+    def on_any(e: ModelTrained | ModelValidated):
+        seen.append(e.value)
+
+    producer = compat.Producer()
+    producer.register(consumer)
+    producer.dispatch(ModelTrained(1)); producer.dispatch(ModelValidated(2)); producer.dispatch('ignored')
+    assert seen == [1, 2] and 'model-trained' in consumer.handlers
+
+
+@pytest.mark.skipif(compat.HAVE_TORCHSYSTEM, reason='real torchsystem on the path')
+def test_standin_aggregate_hooks():
+    calls = []
+
+    class A(compat.Aggregate):
+        def __init__(self):
+            super().__init__()
+            self.epoch = 0
+
+        def onepoch(self): calls.append(('epoch', self.epoch))
+        def onphase(self): calls.append(('phase', self.phase))
+
+    a = A()
+    a.phase = 'train'; a.phase = 'evaluation'; a.epoch += 1
+    assert calls == [('phase', 'train'), ('phase', 'evaluation'), ('epoch', 1)] and not a.training
+
+
+def _trace_handlers(mod, n_batches=3):
+    """Run iterate() of a handlers module over fakes; return the sequence of observable calls."""
+    log = []
+    model = MagicMock()
+    model.epoch = 0
+    model.fit.side_effect = lambda i, t: (log.append(('fit', i, t)) or ('p', 'l'))
+    model.evaluate.side_effect = lambda i, t: (log.append(('evaluate', i, t)) or ('p', 'l'))
+    metrics = MagicMock()
+    metrics.update.side_effect = lambda b, l, p, t: log.append(('update', b, l, p, t))
+    metrics.compute.side_effect = lambda: (log.append(('compute',)) or {'loss': 0, 'accuracy': 1})
+    metrics.reset.side_effect = lambda: log.append(('reset',))
+
+    class T:
+        def __init__(self, name): self.name = name
+        def to(self, device): log.append(('to', self.name, device)); return self.name
+
+    loader = [(T(f'x{i}'), T(f'y{i}')) for i in range(n_batches)]
+    consumer = (compat.Consumer if mod is training else __import__('torchsystem.services', fromlist=['Consumer']).Consumer)()
+
+    def on_trained(e: mod.Trained): log.append(('Trained', e.results['accuracy']))
+    def on_validated(e: mod.Validated): log.append(('Validated', e.results['accuracy']))
+    def on_iterated(e: mod.Iterated): log.append(('Iterated', e.model.epoch))
+    for h in (on_trained, on_validated, on_iterated):
+        consumer.handler(h)
+    mod.producer.consumers.clear()
+    mod.producer.register(consumer)
+    mod.provider.override(mod.device, lambda: 'cuda:7')
+    mod.service.handle('iterate', model, [('train', loader), ('validation', loader)], metrics)
+    phases = [c.args[0] for c in type(model).phase.mock_calls] if hasattr(type(model), 'phase') else None
+    return log, model.epoch, phases
+
+
+def test_handlers_trace_without_reference():
+    log, epoch, _ = _trace_handlers(training)
+    kinds = [e[0] for e in log]
+    assert kinds.count('fit') == 3 and kinds.count('evaluate') == 3 and kinds.count('update') == 6
+    assert kinds[-1] == 'Iterated' and epoch == 1
+    assert log[0] == ('to', 'x0', 'cuda:7') and ('update', 1, 'l', 'p', 'y0') in log
+    assert kinds.index('Trained') < kinds.index('evaluate') and kinds.count('reset') == 2
+
+
+@pytest.mark.skipif(not have_reference, reason='needs /root/reference (build container only)')
+def test_handlers_trace_equals_unmodified_reference_handlers():
+    """Same observable call sequence as /root/reference/examples/tinysys/tinysys/services/training.py."""
+    code = textwrap.dedent(f'''
+        import sys, json
+        sys.path[:0] = [{ROOT!r}, {REFERENCE!r}, {REFERENCE + '/examples/tinysys'!r}]
+        from tests.test_host_logic import _trace_handlers
+        from torchsystem_b200 import compat, training as mine
+        assert compat.HAVE_TORCHSYSTEM
+        from tinysys.services import training as theirs
+        a = _trace_handlers(theirs)
+        b = _trace_handlers(mine)
+        assert a[0] == b[0] and a[1] == b[1], (a, b)
+        # B200Classifier plugs into the real Aggregate
+        import torchsystem
+        from torchsystem_b200 import B200Classifier
+        assert issubclass(B200Classifier, torchsystem.Aggregate)
+        print('same', len(a[0]))
+    ''')
+    out = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, cwd=ROOT)
+    assert out.returncode == 0 and out.stdout.startswith('same'), out.stderr[-2000:]
+
+
+@pytest.mark.skipif(not have_reference, reason='needs /root/reference (build container only)')
+def test_reference_suite_still_passes_with_this_package_imported(tmp_path):
+    """The reference's own unit tests (DI, services, events, aggregate, registry) with torchsystem_b200 loaded
+    first: the package must not disturb the orchestration layer. test_compiler.py fails on torch >= 2.6 with or
+    without this package and is excluded."""
+    conftest = tmp_path / 'conftest.py'
+    conftest.write_text(f'import sys; sys.path[:0] = [{ROOT!r}, {REFERENCE!r}]\nimport torchsystem_b200\n')
+    import shutil
+    shutil.copytree(os.path.join(REFERENCE, 'tests'), tmp_path / 'tests', ignore=shutil.ignore_patterns('conftest.py', '__pycache__'))
+    out = subprocess.run([sys.executable, '-m', 'pytest', '-q', '-p', 'no:cacheprovider', '--deselect',
+                          'tests/test_compiler.py', str(tmp_path / 'tests'), '-c', str(conftest)],
+                         capture_output=True, text=True, cwd=tmp_path)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
+    assert '17 passed' in out.stdout, out.stdout[-500:]

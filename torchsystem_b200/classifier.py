@@ -1,0 +1,150 @@
+"""B200Classifier: the aggregate the `train` / `validate` / `iterate` handlers drive, with its per-batch
+work done by hand-written sm_100a kernels instead of eager PyTorch.
+
+It honours the reference's `Model` protocol (/root/reference/examples/tinysys/tinysys/domain.py:10-24) and
+mirrors the reference aggregate (/root/reference/examples/tinysys/tinysys/classifier.py:9-39):
+
+    id, epoch, phase, nn, criterion, optimizer          attributes the handlers and consumers read
+    fit(inputs, targets)      -> (predictions, loss)    classifier.py:29-35
+    evaluate(inputs, targets) -> (predictions, loss)    classifier.py:37-39
+
+`nn` stays an ordinary torch Module whose Parameters alias the engine's fp32 master weights, so
+`torch.save(model.nn)`, `load_state_dict` and `gethash(model.nn)` behave as before."""
+from __future__ import annotations
+
+import torch
+from torch import Tensor, nn
+
+from .compat import Aggregate, gethash
+from .engine import Engine
+from .modules import inspect_mlp
+from . import parallel
+
+
+def _check_criterion(criterion: nn.Module) -> None:
+    if not isinstance(criterion, nn.CrossEntropyLoss):
+        raise TypeError(f'B200Classifier fuses CrossEntropyLoss; got {type(criterion).__name__}')
+    if (criterion.weight is not None or criterion.reduction != 'mean' or criterion.label_smoothing != 0.0):
+        raise TypeError('only CrossEntropyLoss() with default weight/reduction/label_smoothing is supported')
+
+
+def _optimizer_config(optimizer: torch.optim.Optimizer):
+    if len(optimizer.param_groups) != 1:
+        raise TypeError('exactly one optimizer param group is supported')
+    g = optimizer.param_groups[0]
+    if isinstance(optimizer, torch.optim.Adam) and type(optimizer) is torch.optim.Adam:
+        if g.get('weight_decay', 0) != 0 or g.get('amsgrad', False) or g.get('maximize', False):
+            raise NotImplementedError('Adam weight_decay / amsgrad / maximize are not supported by the fused optimizer')
+        return 'adam', dict(lr=float(g['lr']), betas=tuple(float(b) for b in g['betas']), eps=float(g['eps']))
+    if type(optimizer) is torch.optim.SGD:
+        if g.get('momentum', 0) != 0 or g.get('weight_decay', 0) != 0 or g.get('nesterov', False) or g.get('maximize', False):
+            raise NotImplementedError('SGD momentum / weight_decay / nesterov / maximize are not supported by the fused optimizer')
+        return 'sgd', dict(lr=float(g['lr']))
+    raise TypeError(f'unsupported optimizer {type(optimizer).__name__}: the fused step implements Adam and SGD')
+
+
+class B200Classifier(Aggregate):
+    """Drop-in for the reference `Classifier(nn, criterion, optimizer)`.
+
+    precision   'bf16' (tcgen05 tensor cores, fp32 accumulate; parity 1e-2) or 'f32' (SIMT; parity 1e-5)
+    dropout_seed  key of the in-kernel Philox dropout masks (pass `masks=` to `fit` to supply them instead)
+    process_group  torch.distributed group for data-parallel training (default: the world, if initialised)
+    """
+
+    def __init__(self, nn: nn.Module, criterion: nn.Module, optimizer: torch.optim.Optimizer, *, precision: str = 'bf16',
+                 device: str | torch.device = 'cuda', max_batch: int = 4096, dropout_seed: int = 42, process_group=None):
+        super().__init__()
+        _check_criterion(criterion)
+        spec = inspect_mlp(nn)
+        kind, hyper = _optimizer_config(optimizer)
+        dev = torch.device(device)
+        if dev.type == 'cuda' and dev.index is None:
+            dev = torch.device('cuda', torch.cuda.current_device())
+        self.nn = nn
+        self.epoch = 0
+        self.criterion = criterion
+        self.optimizer = optimizer
+        self.precision = precision
+        self.dropout_seed = int(dropout_seed)
+        self._params = [p for lin in spec.linears for p in (lin.weight, lin.bias)]
+        owned = {id(p) for p in self._params}
+        extra = [p for p in nn.parameters() if id(p) not in owned]
+        if extra:
+            raise TypeError('the network has parameters outside its Linear layers; unsupported')
+        nn.to(dev)
+        self.engine = Engine(spec, precision, dev, max_batch=max_batch)
+        self.engine.adopt(self._params)
+        step = self._adopt_optimizer_state(kind)
+        self.engine.bind_optimizer(kind, step=step, **hyper)
+        self._dp = parallel.DataParallel(process_group)
+        if self._dp.world > 1:
+            self._dp.broadcast_(self.engine.params)          # same initial weights on every rank
+            self.engine.sync_weights()
+
+    # ------------------------------------------------------------------ identity / hooks
+    @property
+    def id(self) -> str:
+        return gethash(self.nn)          # classifier.py:18-20
+
+    def onphase(self) -> None:
+        # weights may have been replaced between phases (repository.restore -> load_state_dict)
+        self.engine.sync_weights()
+
+    def sync(self) -> None:
+        """Call after editing `nn`'s weights by hand; re-derives the bf16 operand copies."""
+        self.engine.sync_weights()
+
+    def _adopt_optimizer_state(self, kind: str) -> int:
+        """Resume: take over exp_avg / exp_avg_sq / step if the torch optimizer already holds state, and make
+        the optimizer's state dict alias the engine's buffers from now on."""
+        step = 0
+        if kind != 'adam':
+            return step
+        eng = self.engine
+        eng.exp_avg = torch.zeros_like(eng.params)
+        eng.exp_avg_sq = torch.zeros_like(eng.params)
+        for i, p in enumerate(self._params):
+            o, n = eng.offsets[i], p.numel()
+            st = self.optimizer.state.get(p, {})
+            if 'exp_avg' in st:
+                eng.exp_avg[o:o + n].copy_(st['exp_avg'].reshape(-1))
+                eng.exp_avg_sq[o:o + n].copy_(st['exp_avg_sq'].reshape(-1))
+                step = int(st['step']) if not isinstance(st['step'], Tensor) else int(st['step'].item())
+            self.optimizer.state[p] = {'step': torch.tensor(float(step)),
+                                       'exp_avg': eng.exp_avg[o:o + n].view(p.shape),
+                                       'exp_avg_sq': eng.exp_avg_sq[o:o + n].view(p.shape)}
+        return step
+
+    def sync_optimizer_state(self) -> None:
+        """Refresh the `step` entries torch's optimizer.state_dict() reports (the moments alias live buffers)."""
+        step = self.engine.step_count
+        for p in self._params:
+            st = self.optimizer.state.get(p)
+            if st is not None and 'step' in st:
+                st['step'] = torch.tensor(float(step))
+
+    def _refresh_hyper(self) -> None:
+        kind, hyper = _optimizer_config(self.optimizer)      # follows lr schedulers / manual edits
+        want = (kind, hyper['lr'], tuple(hyper.get('betas', (0.9, 0.999))), hyper.get('eps', 1e-8))
+        if want != self.engine._hyper:
+            self.engine.bind_optimizer(kind, step=self.engine.step_count, **hyper)
+
+    # ------------------------------------------------------------------ the hot path
+    def forward(self, input: Tensor) -> Tensor:
+        raise RuntimeError('B200Classifier fuses forward, loss and argmax; call fit() or evaluate()')
+
+    def fit(self, inputs: Tensor, targets: Tensor, *, masks=None) -> tuple[Tensor, Tensor]:
+        """One optimisation step on a batch; returns (argmax of the pre-update logits, mean CE loss).
+        `masks`: optional list of [B, hidden] 0/1 keep-masks, one per hidden layer (parity runs)."""
+        g = self.optimizer.param_groups[0]
+        if g['lr'] != self.engine._hyper[1]:
+            self._refresh_hyper()
+        if self._dp.world == 1:
+            return self.engine.fit(inputs, targets, masks, self.dropout_seed)
+        out = self.engine.fit(inputs, targets, masks, self.dropout_seed + self._dp.rank, update=False)
+        self._dp.all_reduce_sum_(self.engine.grads)
+        self.engine.apply(1.0 / self._dp.world)
+        return out
+
+    def evaluate(self, inputs: Tensor, targets: Tensor) -> tuple[Tensor, Tensor]:
+        return self.engine.evaluate(inputs, targets)

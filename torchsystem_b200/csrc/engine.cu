@@ -1,0 +1,585 @@
+// C ABI of the tsb200 engine (include/tsb200.h): handle management, workspace carving and the
+// per-batch kernel sequences behind Classifier.fit / Classifier.evaluate / Metrics.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "kernels.h"
+
+namespace tsb {
+
+static thread_local char g_err[1024] = "";
+long long g_launch_count = 0;
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+// ---- optional per-kernel timing: CUDA events recorded on the launching stream around each launch.
+enum { K_CAST = 0, K_FWD_GEMM, K_HEAD, K_HEAD_WGRAD, K_COLSUM, K_DW_GEMM, K_DX_GEMM, K_OPT, K_COUNT };
+static const char *const kKindNames[K_COUNT] = {"cast_bf16", "fwd_gemm", "head", "head_wgrad", "colsum",
+                                                "dw_gemm",   "dx_gemm",  "optimizer"};
+struct ProfPair { int kind; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfPair> g_prof;
+
+struct ProfScope {
+    int kind; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
+    ProfScope(int k, cudaStream_t s) : kind(k), st(s) {
+        if (!g_prof_on) return;
+        if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) { a = b = nullptr; return; }
+        cudaEventRecord(a, st);
+    }
+    ~ProfScope() {
+        if (!a) return;
+        cudaEventRecord(b, st);
+        g_prof.push_back({kind, a, b});
+    }
+};
+
+}  // namespace tsb
+
+using namespace tsb;
+
+struct ts_mlp {
+    int n_layers = 0;  // dense layers
+    int dims[kMaxLayers + 1] = {0};
+    int act = TS_ACT_RELU;
+    float p = 0.0f, scale = 1.0f;
+    int prec = TS_PREC_F32;
+    int device = 0;
+    int sm_count = 148;
+
+    // flat parameter layout (torch order: W0, b0, W1, b1, ...)
+    int n_tensors = 0;
+    int64_t off[2 * kMaxLayers] = {0}, cnt[2 * kMaxLayers] = {0};
+    int max_split[2 * kMaxLayers] = {0};
+    int64_t total = 0, n_chunks = 0;
+    std::vector<int32_t> chunk_tensor_host;
+
+    float *params = nullptr, *grads = nullptr;
+    bool opt_bound = false;
+    int opt_kind = TS_OPT_SGD;
+    ts_opt_hyper hyper = {0, 0, 0, 0};
+    float *exp_avg = nullptr, *exp_avg_sq = nullptr;
+    int64_t step = 0;
+
+    // workspace (caller-owned memory)
+    bool ws_set = false;
+    int64_t max_batch = 0;
+    int32_t *d_chunk_tensor = nullptr;
+    unsigned int *ticket = nullptr;
+    HeadPartial *head_partials = nullptr;
+    void *acts[kMaxLayers] = {nullptr};
+    float *upre[kMaxLayers] = {nullptr};
+    float *dz = nullptr;
+    void *dh[2] = {nullptr, nullptr};
+    float *partials = nullptr;
+    int64_t partial_off[2 * kMaxLayers] = {0}, partial_stride[2 * kMaxLayers] = {0};
+    __nv_bfloat16 *x_bf16 = nullptr, *shadow = nullptr;
+    int64_t shadow_off[kMaxLayers] = {0};
+    int64_t shadow_total = 0;
+
+    int hidden_layers() const { return n_layers - 1; }
+    int classes() const { return dims[n_layers]; }
+    size_t elem() const { return prec == TS_PREC_BF16 ? 2 : 4; }
+};
+
+namespace {
+
+struct Carver {
+    char *base;
+    int64_t used = 0;
+    explicit Carver(void *b) : base(reinterpret_cast<char *>(b)) {}
+    void *take(int64_t bytes) {
+        void *p = base ? base + used : nullptr;
+        used += round_up(bytes < 1 ? 1 : bytes, 256);
+        return p;
+    }
+};
+
+// Lays the workspace out; with base == nullptr only measures it.
+int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
+    Carver c(base);
+    const int L = m->n_layers;
+    m->d_chunk_tensor = (int32_t *)c.take(m->n_chunks * 4);
+    m->ticket = (unsigned int *)c.take(256);
+    m->head_partials = (HeadPartial *)c.take(sizeof(HeadPartial) * kMaxHeadBlocks);
+    int maxH = 0;
+    for (int l = 0; l < L - 1; ++l) {
+        const int H = m->dims[l + 1];
+        maxH = H > maxH ? H : maxH;
+        m->acts[l] = c.take(Bm * H * (int64_t)m->elem());
+        m->upre[l] = (m->act == TS_ACT_GELU) ? (float *)c.take(Bm * H * 4) : nullptr;
+    }
+    m->dz = (float *)c.take(Bm * m->classes() * 4);
+    m->dh[0] = c.take(Bm * maxH * (int64_t)m->elem());
+    m->dh[1] = (L > 2) ? c.take(Bm * maxH * (int64_t)m->elem()) : nullptr;
+    int64_t pfloats = 0;
+    for (int t = 0; t < m->n_tensors; ++t) {
+        m->partial_stride[t] = round_up(m->cnt[t], 4);
+        m->partial_off[t] = pfloats;
+        if (m->max_split[t] > 1) pfloats += (int64_t)m->max_split[t] * m->partial_stride[t];
+    }
+    m->partials = (float *)c.take(pfloats * 4);
+    if (m->prec == TS_PREC_BF16) {
+        m->x_bf16 = (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2);
+        m->shadow = (__nv_bfloat16 *)c.take(m->shadow_total * 2);
+    }
+    return c.used;
+}
+
+int splits_for(int64_t B, int max_split, int granule, int *k_chunk) {
+    int64_t s = (B + 63) / 64;
+    if (s > max_split) s = max_split;
+    if (s < 1) s = 1;
+    int64_t kc = round_up((B + s - 1) / s, granule);
+    *k_chunk = (int)kc;
+    return (int)((B + kc - 1) / kc);
+}
+
+DropoutSpec drop_spec(const ts_mlp *m, const uint8_t *const *masks, uint64_t seed, int layer, bool training) {
+    DropoutSpec d;
+    d.mask = (masks && training) ? masks[layer] : nullptr;
+    d.seed = seed;
+    d.step = (uint32_t)m->step;
+    d.layer = (uint32_t)layer;
+    d.p = training ? m->p : 0.0f;
+    d.scale = training ? m->scale : 1.0f;
+    return d;
+}
+
+int check_ready(const ts_mlp *m, int64_t B, bool need_opt) {
+    TS_REQUIRE(m != nullptr, TS_E_INVALID, "null handle");
+    TS_REQUIRE(m->params && m->grads, TS_E_STATE, "parameters not bound: call ts_mlp_bind_params first");
+    TS_REQUIRE(m->ws_set, TS_E_STATE, "workspace not set: call ts_mlp_set_workspace first");
+    TS_REQUIRE(!need_opt || m->opt_bound, TS_E_STATE, "optimizer not bound: call ts_opt_bind first");
+    TS_REQUIRE(B >= 1 && B <= m->max_batch, TS_E_INVALID, "batch %lld outside [1, %lld] (workspace capacity)",
+               (long long)B, (long long)m->max_batch);
+    return TS_OK;
+}
+
+// Forward through the hidden layers; *a_last receives the last hidden activation.
+int forward_hidden(ts_mlp *m, const void *x, int x_dtype, int64_t B, const uint8_t *const *masks, uint64_t seed,
+                   bool training, const void **a0_out, const void **a_last, cudaStream_t st) {
+    const void *a_in = x;
+    if (m->prec == TS_PREC_F32) {
+        TS_REQUIRE(x_dtype == TS_DT_F32, TS_E_UNSUPPORTED, "TS_PREC_F32 takes fp32 inputs");
+    } else if (x_dtype == TS_DT_F32) {
+        ProfScope ps(K_CAST, st);
+        int rc = launch_cast_bf16((const float *)x, m->x_bf16, B * m->dims[0], st);
+        if (rc) return rc;
+        a_in = m->x_bf16;
+    } else {
+        TS_REQUIRE(x_dtype == TS_DT_BF16, TS_E_INVALID, "unknown inputs dtype %d", x_dtype);
+    }
+    *a0_out = a_in;
+    for (int l = 0; l < m->n_layers - 1; ++l) {
+        const int in = m->dims[l], out = m->dims[l + 1];
+        const DropoutSpec ds = drop_spec(m, masks, seed, l, training);
+        int rc;
+        ProfScope ps(K_FWD_GEMM, st);
+        if (m->prec == TS_PREC_F32) {
+            SgemmArgs g{};
+            g.A = (const float *)a_in; g.sam = in; g.sak = 1;
+            g.B = m->params + m->off[2 * l]; g.sbk = 1; g.sbn = in;
+            g.C = (float *)m->acts[l]; g.ldc = out;
+            g.M = (int)B; g.N = out; g.K = in;
+            g.k_chunk = (int)round_up(in, 16); g.c_split_stride = 0;
+            g.bias = m->params + m->off[2 * l + 1];
+            g.U_out = m->upre[l];
+            g.drop = ds; g.act = m->act; g.training = training && m->p > 0.0f;
+            rc = launch_sgemm(EPI_FWD, g, 1, st);
+        } else {
+            TcGemmArgs g{};
+            g.A = (const __nv_bfloat16 *)a_in; g.a_major = TC_MAJOR_K; g.lda = in;
+            g.B = m->shadow + m->shadow_off[l]; g.b_major = TC_MAJOR_K; g.ldb = in;
+            g.M = (int)B; g.N = out; g.K = in;
+            g.epi = TC_EPI_FWD; g.out = m->acts[l]; g.ldo = out; g.splits = 1; g.split_stride = 0;
+            g.bias = m->params + m->off[2 * l + 1];
+            g.drop = ds; g.training = training && m->p > 0.0f;
+            rc = launch_tc_gemm(g, m->sm_count, st);
+        }
+        if (rc) return rc;
+        a_in = m->acts[l];
+    }
+    *a_last = a_in;
+    return TS_OK;
+}
+
+void fill_head(const ts_mlp *m, HeadArgs &h, const void *a_last, const int64_t *y, int64_t B, int64_t *pred,
+               ts_batch_record *rec) {
+    const int L = m->n_layers;
+    h.A = a_last;
+    h.W = m->params + m->off[2 * (L - 1)];
+    h.bias = m->params + m->off[2 * (L - 1) + 1];
+    h.y = y; h.B = B; h.K = m->dims[L - 1]; h.C = m->dims[L];
+    h.a_is_bf16 = m->prec == TS_PREC_BF16;
+    h.round_w_bf16 = m->prec == TS_PREC_BF16;
+    h.pred = pred; h.dz = nullptr; h.dH = nullptr; h.U_prev = nullptr;
+    h.act = m->act;
+    h.partials = m->head_partials; h.ticket = m->ticket; h.record = rec;
+}
+
+int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, cudaStream_t st) {
+    OptArgs o{};
+    o.n_tensors = m->n_tensors;
+    bool any_partial = false;
+    for (int t = 0; t < m->n_tensors; ++t) {
+        o.t[t].offset = m->off[t]; o.t[t].count = m->cnt[t];
+        o.t[t].partial_off = m->partial_off[t]; o.t[t].partial_stride = m->partial_stride[t];
+        const int l = t / 2;
+        o.t[t].shadow_off = (m->prec == TS_PREC_BF16 && t % 2 == 0 && l < m->n_layers - 1) ? m->shadow_off[l] : -1;
+        o.t[t].nsplit = nsplit ? nsplit[t] : 0;
+        any_partial |= o.t[t].nsplit > 0;
+    }
+    if (!update && !any_partial) return TS_OK;
+    o.params = m->params; o.grads = m->grads; o.exp_avg = m->exp_avg; o.exp_avg_sq = m->exp_avg_sq;
+    o.partials = m->partials; o.shadow = m->shadow; o.chunk_tensor = m->d_chunk_tensor;
+    o.kind = m->opt_kind; o.update = update ? 1 : 0; o.grad_scale = grad_scale;
+    if (update) {
+        m->step += 1;
+        const double b1 = m->hyper.beta1, b2 = m->hyper.beta2;
+        o.lr = (float)m->hyper.lr;
+        o.beta1 = (float)b1; o.beta2 = (float)b2; o.eps = (float)m->hyper.eps;
+        o.one_minus_beta1 = (float)(1.0 - b1); o.one_minus_beta2 = (float)(1.0 - b2);
+        if (m->opt_kind == TS_OPT_ADAM) {
+            // host doubles exactly as torch computes them (adam.py: bias_correction*, step_size)
+            const double bc1 = 1.0 - pow(b1, (double)m->step);
+            const double bc2 = 1.0 - pow(b2, (double)m->step);
+            o.step_size = (float)(m->hyper.lr / bc1);
+            o.bc2_sqrt = (float)sqrt(bc2);
+        }
+    }
+    ProfScope ps(K_OPT, st);
+    return launch_optimizer(o, m->n_chunks, st);
+}
+
+int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
+             uint64_t seed, int64_t *pred, ts_batch_record *rec, cudaStream_t st, bool update) {
+    int rc = check_ready(m, B, update);
+    if (rc) return rc;
+    TS_REQUIRE(x && y && pred && rec, TS_E_INVALID, "null inputs/targets/predictions/record pointer");
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    const int L = m->n_layers;
+    const bool bf16 = m->prec == TS_PREC_BF16;
+    const void *a0 = nullptr, *a_last = nullptr;
+    rc = forward_hidden(m, x, x_dtype, B, masks, seed, true, &a0, &a_last, st);
+    if (rc) return rc;
+
+    HeadArgs h{};
+    fill_head(m, h, a_last, y, B, pred, rec);
+    h.dz = m->dz; h.dH = m->dh[0];
+    h.U_prev = m->upre[L - 2];
+    h.drop = drop_spec(m, masks, seed, L - 2, true);
+    { ProfScope ps(K_HEAD, st); rc = launch_head(h, m->sm_count, st); }
+    if (rc) return rc;
+
+    int nsplit[2 * kMaxLayers] = {0};
+    {   // last layer: dW = dz^T a_last, db = colsum(dz)
+        const int tw = 2 * (L - 1), tb = tw + 1;
+        int kc;
+        const int S = splits_for(B, m->max_split[tw], 1, &kc);
+        float *wp = S > 1 ? m->partials + m->partial_off[tw] : m->grads + m->off[tw];
+        float *bp = S > 1 ? m->partials + m->partial_off[tb] : m->grads + m->off[tb];
+        ProfScope ps(K_HEAD_WGRAD, st);
+        rc = launch_head_wgrad(a_last, bf16, m->dz, B, m->dims[L - 1], m->dims[L], wp, m->partial_stride[tw], bp,
+                               m->partial_stride[tb], S, st);
+        if (rc) return rc;
+        nsplit[tw] = nsplit[tb] = S > 1 ? S : 0;
+    }
+    int cur = 0;
+    for (int l = L - 2; l >= 0; --l) {
+        const int in = m->dims[l], out = m->dims[l + 1];
+        const void *dHl = m->dh[cur];
+        const void *a_prev = (l == 0) ? a0 : m->acts[l - 1];
+        const int tw = 2 * l, tb = tw + 1;
+        {   // db_l = colsum(dH_l)
+            int kc;
+            const int S = splits_for(B, m->max_split[tb], 1, &kc);
+            float *bp = S > 1 ? m->partials + m->partial_off[tb] : m->grads + m->off[tb];
+            ProfScope ps(K_COLSUM, st);
+            rc = launch_colsum(dHl, bf16, B, out, bp, m->partial_stride[tb], S, st);
+            if (rc) return rc;
+            nsplit[tb] = S > 1 ? S : 0;
+        }
+        {   // dW_l[out,in] = dH_l^T a_prev, batch is the contraction (split across CTAs)
+            int kc;
+            const int S = splits_for(B, m->max_split[tw], bf16 ? 64 : 16, &kc);
+            float *wp = S > 1 ? m->partials + m->partial_off[tw] : m->grads + m->off[tw];
+            ProfScope ps(K_DW_GEMM, st);
+            if (!bf16) {
+                SgemmArgs g{};
+                g.A = (const float *)dHl; g.sam = 1; g.sak = out;
+                g.B = (const float *)a_prev; g.sbk = in; g.sbn = 1;
+                g.C = wp; g.ldc = in; g.M = out; g.N = in; g.K = (int)B;
+                g.k_chunk = kc; g.c_split_stride = m->partial_stride[tw];
+                rc = launch_sgemm(EPI_STORE, g, S, st);
+            } else {
+                TcGemmArgs g{};
+                g.A = (const __nv_bfloat16 *)dHl; g.a_major = TC_MAJOR_MN; g.lda = out;
+                g.B = (const __nv_bfloat16 *)a_prev; g.b_major = TC_MAJOR_MN; g.ldb = in;
+                g.M = out; g.N = in; g.K = (int)B;
+                g.epi = TC_EPI_STORE_F32; g.out = wp; g.ldo = in; g.splits = S; g.split_stride = m->partial_stride[tw];
+                rc = launch_tc_gemm(g, m->sm_count, st);
+            }
+            if (rc) return rc;
+            nsplit[tw] = S > 1 ? S : 0;
+        }
+        if (l > 0) {   // dH_{l-1} = (dH_l W_l) * act'(layer l-1) * keep/(1-p)
+            const DropoutSpec ds = drop_spec(m, masks, seed, l - 1, true);
+            ProfScope ps(K_DX_GEMM, st);
+            if (!bf16) {
+                SgemmArgs g{};
+                g.A = (const float *)dHl; g.sam = out; g.sak = 1;
+                g.B = m->params + m->off[tw]; g.sbk = in; g.sbn = 1;
+                g.C = (float *)m->dh[cur ^ 1]; g.ldc = in; g.M = (int)B; g.N = in; g.K = out;
+                g.k_chunk = (int)round_up(out, 16); g.c_split_stride = 0;
+                g.A_prev = (const float *)m->acts[l - 1]; g.U_prev = m->upre[l - 1];
+                g.drop = ds; g.act = m->act; g.training = m->p > 0.0f;
+                rc = launch_sgemm(EPI_ACTGRAD, g, 1, st);
+            } else {
+                TcGemmArgs g{};
+                g.A = (const __nv_bfloat16 *)dHl; g.a_major = TC_MAJOR_K; g.lda = out;
+                g.B = m->shadow + m->shadow_off[l]; g.b_major = TC_MAJOR_MN; g.ldb = in;
+                g.M = (int)B; g.N = in; g.K = out;
+                g.epi = TC_EPI_ACTGRAD; g.out = m->dh[cur ^ 1]; g.ldo = in; g.splits = 1;
+                g.A_prev = (const __nv_bfloat16 *)m->acts[l - 1];
+                g.drop = ds; g.training = m->p > 0.0f;
+                rc = launch_tc_gemm(g, m->sm_count, st);
+            }
+            if (rc) return rc;
+            cur ^= 1;
+        }
+    }
+    return run_optimizer(m, nsplit, update, 1.0f, st);
+}
+
+}  // namespace
+
+// ======================================================================================= C ABI
+extern "C" {
+
+int32_t ts_abi_version(void) { return TS_ABI_VERSION; }
+const char *ts_last_error(void) { return g_err; }
+int64_t ts_launch_count(void) { return g_launch_count; }
+
+int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t activation, float dropout_p,
+                      int32_t precision, int32_t device) {
+    TS_REQUIRE(out && dims, TS_E_INVALID, "null out/dims");
+    *out = nullptr;
+    TS_REQUIRE(n_dims >= 3 && n_dims <= kMaxLayers + 1, TS_E_INVALID,
+               "n_dims = %d: need input, at least one hidden layer, classes (3..%d entries)", n_dims, kMaxLayers + 1);
+    for (int i = 0; i < n_dims; ++i) TS_REQUIRE(dims[i] >= 1, TS_E_INVALID, "dims[%d] = %d", i, dims[i]);
+    TS_REQUIRE(activation == TS_ACT_RELU || activation == TS_ACT_GELU, TS_E_INVALID, "unknown activation %d", activation);
+    TS_REQUIRE(dropout_p >= 0.0f && dropout_p < 1.0f, TS_E_INVALID, "dropout %g outside [0,1)", dropout_p);
+    TS_REQUIRE(precision == TS_PREC_F32 || precision == TS_PREC_BF16, TS_E_INVALID, "unknown precision %d", precision);
+    TS_REQUIRE(dims[n_dims - 1] <= kMaxClasses, TS_E_UNSUPPORTED, "at most %d classes", kMaxClasses);
+    for (int i = 1; i < n_dims - 1; ++i)
+        TS_REQUIRE(dims[i] % 8 == 0, TS_E_UNSUPPORTED, "hidden width %d must be a multiple of 8", dims[i]);
+    if (precision == TS_PREC_BF16) {
+        TS_REQUIRE(activation == TS_ACT_RELU, TS_E_UNSUPPORTED, "TS_PREC_BF16 supports ReLU only (use TS_PREC_F32 for GELU)");
+        TS_REQUIRE(dims[0] % 8 == 0, TS_E_UNSUPPORTED, "TS_PREC_BF16 needs an input width that is a multiple of 8 (TMA pitch)");
+    }
+    int n_dev = 0;
+    TS_CUDA_CHECK(cudaGetDeviceCount(&n_dev));
+    TS_REQUIRE(device >= 0 && device < n_dev, TS_E_INVALID, "device %d of %d", device, n_dev);
+    int major = 0, sms = 0;
+    TS_CUDA_CHECK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    TS_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    TS_REQUIRE(major == 10, TS_E_UNSUPPORTED, "this library is built for sm_100a only; device %d is sm_%dx", device, major);
+
+    ts_mlp *m = new (std::nothrow) ts_mlp();
+    TS_REQUIRE(m, TS_E_INVALID, "out of host memory");
+    m->n_layers = n_dims - 1;
+    for (int i = 0; i < n_dims; ++i) m->dims[i] = dims[i];
+    m->act = activation; m->p = dropout_p; m->scale = 1.0f / (float)(1.0 - (double)dropout_p);
+    m->prec = precision; m->device = device; m->sm_count = sms;
+    m->n_tensors = 2 * m->n_layers;
+    int64_t o = 0, so = 0;
+    for (int l = 0; l < m->n_layers; ++l) {
+        const int64_t in = dims[l], outw = dims[l + 1];
+        m->off[2 * l] = o; m->cnt[2 * l] = in * outw; o += round_up(in * outw, kChunk);
+        m->off[2 * l + 1] = o; m->cnt[2 * l + 1] = outw; o += round_up(outw, kChunk);
+        // split-K budget: enough CTAs for two waves, none for matrices that already fill the machine
+        const int64_t tiles = ((outw + 127) / 128) * ((in + 127) / 128);
+        int64_t s = (2 * sms + tiles - 1) / tiles;
+        s = s < 1 ? 1 : (s > kMaxSplits ? kMaxSplits : s);
+        m->max_split[2 * l] = (l == m->n_layers - 1) ? kMaxSplits : (int)s;
+        m->max_split[2 * l + 1] = kMaxSplits;
+        if (l < m->n_layers - 1) { m->shadow_off[l] = so; so += round_up(in * outw, 128); }
+    }
+    m->shadow_total = so;
+    m->total = o;
+    m->n_chunks = o / kChunk;
+    m->chunk_tensor_host.assign((size_t)m->n_chunks, -1);
+    for (int t = 0; t < m->n_tensors; ++t)
+        for (int64_t c = m->off[t] / kChunk; c < (m->off[t] + round_up(m->cnt[t], kChunk)) / kChunk; ++c)
+            m->chunk_tensor_host[(size_t)c] = t;
+    *out = m;
+    return TS_OK;
+}
+
+int32_t ts_mlp_destroy(ts_mlp *m) {
+    delete m;
+    return TS_OK;
+}
+
+int32_t ts_mlp_param_layout(const ts_mlp *m, int64_t *offsets, int64_t *total) {
+    TS_REQUIRE(m && offsets && total, TS_E_INVALID, "null argument");
+    for (int t = 0; t < m->n_tensors; ++t) offsets[t] = m->off[t];
+    *total = m->total;
+    return TS_OK;
+}
+
+int32_t ts_mlp_bind_params(ts_mlp *m, float *params, float *grads) {
+    TS_REQUIRE(m && params && grads, TS_E_INVALID, "null argument");
+    TS_REQUIRE(((uintptr_t)params % 256 == 0) && ((uintptr_t)grads % 256 == 0), TS_E_INVALID,
+               "flat parameter/gradient buffers must be 256-byte aligned");
+    m->params = params;
+    m->grads = grads;
+    return TS_OK;
+}
+
+int32_t ts_opt_bind(ts_mlp *m, int32_t kind, const ts_opt_hyper *hyper, float *exp_avg, float *exp_avg_sq, int64_t step) {
+    TS_REQUIRE(m && hyper, TS_E_INVALID, "null argument");
+    TS_REQUIRE(kind == TS_OPT_SGD || kind == TS_OPT_ADAM, TS_E_INVALID, "unknown optimizer kind %d", kind);
+    TS_REQUIRE(kind == TS_OPT_SGD || (exp_avg && exp_avg_sq), TS_E_INVALID, "Adam needs exp_avg and exp_avg_sq buffers");
+    TS_REQUIRE(step >= 0, TS_E_INVALID, "negative step");
+    m->opt_kind = kind; m->hyper = *hyper; m->exp_avg = exp_avg; m->exp_avg_sq = exp_avg_sq; m->step = step;
+    m->opt_bound = true;
+    return TS_OK;
+}
+
+int64_t ts_opt_step_count(const ts_mlp *m) { return m ? m->step : -1; }
+
+int64_t ts_mlp_workspace_bytes(const ts_mlp *m, int64_t max_batch) {
+    if (!m || max_batch < 1) { set_error("ts_mlp_workspace_bytes: bad argument"); return TS_E_INVALID; }
+    ts_mlp tmp = *m;   // carve() writes pointers; measure on a copy
+    return carve(&tmp, nullptr, max_batch);
+}
+
+int32_t ts_mlp_set_workspace(ts_mlp *m, void *workspace, int64_t bytes, int64_t max_batch) {
+    TS_REQUIRE(m && workspace, TS_E_INVALID, "null argument");
+    TS_REQUIRE((uintptr_t)workspace % 256 == 0, TS_E_INVALID, "workspace must be 256-byte aligned");
+    TS_REQUIRE(max_batch >= 1, TS_E_INVALID, "max_batch %lld", (long long)max_batch);
+    const int64_t need = ts_mlp_workspace_bytes(m, max_batch);
+    TS_REQUIRE(bytes >= need, TS_E_INVALID, "workspace of %lld bytes < %lld needed for batch %lld", (long long)bytes,
+               (long long)need, (long long)max_batch);
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    carve(m, workspace, max_batch);
+    m->max_batch = max_batch;
+    // one-time set-up copies (synchronous): chunk map, ticket
+    TS_CUDA_CHECK(cudaMemcpy(m->d_chunk_tensor, m->chunk_tensor_host.data(), (size_t)m->n_chunks * 4, cudaMemcpyHostToDevice));
+    TS_CUDA_CHECK(cudaMemset(m->ticket, 0, 256));
+    m->ws_set = true;
+    return TS_OK;
+}
+
+int32_t ts_mlp_sync_weights(ts_mlp *m, void *stream) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    if (m->prec != TS_PREC_BF16) return TS_OK;
+    TS_REQUIRE(m->params && m->ws_set, TS_E_STATE, "bind parameters and workspace before ts_mlp_sync_weights");
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    for (int l = 0; l < m->n_layers - 1; ++l) {
+        int rc = launch_cast_bf16(m->params + m->off[2 * l], m->shadow + m->shadow_off[l], m->cnt[2 * l], (cudaStream_t)stream);
+        if (rc) return rc;
+    }
+    return TS_OK;
+}
+
+int32_t ts_fit_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                    const uint8_t *const *masks, uint64_t seed, int64_t *predictions, ts_batch_record *record, void *stream) {
+    return fit_impl(m, inputs, inputs_dtype, targets, batch, masks, seed, predictions, record, (cudaStream_t)stream, true);
+}
+
+int32_t ts_fit_backward(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                        const uint8_t *const *masks, uint64_t seed, int64_t *predictions, ts_batch_record *record, void *stream) {
+    return fit_impl(m, inputs, inputs_dtype, targets, batch, masks, seed, predictions, record, (cudaStream_t)stream, false);
+}
+
+int32_t ts_opt_apply(ts_mlp *m, float grad_scale, void *stream) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    TS_REQUIRE(m->params && m->grads && m->ws_set && m->opt_bound, TS_E_STATE, "bind parameters, optimizer and workspace first");
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    return run_optimizer(m, nullptr, true, grad_scale, (cudaStream_t)stream);
+}
+
+int32_t ts_eval_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                     int64_t *predictions, ts_batch_record *record, void *stream) {
+    int rc = check_ready(m, batch, false);
+    if (rc) return rc;
+    TS_REQUIRE(inputs && targets && predictions && record, TS_E_INVALID, "null inputs/targets/predictions/record pointer");
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    const void *a0 = nullptr, *a_last = nullptr;
+    rc = forward_hidden(m, inputs, inputs_dtype, batch, nullptr, 0, false, &a0, &a_last, (cudaStream_t)stream);
+    if (rc) return rc;
+    HeadArgs h{};
+    fill_head(m, h, a_last, targets, batch, predictions, record);
+    h.drop = drop_spec(m, nullptr, 0, m->n_layers - 2, false);
+    ProfScope ps(K_HEAD, (cudaStream_t)stream);
+    return launch_head(h, m->sm_count, (cudaStream_t)stream);
+}
+
+int32_t ts_metrics_accumulate(ts_metrics_state *state, const ts_batch_record *ring, int64_t ring_len, int64_t first,
+                              int64_t count, void *stream) {
+    TS_REQUIRE(state && ring && ring_len > 0 && first >= 0 && count >= 0 && count <= ring_len, TS_E_INVALID,
+               "bad ring arguments (len %lld, first %lld, count %lld)", (long long)ring_len, (long long)first, (long long)count);
+    return launch_metrics_accumulate(state, ring, ring_len, first % ring_len, count, (cudaStream_t)stream);
+}
+
+int32_t ts_metrics_update_raw(ts_metrics_state *state, const float *loss, const int64_t *predictions, const int64_t *targets,
+                              int64_t batch, void *stream) {
+    TS_REQUIRE(state && loss && predictions && targets && batch >= 0, TS_E_INVALID, "null argument");
+    return launch_metrics_update_raw(state, loss, predictions, targets, batch, (cudaStream_t)stream);
+}
+
+int32_t ts_metrics_reset(ts_metrics_state *state, void *stream) {
+    TS_REQUIRE(state, TS_E_INVALID, "null state");
+    TS_CUDA_CHECK(cudaMemsetAsync(state, 0, sizeof(ts_metrics_state), (cudaStream_t)stream));
+    return TS_OK;
+}
+
+int32_t ts_metrics_read(const ts_metrics_state *state, ts_metrics_state *out, void *stream) {
+    TS_REQUIRE(state && out, TS_E_INVALID, "null argument");
+    TS_CUDA_CHECK(cudaMemcpyAsync(out, state, sizeof(ts_metrics_state), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    TS_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    return TS_OK;
+}
+
+int32_t ts_profile_begin(void) {
+    for (auto &p : g_prof) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    g_prof.clear();
+    g_prof_on = true;
+    return TS_OK;
+}
+
+int32_t ts_profile_end(double *ms_per_kind, int64_t *launches_per_kind, int32_t n_kinds) {
+    g_prof_on = false;
+    TS_REQUIRE(ms_per_kind && launches_per_kind && n_kinds >= K_COUNT, TS_E_INVALID, "need room for %d kinds", K_COUNT);
+    for (int i = 0; i < n_kinds; ++i) { ms_per_kind[i] = 0.0; launches_per_kind[i] = 0; }
+    for (auto &p : g_prof) {
+        TS_CUDA_CHECK(cudaEventSynchronize(p.b));
+        float ms = 0.0f;
+        TS_CUDA_CHECK(cudaEventElapsedTime(&ms, p.a, p.b));
+        ms_per_kind[p.kind] += ms;
+        launches_per_kind[p.kind] += 1;
+        cudaEventDestroy(p.a);
+        cudaEventDestroy(p.b);
+    }
+    g_prof.clear();
+    return TS_OK;
+}
+
+int32_t ts_profile_kind_count(void) { return K_COUNT; }
+const char *ts_profile_kind_name(int32_t kind) { return (kind >= 0 && kind < K_COUNT) ? kKindNames[kind] : ""; }
+
+}  // extern "C"

@@ -1,0 +1,131 @@
+// Internal launcher API shared by engine.cu, simt_kernels.cu and tc_gemm.cu.
+#pragma once
+
+#include "common.cuh"
+
+namespace tsb {
+
+constexpr int kMaxLayers = 8;          // dense layers per aggregate
+constexpr int kMaxClasses = 32;        // width of the last layer handled by the fused head kernel
+constexpr int kChunk = 1024;           // flat-buffer alignment of every parameter tensor (elements)
+constexpr int kMaxSplits = 32;         // split-K partials per tensor
+constexpr int kMaxHeadBlocks = 1024;   // head-kernel grid cap (partials buffer size)
+
+// ---------------------------------------------------------------- fp32 SIMT GEMM (precision mode F32)
+enum { EPI_STORE = 0, EPI_FWD = 1, EPI_ACTGRAD = 2 };
+
+struct SgemmArgs {
+    const float *A, *B;
+    float *C;
+    int M, N, K;
+    int64_t sam, sak, sbk, sbn;  // A(m,k) = A[m*sam + k*sak], B(k,n) = B[k*sbk + n*sbn]
+    int ldc;
+    int k_chunk;                 // K range per blockIdx.z (multiple of 16)
+    int64_t c_split_stride;      // elements between split outputs
+    // epilogue operands
+    const float *bias;           // EPI_FWD
+    float *U_out;                // EPI_FWD, GELU: post-dropout pre-activation
+    const float *A_prev;         // EPI_ACTGRAD, ReLU: the layer's own output
+    const float *U_prev;         // EPI_ACTGRAD, GELU
+    DropoutSpec drop;
+    int act;
+    int training;
+};
+int launch_sgemm(int epi, const SgemmArgs &a, int splits, cudaStream_t st);
+
+// ---------------------------------------------------------------- fused head: last Linear + CE + argmax + dZ + dA
+struct HeadPartial {
+    float loss_sum;
+    int correct;
+};
+
+struct HeadArgs {
+    const void *A;        // [B, K] last hidden activation (float or bf16)
+    const float *W;       // [C, K] fp32 master
+    const float *bias;    // [C]
+    const int64_t *y;     // [B]
+    int64_t B;
+    int K, C;
+    int a_is_bf16;        // element type of A and dH
+    int round_w_bf16;     // bf16 mode: contract with bf16-rounded weights (what the shadow holds)
+    int64_t *pred;        // [B]
+    float *dz;            // [B, C] or nullptr (evaluate)
+    void *dH;             // [B, K] or nullptr
+    const float *U_prev;  // GELU: pre-activation of the last hidden layer
+    DropoutSpec drop;     // dropout of the last hidden layer (for the activation gradient)
+    int act;
+    HeadPartial *partials;
+    unsigned int *ticket;
+    ts_batch_record *record;
+};
+int launch_head(const HeadArgs &a, int sm_count, cudaStream_t st);
+
+// dW_last[c,k] = sum_r dz[r,c] * A[r,k], db_last[c] = sum_r dz[r,c]; `splits` row ranges -> partials
+int launch_head_wgrad(const void *A, int a_is_bf16, const float *dz, int64_t B, int K, int C, float *w_partial,
+                      int64_t w_stride, float *b_partial, int64_t b_stride, int splits, cudaStream_t st);
+
+// column sums of X[B,H] (float or bf16) over `splits` row ranges -> partial[s*stride + h]
+int launch_colsum(const void *X, int is_bf16, int64_t B, int H, float *partial, int64_t stride, int splits,
+                  cudaStream_t st);
+
+// ---------------------------------------------------------------- optimizer over the flat buffers
+struct TensorDesc {
+    int64_t offset;       // element offset in the flat buffers
+    int64_t count;        // elements
+    int64_t partial_off;  // element offset of this tensor's partials in the partial scratch
+    int64_t partial_stride;
+    int64_t shadow_off;   // element offset in the bf16 shadow buffer, -1 if none
+    int32_t nsplit;       // 0: gradient already in `grads`; >0: sum this many partials
+};
+
+struct OptArgs {
+    TensorDesc t[2 * kMaxLayers];
+    int n_tensors;
+    float *params, *grads, *exp_avg, *exp_avg_sq;
+    const float *partials;
+    __nv_bfloat16 *shadow;
+    const int32_t *chunk_tensor;
+    int kind;
+    int update;          // 0: only reduce partials into grads (data-parallel backward)
+    float grad_scale;
+    float lr, beta1, beta2, eps, one_minus_beta1, one_minus_beta2, step_size, bc2_sqrt;
+};
+int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st);
+
+int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st);
+
+// ---------------------------------------------------------------- metrics
+int launch_metrics_accumulate(ts_metrics_state *state, const ts_batch_record *ring, int64_t ring_len, int64_t first,
+                              int64_t count, cudaStream_t st);
+int launch_metrics_update_raw(ts_metrics_state *state, const float *loss, const int64_t *pred, const int64_t *tgt,
+                              int64_t B, cudaStream_t st);
+
+}  // namespace tsb
+
+// ---------------------------------------------------------------- tcgen05 bf16 GEMM (precision mode BF16), tc_gemm.cu
+namespace tsb {
+
+enum { TC_EPI_STORE_F32 = 0, TC_EPI_FWD = 1, TC_EPI_ACTGRAD = 2 };
+enum { TC_MAJOR_K = 0, TC_MAJOR_MN = 1 };
+
+// D[M,N] = A[M,K] * B[K,N], bf16 operands fed by TMA, fp32 accumulation in TMEM.
+//   a_major K : A stored [M][K] (row pitch lda)     a_major MN : A stored [K][M]
+//   b_major K : B stored [N][K] (row pitch ldb)     b_major MN : B stored [K][N]
+struct TcGemmArgs {
+    const __nv_bfloat16 *A, *B;
+    int a_major, b_major;
+    int64_t lda, ldb;
+    int M, N, K;
+    int epi;
+    void *out;             // STORE_F32: float [splits][M][ldo]; FWD / ACTGRAD: bf16 [M][ldo]
+    int64_t ldo;
+    int splits;            // split-K (STORE_F32 only)
+    int64_t split_stride;  // elements between split outputs
+    const float *bias;             // FWD: [N]
+    const __nv_bfloat16 *A_prev;   // ACTGRAD: the layer's own bf16 output [M][ldo]
+    DropoutSpec drop;
+    int training;
+};
+int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st);
+
+}  // namespace tsb

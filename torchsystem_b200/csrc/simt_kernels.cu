@@ -1,0 +1,528 @@
+// SIMT kernels of the tsb200 engine: the fp32 dense path (1e-5 parity mode), the fused head
+// (last Linear + cross-entropy + argmax + dZ + dA, shared by both precision modes), gradient
+// reductions, the flat optimizer and the metric accumulators. sm_100a only.
+#include "kernels.h"
+
+namespace tsb {
+
+// =====================================================================================
+// fp32 GEMM, 64x64x16 tiles, 256 threads, 4x4 outputs per thread, optional split-K.
+// Generic strides cover the three contractions of a Linear layer:
+//   forward  Y = X W^T   (A K-contiguous, B K-contiguous)      mlp.py:14,17
+//   dX = dY W            (A K-contiguous, B N-contiguous)      autograd of the same
+//   dW = dY^T X          (A M-contiguous, B N-contiguous), K = batch, split across blockIdx.z
+// =====================================================================================
+template <int EPI>
+__global__ void __launch_bounds__(256) sgemm_kernel(SgemmArgs p) {
+    __shared__ __align__(16) float As[16][68];
+    __shared__ __align__(16) float Bs[16][68];
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+    const int kb = blockIdx.z * p.k_chunk;
+    const int ke = min(p.K, kb + p.k_chunk);
+    const int ty = tid >> 4, tx = tid & 15;
+    const bool a_kc = (p.sak == 1), b_kc = (p.sbk == 1);
+
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+
+    for (int k0 = kb; k0 < ke; k0 += 16) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int m, k;
+            if (a_kc) { k = tid & 15; m = (tid >> 4) + i * 16; } else { m = tid & 63; k = (tid >> 6) + i * 4; }
+            const int gm = m0 + m, gk = k0 + k;
+            As[k][m] = (gm < p.M && gk < ke) ? p.A[(int64_t)gm * p.sam + (int64_t)gk * p.sak] : 0.0f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int n, k;
+            if (b_kc) { k = tid & 15; n = (tid >> 4) + i * 16; } else { n = tid & 63; k = (tid >> 6) + i * 4; }
+            const int gn = n0 + n, gk = k0 + k;
+            Bs[k][n] = (gn < p.N && gk < ke) ? p.B[(int64_t)gk * p.sbk + (int64_t)gn * p.sbn] : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const float4 a = *reinterpret_cast<const float4 *>(&As[k][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4 *>(&Bs[k][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+            const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+
+    float *C = p.C + (int64_t)blockIdx.z * p.c_split_stride;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gm = m0 + ty * 4 + i;
+        if (gm >= p.M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gn = n0 + tx * 4 + j;
+            if (gn >= p.N) continue;
+            const int64_t o = (int64_t)gm * p.ldc + gn;
+            float v = acc[i][j];
+            if (EPI == EPI_FWD) {
+                // Linear bias, then Dropout, then the activation: mlp.py:14-16
+                float u = v + p.bias[gn];
+                if (p.training) u *= p.drop.factor(gm, gn, p.N);
+                if (p.U_out) p.U_out[o] = u;
+                v = (p.act == TS_ACT_RELU) ? fmaxf(u, 0.0f) : gelu_f(u);
+            } else if (EPI == EPI_ACTGRAD) {
+                // dH = dA * act'(.) * keep/(1-p); ReLU uses the sign of its output (threshold_backward)
+                const float keep = p.training ? p.drop.factor(gm, gn, p.N) : 1.0f;
+                if (p.act == TS_ACT_RELU) v = (p.A_prev[o] > 0.0f) ? v * keep : 0.0f;
+                else v = v * gelu_grad_f(p.U_prev[o]) * keep;
+            }
+            C[o] = v;
+        }
+    }
+}
+
+int launch_sgemm(int epi, const SgemmArgs &a, int splits, cudaStream_t st) {
+    dim3 grid((a.N + 63) / 64, (a.M + 63) / 64, splits);
+    if (epi == EPI_STORE) sgemm_kernel<EPI_STORE><<<grid, 256, 0, st>>>(a);
+    else if (epi == EPI_FWD) sgemm_kernel<EPI_FWD><<<grid, 256, 0, st>>>(a);
+    else sgemm_kernel<EPI_ACTGRAD><<<grid, 256, 0, st>>>(a);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// =====================================================================================
+// Fused head. One warp per row: logits (K-long dot products against W held in shared memory),
+// log-softmax / NLL, first-max argmax, dZ = (softmax - onehot)/B, then dA = dZ W and the hidden
+// activation gradient -> dH. Loss sum and correct count are reduced warp -> block -> grid (last
+// block done finalises in a fixed order), so Metrics never re-reads logits or predictions.
+//   classifier.py:23-27 (forward, loss), :35/:39 (argmax), metrics.py:14-15 (what is counted)
+// =====================================================================================
+template <typename T>
+__device__ __forceinline__ void load4(const T *p, float (&v)[4]);
+template <>
+__device__ __forceinline__ void load4<float>(const float *p, float (&v)[4]) {
+    const float4 t = *reinterpret_cast<const float4 *>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+template <>
+__device__ __forceinline__ void load4<__nv_bfloat16>(const __nv_bfloat16 *p, float (&v)[4]) {
+    const uint2 t = *reinterpret_cast<const uint2 *>(p);
+    const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162 *>(&t.x);
+    const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162 *>(&t.y);
+    v[0] = __low2float(lo); v[1] = __high2float(lo); v[2] = __low2float(hi); v[3] = __high2float(hi);
+}
+__device__ __forceinline__ void store4(float *p, const float (&v)[4]) {
+    *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16 *p, const float (&v)[4]) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
+    __nv_bfloat162 hi = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 t;
+    t.x = *reinterpret_cast<uint32_t *>(&lo);
+    t.y = *reinterpret_cast<uint32_t *>(&hi);
+    *reinterpret_cast<uint2 *>(p) = t;
+}
+
+template <typename T, int MAXC>
+__global__ void __launch_bounds__(256) head_kernel(HeadArgs p) {
+    extern __shared__ __align__(16) float Ws[];  // [C][K]
+    __shared__ float s_loss[8];
+    __shared__ int s_corr[8];
+    __shared__ bool s_last;
+
+    const int K = p.K, C = p.C;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < C * K; i += blockDim.x) {
+        const float w = p.W[i];
+        Ws[i] = p.round_w_bf16 ? round_bf16(w) : w;
+    }
+    __syncthreads();
+
+    const T *A = reinterpret_cast<const T *>(p.A);
+    T *dH = reinterpret_cast<T *>(p.dH);
+    const float inv_B = 1.0f / (float)p.B;
+    float loss_acc = 0.0f;
+    int corr_acc = 0;
+
+    for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < p.B; r += (int64_t)gridDim.x * 8) {
+        const T *a_row = A + r * K;
+        float z[MAXC];
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) z[c] = 0.0f;
+        for (int k = lane * 4; k < K; k += 128) {
+            float a4[4];
+            load4<T>(a_row + k, a4);
+#pragma unroll
+            for (int c = 0; c < MAXC; ++c) {
+                if (c < C) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&Ws[c * K + k]);
+                    z[c] = fmaf(a4[0], w.x, z[c]);
+                    z[c] = fmaf(a4[1], w.y, z[c]);
+                    z[c] = fmaf(a4[2], w.z, z[c]);
+                    z[c] = fmaf(a4[3], w.w, z[c]);
+                }
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c)
+            if (c < C) z[c] = warp_sum(z[c]) + p.bias[c];
+
+        // every lane now holds the full logit row
+        float mx = z[0];
+        int arg = 0;
+#pragma unroll
+        for (int c = 1; c < MAXC; ++c)
+            if (c < C && z[c] > mx) { mx = z[c]; arg = c; }   // strict '>' : first maximum wins, like torch.argmax
+        float s = 0.0f;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c)
+            if (c < C) s += expf(z[c] - mx);
+        const float lse = mx + logf(s);
+        const int yy = (int)p.y[r];
+        float zy = 0.0f;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c)
+            if (c == yy) zy = z[c];
+        float row_loss = lse - zy;
+        if (yy < 0 || yy >= C) row_loss = __int_as_float(0x7fc00000);  // target outside [0,C): poison the loss
+        loss_acc += row_loss;
+        corr_acc += (arg == yy);
+        if (lane == 0) p.pred[r] = arg;
+
+        if (p.dz != nullptr) {
+            float dzv[MAXC];
+#pragma unroll
+            for (int c = 0; c < MAXC; ++c)
+                dzv[c] = (c < C) ? (expf(z[c] - lse) - (c == yy ? 1.0f : 0.0f)) * inv_B : 0.0f;
+            if (lane == 0) {
+#pragma unroll
+                for (int c = 0; c < MAXC; ++c)
+                    if (c < C) p.dz[r * C + c] = dzv[c];
+            }
+            if (dH != nullptr) {
+                for (int k = lane * 4; k < K; k += 128) {
+                    float d[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                    for (int c = 0; c < MAXC; ++c) {
+                        if (c < C) {
+                            const float4 w = *reinterpret_cast<const float4 *>(&Ws[c * K + k]);
+                            d[0] = fmaf(dzv[c], w.x, d[0]);
+                            d[1] = fmaf(dzv[c], w.y, d[1]);
+                            d[2] = fmaf(dzv[c], w.z, d[2]);
+                            d[3] = fmaf(dzv[c], w.w, d[3]);
+                        }
+                    }
+                    if (p.act == TS_ACT_RELU) {
+                        float a4[4];
+                        load4<T>(a_row + k, a4);
+                        const float sc = (p.drop.p > 0.0f) ? p.drop.scale : 1.0f;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) d[i] = (a4[i] > 0.0f) ? d[i] * sc : 0.0f;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            d[i] = d[i] * gelu_grad_f(p.U_prev[r * K + k + i]) * p.drop.factor(r, k + i, K);
+                    }
+                    store4(dH + r * K + k, d);
+                }
+            }
+        }
+    }
+
+    // warp -> block -> grid reduction of (loss sum, correct count)
+    if (lane == 0) { s_loss[warp] = loss_acc; s_corr[warp] = corr_acc; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float l = 0.0f;
+        int c = 0;
+        for (int w = 0; w < 8; ++w) { l += s_loss[w]; c += s_corr[w]; }
+        p.partials[blockIdx.x].loss_sum = l;
+        p.partials[blockIdx.x].correct = c;
+        __threadfence();
+        const unsigned int t = atomicAdd(p.ticket, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last && warp == 0) {
+        __threadfence();
+        float l = 0.0f;
+        int c = 0;
+        for (int b = lane; b < (int)gridDim.x; b += 32) {
+            const volatile HeadPartial *q = p.partials + b;
+            l += q->loss_sum;
+            c += q->correct;
+        }
+        l = warp_sum(l);
+        c = warp_sum(c);
+        if (lane == 0) {
+            p.record->loss = l / (float)p.B;   // reduction='mean'
+            p.record->n_correct = c;
+            p.record->n_rows = (int32_t)p.B;
+            p.record->reserved = 0;
+            *p.ticket = 0u;                    // ready for the next launch on this stream
+        }
+    }
+}
+
+int launch_head(const HeadArgs &a, int sm_count, cudaStream_t st) {
+    TS_REQUIRE(a.C >= 1 && a.C <= kMaxClasses, TS_E_UNSUPPORTED, "head kernel supports 1..%d classes, got %d",
+               kMaxClasses, a.C);
+    TS_REQUIRE(a.K % 8 == 0, TS_E_UNSUPPORTED, "last hidden width must be a multiple of 8, got %d", a.K);
+    const size_t smem = (size_t)a.C * a.K * sizeof(float);
+    TS_REQUIRE(smem <= 200 * 1024, TS_E_TOO_LARGE, "classes*hidden = %d exceeds the head kernel's 51200-element weight tile",
+               a.C * a.K);
+    int per_sm = (int)((220 * 1024) / (smem + 1024));
+    if (per_sm > 4) per_sm = 4;
+    if (per_sm < 1) per_sm = 1;
+    int64_t want = (a.B + 31) / 32;   // >= 4 rows per warp
+    int grid = (int)(want < 1 ? 1 : want);
+    if (grid > sm_count * per_sm) grid = sm_count * per_sm;
+    if (grid > kMaxHeadBlocks) grid = kMaxHeadBlocks;
+
+#define TS_HEAD_LAUNCH(T, MAXC)                                                                                  \
+    do {                                                                                                         \
+        if (smem > 48 * 1024)                                                                                    \
+            TS_CUDA_CHECK(cudaFuncSetAttribute(head_kernel<T, MAXC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                               (int)smem));                                                      \
+        head_kernel<T, MAXC><<<grid, 256, smem, st>>>(a);                                                        \
+    } while (0)
+
+    if (a.a_is_bf16) {
+        if (a.C <= 16) TS_HEAD_LAUNCH(__nv_bfloat16, 16); else TS_HEAD_LAUNCH(__nv_bfloat16, 32);
+    } else {
+        if (a.C <= 16) TS_HEAD_LAUNCH(float, 16); else TS_HEAD_LAUNCH(float, 32);
+    }
+#undef TS_HEAD_LAUNCH
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// =====================================================================================
+// dW_last / db_last partials: thread per hidden column k, dz rows broadcast from shared memory.
+// =====================================================================================
+template <typename T, int MAXC>
+__global__ void __launch_bounds__(128) head_wgrad_kernel(const T *__restrict__ A, const float *__restrict__ dz, int64_t B,
+                                                         int K, int C, float *__restrict__ w_partial, int64_t w_stride,
+                                                         float *__restrict__ b_partial, int64_t b_stride, int rows_per_split) {
+    __shared__ float sdz[64][MAXC];
+    const int k = blockIdx.x * 128 + threadIdx.x;
+    const int s = blockIdx.y;
+    const int64_t r0 = (int64_t)s * rows_per_split;
+    const int64_t r1 = min(B, r0 + rows_per_split);
+    float acc[MAXC];
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) acc[c] = 0.0f;
+    float bsum = 0.0f;   // thread c < C of block x == 0 also sums column c of dz
+    for (int64_t rt = r0; rt < r1; rt += 64) {
+        const int nr = (int)min((int64_t)64, r1 - rt);
+        for (int i = threadIdx.x; i < 64 * MAXC; i += 128) {
+            const int rr = i / MAXC, c = i % MAXC;
+            sdz[rr][c] = (rr < nr && c < C) ? dz[(rt + rr) * C + c] : 0.0f;
+        }
+        __syncthreads();
+        if (k < K) {
+            for (int rr = 0; rr < nr; ++rr) {
+                const float a = to_f32(A[(rt + rr) * K + k]);
+#pragma unroll
+                for (int c = 0; c < MAXC; ++c) acc[c] = fmaf(sdz[rr][c], a, acc[c]);
+            }
+        }
+        if (blockIdx.x == 0 && threadIdx.x < C)
+            for (int rr = 0; rr < nr; ++rr) bsum += sdz[rr][threadIdx.x];
+        __syncthreads();
+    }
+    if (k < K) {
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c)
+            if (c < C) w_partial[(int64_t)s * w_stride + (int64_t)c * K + k] = acc[c];
+    }
+    if (blockIdx.x == 0 && threadIdx.x < C) b_partial[(int64_t)s * b_stride + threadIdx.x] = bsum;
+}
+
+int launch_head_wgrad(const void *A, int a_is_bf16, const float *dz, int64_t B, int K, int C, float *w_partial,
+                      int64_t w_stride, float *b_partial, int64_t b_stride, int splits, cudaStream_t st) {
+    const int rows = (int)((B + splits - 1) / splits);
+    dim3 grid((K + 127) / 128, splits);
+#define TS_WG(T, MAXC)                                                                                       \
+    head_wgrad_kernel<T, MAXC><<<grid, 128, 0, st>>>(reinterpret_cast<const T *>(A), dz, B, K, C, w_partial, \
+                                                     w_stride, b_partial, b_stride, rows)
+    if (a_is_bf16) { if (C <= 16) TS_WG(__nv_bfloat16, 16); else TS_WG(__nv_bfloat16, 32); }
+    else { if (C <= 16) TS_WG(float, 16); else TS_WG(float, 32); }
+#undef TS_WG
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// =====================================================================================
+// Column sums (hidden-layer bias gradients): thread per column, `splits` row ranges.
+// =====================================================================================
+template <typename T>
+__global__ void __launch_bounds__(128) colsum_kernel(const T *__restrict__ X, int64_t B, int H, float *__restrict__ partial,
+                                                     int64_t stride, int rows_per_split) {
+    const int h = blockIdx.x * 128 + threadIdx.x;
+    if (h >= H) return;
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t r1 = min(B, r0 + rows_per_split);
+    float acc = 0.0f;
+    for (int64_t r = r0; r < r1; ++r) acc += to_f32(X[r * H + h]);
+    partial[(int64_t)blockIdx.y * stride + h] = acc;
+}
+
+int launch_colsum(const void *X, int is_bf16, int64_t B, int H, float *partial, int64_t stride, int splits,
+                  cudaStream_t st) {
+    const int rows = (int)((B + splits - 1) / splits);
+    dim3 grid((H + 127) / 128, splits);
+    if (is_bf16)
+        colsum_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(reinterpret_cast<const __nv_bfloat16 *>(X), B, H, partial, stride, rows);
+    else
+        colsum_kernel<float><<<grid, 128, 0, st>>>(reinterpret_cast<const float *>(X), B, H, partial, stride, rows);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// =====================================================================================
+// Flat optimizer: one block per 1024-element chunk of the flat parameter buffer; sums the
+// split partials (fixed order), optionally applies SGD / Adam exactly as torch's single-tensor
+// CPU path does (torch/optim/adam.py _single_tensor_adam, sgd.py _single_tensor_sgd), and
+// refreshes the bf16 shadow of weight matrices.
+// =====================================================================================
+__global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
+    const int tix = p.chunk_tensor[blockIdx.x];
+    if (tix < 0) return;
+    const TensorDesc d = p.t[tix];
+    const int64_t i0 = (int64_t)blockIdx.x * kChunk + threadIdx.x * 4;
+    const int64_t j0 = i0 - d.offset;
+    if (j0 >= d.count) return;
+    const int n = (int)min((int64_t)4, d.count - j0);
+
+    float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    if (d.nsplit > 0) {
+        const float *q = p.partials + d.partial_off + j0;
+        if (n == 4) {   // partial_stride is a multiple of 4 and partial_off 16-byte aligned
+            for (int s = 0; s < d.nsplit; ++s) {
+                const float4 v = *reinterpret_cast<const float4 *>(q + (int64_t)s * d.partial_stride);
+                g[0] += v.x; g[1] += v.y; g[2] += v.z; g[3] += v.w;
+            }
+        } else {
+            for (int s = 0; s < d.nsplit; ++s)
+                for (int e = 0; e < n; ++e) g[e] += q[(int64_t)s * d.partial_stride + e];
+        }
+        for (int e = 0; e < n; ++e) p.grads[i0 + e] = g[e];
+    } else {
+        for (int e = 0; e < n; ++e) g[e] = p.grads[i0 + e];
+    }
+    if (!p.update) return;
+
+    for (int e = 0; e < n; ++e) {
+        const int64_t i = i0 + e;
+        const float grad = g[e] * p.grad_scale;
+        float w = p.params[i];
+        if (p.kind == TS_OPT_SGD) {
+            w = w - p.lr * grad;                                   // param.add_(grad, alpha=-lr)
+        } else {
+            float m = p.exp_avg[i], v = p.exp_avg_sq[i];
+            m = m + p.one_minus_beta1 * (grad - m);                // exp_avg.lerp_(grad, 1 - beta1)
+            v = v * p.beta2;                                       // exp_avg_sq.mul_(beta2)
+            v = v + p.one_minus_beta2 * (grad * grad);             //   .addcmul_(grad, grad, value=1 - beta2)
+            const float denom = sqrtf(v) / p.bc2_sqrt + p.eps;     // (sqrt(v) / sqrt(bias_correction2)).add_(eps)
+            w = w - p.step_size * (m / denom);                     // param.addcdiv_(exp_avg, denom, value=-step_size)
+            p.exp_avg[i] = m;
+            p.exp_avg_sq[i] = v;
+        }
+        p.params[i] = w;
+        if (d.shadow_off >= 0 && p.shadow != nullptr) p.shadow[d.shadow_off + j0 + e] = __float2bfloat16_rn(w);
+    }
+}
+
+int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st) {
+    optimizer_kernel<<<(unsigned)n_chunks, 256, 0, st>>>(a);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// =====================================================================================
+__global__ void __launch_bounds__(256) cast_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int64_t n) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 8;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
+        if (i + 8 <= n) {
+            const float4 a = *reinterpret_cast<const float4 *>(src + i);
+            const float4 b = *reinterpret_cast<const float4 *>(src + i + 4);
+            __nv_bfloat162 o[4] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w),
+                                   __floats2bfloat162_rn(b.x, b.y), __floats2bfloat162_rn(b.z, b.w)};
+            *reinterpret_cast<uint4 *>(dst + i) = *reinterpret_cast<uint4 *>(o);
+        } else {
+            for (int64_t e = i; e < n; ++e) dst[e] = __float2bfloat16_rn(src[e]);
+        }
+    }
+}
+
+int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st) {
+    if (n <= 0) return TS_OK;
+    int64_t blocks = (n / 8 + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    cast_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, dst, n);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// =====================================================================================
+// Metrics (metrics.py:13-27): fold per-batch records into the running state in slot order.
+// =====================================================================================
+__global__ void metrics_accumulate_kernel(ts_metrics_state *state, const ts_batch_record *ring, int64_t ring_len,
+                                          int64_t first, int64_t count) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double ls = state->loss_sum;
+    int64_t nc = state->n_correct, nt = state->n_total;
+    for (int64_t i = 0; i < count; ++i) {
+        const ts_batch_record r = ring[(first + i) % ring_len];
+        ls += (double)r.loss;          // Mean.update: weighted_sum += loss (fp64), weights += 1
+        nc += r.n_correct;             // MulticlassAccuracy.update: num_correct += (pred == tgt).sum()
+        nt += r.n_rows;                //                            num_total += B
+    }
+    state->loss_sum = ls;
+    state->n_batches += count;
+    state->n_correct = nc;
+    state->n_total = nt;
+}
+
+int launch_metrics_accumulate(ts_metrics_state *state, const ts_batch_record *ring, int64_t ring_len, int64_t first,
+                              int64_t count, cudaStream_t st) {
+    if (count <= 0) return TS_OK;
+    metrics_accumulate_kernel<<<1, 32, 0, st>>>(state, ring, ring_len, first, count);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+__global__ void __launch_bounds__(256) metrics_update_raw_kernel(ts_metrics_state *state, const float *loss,
+                                                                 const int64_t *pred, const int64_t *tgt, int64_t B) {
+    __shared__ int s_c[8];
+    int c = 0;
+    for (int64_t i = threadIdx.x; i < B; i += blockDim.x) c += (pred[i] == tgt[i]);
+    c = warp_sum(c);
+    if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < 8; ++w) t += s_c[w];
+        state->loss_sum += (double)loss[0];
+        state->n_batches += 1;
+        state->n_correct += t;
+        state->n_total += B;
+    }
+}
+
+int launch_metrics_update_raw(ts_metrics_state *state, const float *loss, const int64_t *pred, const int64_t *tgt,
+                              int64_t B, cudaStream_t st) {
+    metrics_update_raw_kernel<<<1, 256, 0, st>>>(state, loss, pred, tgt, B);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+}  // namespace tsb

@@ -1,0 +1,45 @@
+"""Data-parallel plumbing: one process per GPU, `torch.distributed` (NCCL over NVLink 5 / NVSwitch on the
+box, gloo in the CPU tests). The reference is single-process; this is the north star's
+addition: every rank runs the same handlers on its shard of the loader, gradients are averaged once per
+step, metric counters are summed once per `compute()`.
+
+Everything here is device-agnostic on purpose, so the world_size-2 gloo tests exercise the same code."""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+from torch import Tensor
+
+
+def shard_bounds(n: int, rank: int, world: int, granule: int = 1) -> tuple[int, int]:
+    """Contiguous, equal shards of `n` samples (the remainder is dropped so every rank sees the same number of
+    equally sized batches: mean of local means == global mean, as CrossEntropyLoss(reduction='mean') needs)."""
+    per = (n // world) // granule * granule
+    return rank * per, rank * per + per
+
+
+class DataParallel:
+    def __init__(self, group=None):
+        self.group = group
+        if dist.is_available() and dist.is_initialized():
+            self.world = dist.get_world_size(group)
+            self.rank = dist.get_rank(group)
+        else:
+            self.world, self.rank = 1, 0
+
+    def broadcast_(self, flat: Tensor, src: int = 0) -> None:
+        if self.world > 1:
+            dist.broadcast(flat, src=src, group=self.group)
+
+    def all_reduce_sum_(self, flat: Tensor) -> None:
+        if self.world > 1:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+
+    def reduce_metrics(self, loss_sum: float, n_batches: int, n_correct: int, n_total: int, device) -> tuple:
+        """Sum the four metric accumulators over ranks (fp64 carries the integer counts exactly below 2**53)."""
+        if self.world == 1:
+            return loss_sum, n_batches, n_correct, n_total
+        t = torch.tensor([loss_sum, float(n_batches), float(n_correct), float(n_total)], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        v = t.tolist()
+        return v[0], int(v[1]), int(v[2]), int(v[3])
