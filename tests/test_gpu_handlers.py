@@ -94,6 +94,10 @@ def test_id_and_checkpoint_roundtrip():
     assert torch.equal(p1, p2) and l1.item() == l2.item()
     with pytest.raises(AttributeError):
         _ = model.id                     # not registered: same behaviour as gethash in the reference
-    compat.register(type(model.nn))
-    reg = type(model.nn)(784, 64, 10, dropout=0.0, activation=nn.ReLU())
-    assert isinstance(compat.gethash(reg), str)
+    cls = type('MLP', (type(model.nn),), {})
+    relu = type('ReLU', (nn.ReLU,), {})
+    compat.register(cls); compat.register(relu)
+    reg, _ = build_model([784, 256, 10], 0.1, 'relu', 'sgd', 0.1, seeded_init([784, 256, 10]), 'f32', max_batch=B)
+    object.__setattr__(reg, 'nn', None)
+    reg.nn = cls(784, 256, 10, dropout=0.1, activation=relu())
+    assert reg.id == '302adcec37ba79ed6a33d58956391d20'        # examples/tinysys/notebook.ipynb:34
