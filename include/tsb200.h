@@ -139,6 +139,26 @@ int32_t ts_opt_apply(ts_mlp *m, float grad_scale, void *stream);
 int32_t ts_eval_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
                      int64_t *predictions, ts_batch_record *record, void *stream);
 
+/* Evaluate with no device allocation anywhere. No counterpart in the reference; added for hosts that are not
+ * in a position to hand the library a workspace: a serving process whose GPU memory is wholly owned by another
+ * framework's pool, a latency-sensitive loop that cannot afford the device-wide synchronisation cudaMalloc and
+ * cudaFree imply, or a plug-in that is simply not given an allocator. Same inputs, outputs and arithmetic as
+ * ts_eval_step for TS_PREC_F32 handles with fp32 inputs (other combinations: TS_E_UNSUPPORTED), and it needs
+ * only ts_mlp_create + ts_mlp_bind_params, not ts_mlp_set_workspace.
+ *   - All intermediates (hidden activations, the loss/accuracy partials, the completion ticket) live in a
+ *     16 MiB array compiled into the library; every GPU that loads the library carries it until the process exits.
+ *   - Limit: batch * (sum of hidden widths) * 4 bytes plus about 8 KiB must fit in those 16 MiB (batch 4096 with one
+ *     256-wide hidden layer uses 4 MiB; GELU handles need twice the activation space). Larger requests return
+ *     TS_E_TOO_LARGE and launch nothing.
+ *   - The first call on each device looks the array's device address up (cudaGetSymbolAddress); make that first
+ *     call before starting any stream capture on that device.
+ *   - The array is shared by every handle and every call in the process and still holds the previous call's
+ *     data: the function re-zeroes the one word that has to start at zero, but two calls that can overlap on the
+ *     GPU (different streams, or host threads sharing a device) race on it. Serialise them.
+ *   - It calls no cudaMalloc / cudaFree or any other allocating routine. */
+int32_t ts_eval_step_static(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                            int64_t *predictions, ts_batch_record *record, void *stream);
+
 /* ---- metrics: replaces Metrics.update/compute/reset (examples/tinysys/tinysys/metrics.py:13-27) ---- */
 
 /* Fold `count` records of a ring of `ring_len` records, starting at slot `first`, into `state`

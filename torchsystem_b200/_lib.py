@@ -51,6 +51,8 @@ PROTOTYPES = {
     'ts_opt_apply': (C.c_int32, [C.c_void_p, C.c_float, C.c_void_p]),
     'ts_eval_step': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                  C.c_void_p]),
+    'ts_eval_step_static': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                        C.c_void_p]),
     'ts_metrics_accumulate': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     'ts_metrics_update_raw': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     'ts_metrics_reset': (C.c_int32, [C.c_void_p, C.c_void_p]),

@@ -583,3 +583,75 @@ int32_t ts_profile_kind_count(void) { return K_COUNT; }
 const char *ts_profile_kind_name(int32_t kind) { return (kind >= 0 && kind < K_COUNT) ? kKindNames[kind] : ""; }
 
 }  // extern "C"
+
+// ======================================================================================= evaluate without any allocation
+// ts_eval_step_static: the same arithmetic as ts_eval_step (fp32 handles), but every intermediate lives in one
+// fixed array that is part of the library image, so neither the caller nor the library has to obtain device memory.
+namespace {
+constexpr int64_t kStaticScratchBytes = 16ll << 20;   // 16 MiB, resident on every GPU that loads the library
+constexpr int kStaticMaxDevices = 64;
+void *g_static_scratch_addr[kStaticMaxDevices] = {nullptr};   // device address of the array, per device
+}  // namespace
+
+// In host code this name is only a handle for cudaGetSymbolAddress; kernels get the resolved device address.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+extern "C" int32_t ts_eval_step_static(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets,
+                                       int64_t batch, int64_t *predictions, ts_batch_record *record, void *stream) {
+    TS_REQUIRE(m != nullptr, TS_E_INVALID, "null handle");
+    TS_REQUIRE(m->params != nullptr, TS_E_STATE, "parameters not bound: call ts_mlp_bind_params first");
+    TS_REQUIRE(inputs && targets && predictions && record, TS_E_INVALID, "null inputs/targets/predictions/record pointer");
+    TS_REQUIRE(m->prec == TS_PREC_F32 && inputs_dtype == TS_DT_F32, TS_E_UNSUPPORTED,
+               "ts_eval_step_static runs fp32 handles on fp32 inputs only; use ts_eval_step with a workspace otherwise");
+    TS_REQUIRE(batch >= 1, TS_E_INVALID, "batch %lld", (long long)batch);
+    TS_REQUIRE(m->device >= 0 && m->device < kStaticMaxDevices, TS_E_UNSUPPORTED, "device index %d beyond %d", m->device,
+               kStaticMaxDevices);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int L = m->n_layers;
+
+    // how much of the array this call needs: ticket | head partials | per hidden layer: activation (+ GELU pre-activation)
+    int64_t need = 256 + round_up((int64_t)sizeof(HeadPartial) * kMaxHeadBlocks, 256);
+    for (int l = 0; l < L - 1; ++l)
+        need += round_up(batch * m->dims[l + 1] * 4, 256) * (m->act == TS_ACT_GELU ? 2 : 1);
+    TS_REQUIRE(need <= kStaticScratchBytes, TS_E_TOO_LARGE,
+               "ts_eval_step_static: batch %lld needs %lld bytes of scratch, the built-in array holds %lld (batch * sum of hidden "
+               "widths * 4 must stay below about 16 MiB); use ts_eval_step with a caller workspace for larger batches",
+               (long long)batch, (long long)need, (long long)kStaticScratchBytes);
+
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    if (g_static_scratch_addr[m->device] == nullptr) {   // set-up, once per device, with that device current
+        void *addr = nullptr;
+        TS_CUDA_CHECK(cudaGetSymbolAddress(&addr, g_static_scratch));
+        TS_REQUIRE(addr != nullptr, TS_E_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_scratch_addr[m->device] = addr;
+    }
+    Carver c(g_static_scratch_addr[m->device]);
+    unsigned int *ticket = (unsigned int *)c.take(256);
+    HeadPartial *partials = (HeadPartial *)c.take(sizeof(HeadPartial) * kMaxHeadBlocks);
+    // the array keeps whatever the previous call left: the completion ticket is the one thing that must start at zero
+    TS_CUDA_CHECK(cudaMemsetAsync(ticket, 0, 256, st));
+
+    const float *a_in = (const float *)inputs;
+    for (int l = 0; l < L - 1; ++l) {
+        const int in = m->dims[l], out = m->dims[l + 1];
+        float *a_out = (float *)c.take(batch * out * 4);
+        float *u_out = (m->act == TS_ACT_GELU) ? (float *)c.take(batch * out * 4) : nullptr;
+        SgemmArgs g{};
+        g.A = a_in; g.sam = in; g.sak = 1;
+        g.B = m->params + m->off[2 * l]; g.sbk = 1; g.sbn = in;
+        g.C = a_out; g.ldc = out; g.M = (int)batch; g.N = out; g.K = in;
+        g.k_chunk = (int)round_up(in, 16); g.c_split_stride = 0;
+        g.bias = m->params + m->off[2 * l + 1];
+        g.U_out = u_out; g.act = m->act; g.training = 0;
+        g.drop = drop_spec(m, nullptr, 0, l, false);
+        int rc = launch_sgemm(EPI_FWD, g, 1, st);
+        if (rc) return rc;
+        a_in = a_out;
+    }
+    HeadArgs h{};
+    fill_head(m, h, a_in, targets, batch, predictions, record);
+    h.a_is_bf16 = 0; h.round_w_bf16 = 0;
+    h.partials = partials; h.ticket = ticket;
+    h.drop = drop_spec(m, nullptr, 0, L - 2, false);
+    return launch_head(h, m->sm_count, st);
+}
