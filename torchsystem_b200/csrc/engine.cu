@@ -328,7 +328,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
                 g.A = (const __nv_bfloat16 *)dHl; g.a_major = TC_MAJOR_MN; g.lda = out;
                 g.B = (const __nv_bfloat16 *)a_prev; g.b_major = TC_MAJOR_MN; g.ldb = in;
                 g.M = out; g.N = in; g.K = (int)B;
-                g.epi = TC_EPI_STORE_F32; g.out = wp; g.ldo = in; g.splits = S; g.split_stride = m->partial_stride[tw];
+                g.epi = TC_EPI_STORE_F32; g.out = wp; g.ldo = in; g.splits = S; g.k_chunk = kc; g.split_stride = m->partial_stride[tw];
                 rc = launch_tc_gemm(g, m->sm_count, st);
             }
             if (rc) return rc;
@@ -411,7 +411,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
         m->off[2 * l + 1] = o; m->cnt[2 * l + 1] = outw; o += round_up(outw, kChunk);
         // split-K budget: enough CTAs for two waves, none for matrices that already fill the machine
         const int64_t tiles = ((outw + 127) / 128) * ((in + 127) / 128);
-        int64_t s = (2 * sms + tiles - 1) / tiles;
+        int64_t s = sms / tiles;   // one wave of CTAs
         s = s < 1 ? 1 : (s > kMaxSplits ? kMaxSplits : s);
         m->max_split[2 * l] = (l == m->n_layers - 1) ? kMaxSplits : (int)s;
         m->max_split[2 * l + 1] = kMaxSplits;
@@ -553,6 +553,20 @@ int32_t ts_metrics_read(const ts_metrics_state *state, ts_metrics_state *out, vo
     TS_CUDA_CHECK(cudaMemcpyAsync(out, state, sizeof(ts_metrics_state), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     TS_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
     return TS_OK;
+}
+
+int32_t ts_test_gemm_bf16(const void *A, int32_t a_major, int64_t lda, const void *B, int32_t b_major, int64_t ldb, int32_t M,
+                          int32_t N, int32_t K, float *out, int64_t ldo, int32_t splits, int64_t split_stride, void *stream) {
+    TS_REQUIRE(A && B && out, TS_E_INVALID, "null argument");
+    int dev = 0, sms = 0;
+    TS_CUDA_CHECK(cudaGetDevice(&dev));
+    TS_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    TcGemmArgs g{};
+    g.A = (const __nv_bfloat16 *)A; g.a_major = a_major; g.lda = lda;
+    g.B = (const __nv_bfloat16 *)B; g.b_major = b_major; g.ldb = ldb;
+    g.M = M; g.N = N; g.K = K; g.epi = TC_EPI_STORE_F32; g.out = out; g.ldo = ldo;
+    g.splits = splits; g.k_chunk = 0; g.split_stride = split_stride;
+    return launch_tc_gemm(g, sms, (cudaStream_t)stream);
 }
 
 int32_t ts_profile_begin(void) {

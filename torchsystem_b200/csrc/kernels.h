@@ -120,6 +120,7 @@ struct TcGemmArgs {
     void *out;             // STORE_F32: float [splits][M][ldo]; FWD / ACTGRAD: bf16 [M][ldo]
     int64_t ldo;
     int splits;            // split-K (STORE_F32 only)
+    int k_chunk;           // K elements per split (multiple of 64); 0 = derive from splits
     int64_t split_stride;  // elements between split outputs
     const float *bias;             // FWD: [N]
     const __nv_bfloat16 *A_prev;   // ACTGRAD: the layer's own bf16 output [M][ldo]
