@@ -49,6 +49,7 @@ def parse():
     ap.add_argument('--e2e-steps', type=int, default=2)
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the cpu_baseline leg')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--skip-e2e', action='store_true', help='profiling runs only')
     return ap.parse_args()
 
 
@@ -257,11 +258,14 @@ def main():
     }
 
     # ---- e2e: host buffers, H2D every step, result read back
-    pin_loader = PinnedLoader(x.cpu(), y.cpu(), BATCH, device=dev, prefetch=3)
-    pin_loader.h2d_bytes = 0
-    e_ms, _, _ = timed(pin_loader, args.e2e_steps, 1)
-    h2d_per_step = pin_loader.h2d_bytes // (args.e2e_steps + 1)
-    e2e = {'value': world * n * args.e2e_steps / (e_ms * 1e-3), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d_per_step,
+    if args.skip_e2e:
+        e2e = None
+    else:
+      pin_loader = PinnedLoader(x.cpu(), y.cpu(), BATCH, device=dev, prefetch=3)
+      pin_loader.h2d_bytes = 0
+      e_ms, _, _ = timed(pin_loader, args.e2e_steps, 1)
+      h2d_per_step = pin_loader.h2d_bytes // (args.e2e_steps + 1)
+      e2e = {'value': world * n * args.e2e_steps / (e_ms * 1e-3), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d_per_step,
            'd2h_bytes_per_step': 32, 'steps': args.e2e_steps, 'ms_per_step': e_ms / args.e2e_steps,
            'path': 'training.service.handle("train") over PinnedLoader (pinned host -> device on a copy stream, 3 batches ahead)'}
 

@@ -184,7 +184,8 @@ const char *ts_profile_kind_name(int32_t kind);
 /* Test hook (no counterpart in the reference): the tcgen05 GEMM on its own, D[M,N] = A[M,K] * B[K,N] with bf16
  * operands and fp32 output `out[split][M][ldo]`. a_major/b_major 0: operand stored [MN][K]; 1: stored [K][MN]. */
 int32_t ts_test_gemm_bf16(const void *A, int32_t a_major, int64_t lda, const void *B, int32_t b_major, int64_t ldb, int32_t M,
-                          int32_t N, int32_t K, float *out, int64_t ldo, int32_t splits, int64_t split_stride, void *stream);
+                          int32_t N, int32_t K, float *out, int64_t ldo, int32_t splits, int64_t split_stride,
+                          uint64_t *debug_clocks /* 32 x u64 device buffer for an in-kernel clock trace, or NULL */, void *stream);
 
 /* number of kernels this library has launched on the calling process so far (bench.py's gpu_launches) */
 int64_t ts_launch_count(void);

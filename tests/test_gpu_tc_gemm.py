@@ -13,7 +13,7 @@ def run_gemm(A, a_major, B, b_major, M, N, K, splits=1):
     dev = A.device
     out = torch.full((splits, M, N), float('nan'), dtype=torch.float32, device=dev)
     rc = _lib.lib.ts_test_gemm_bf16(A.data_ptr(), a_major, A.stride(0), B.data_ptr(), b_major, B.stride(0), M, N, K,
-                                   out.data_ptr(), N, splits, M * N, torch.cuda.current_stream(dev).cuda_stream)
+                                   out.data_ptr(), N, splits, M * N, None, torch.cuda.current_stream(dev).cuda_stream)
     _lib.check(rc, 'ts_test_gemm_bf16')
     torch.cuda.synchronize()
     return out.sum(0)

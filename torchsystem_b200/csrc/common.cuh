@@ -102,6 +102,24 @@ struct DropoutSpec {
         const bool keep = mask ? (mask[idx] != 0) : philox_keep(seed, step, layer, (uint64_t)idx, p);
         return keep ? scale : 0.0f;
     }
+    // Four consecutive columns starting at a multiple of 4 (one Philox call covers them when H % 4 == 0).
+    __device__ __forceinline__ void factor4(int64_t row, int col, int H, float (&f)[4]) const {
+        if (p <= 0.0f) { f[0] = f[1] = f[2] = f[3] = 1.0f; return; }
+        const int64_t idx = row * (int64_t)H + col;
+        if (mask == nullptr && (idx & 3) == 0) {
+            const uint64_t blk = (uint64_t)idx >> 2;
+            const uint4 r = philox4x32_10(make_uint4((uint32_t)blk, (uint32_t)(blk >> 32), step, layer),
+                                          make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+            const float k = 1.0f / 16777216.0f;
+            f[0] = ((float)(r.x >> 8) * k >= p) ? scale : 0.0f;
+            f[1] = ((float)(r.y >> 8) * k >= p) ? scale : 0.0f;
+            f[2] = ((float)(r.z >> 8) * k >= p) ? scale : 0.0f;
+            f[3] = ((float)(r.w >> 8) * k >= p) ? scale : 0.0f;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) f[j] = (col + j < H) ? factor(row, col + j, H) : 0.0f;
+        }
+    }
 };
 
 }  // namespace tsb

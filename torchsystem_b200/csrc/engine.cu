@@ -313,7 +313,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         }
         {   // dW_l[out,in] = dH_l^T a_prev, batch is the contraction (split across CTAs)
             int kc;
-            const int S = splits_for(B, m->max_split[tw], bf16 ? 64 : 16, &kc);
+            const int S = splits_for(B, m->max_split[tw], bf16 ? 128 : 16, &kc);
             float *wp = S > 1 ? m->partials + m->partial_off[tw] : m->grads + m->off[tw];
             ProfScope ps(K_DW_GEMM, st);
             if (!bf16) {
@@ -556,7 +556,8 @@ int32_t ts_metrics_read(const ts_metrics_state *state, ts_metrics_state *out, vo
 }
 
 int32_t ts_test_gemm_bf16(const void *A, int32_t a_major, int64_t lda, const void *B, int32_t b_major, int64_t ldb, int32_t M,
-                          int32_t N, int32_t K, float *out, int64_t ldo, int32_t splits, int64_t split_stride, void *stream) {
+                          int32_t N, int32_t K, float *out, int64_t ldo, int32_t splits, int64_t split_stride, uint64_t *debug_clocks,
+                          void *stream) {
     TS_REQUIRE(A && B && out, TS_E_INVALID, "null argument");
     int dev = 0, sms = 0;
     TS_CUDA_CHECK(cudaGetDevice(&dev));
@@ -566,6 +567,7 @@ int32_t ts_test_gemm_bf16(const void *A, int32_t a_major, int64_t lda, const voi
     g.B = (const __nv_bfloat16 *)B; g.b_major = b_major; g.ldb = ldb;
     g.M = M; g.N = N; g.K = K; g.epi = TC_EPI_STORE_F32; g.out = out; g.ldo = ldo;
     g.splits = splits; g.k_chunk = 0; g.split_stride = split_stride;
+    g.dbg = (unsigned long long *)debug_clocks;
     return launch_tc_gemm(g, sms, (cudaStream_t)stream);
 }
 

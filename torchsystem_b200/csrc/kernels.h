@@ -126,6 +126,7 @@ struct TcGemmArgs {
     const __nv_bfloat16 *A_prev;   // ACTGRAD: the layer's own bf16 output [M][ldo]
     DropoutSpec drop;
     int training;
+    unsigned long long *dbg;       // optional device buffer of 32 clock64 samples from CTA (0,0,0)
 };
 int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st);
 

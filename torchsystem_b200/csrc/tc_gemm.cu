@@ -13,6 +13,7 @@
 //   dW          = dY^T X : A = dY [K][M] MN-major,  B = X  [K][N] MN-major   (K = batch, split across CTAs)
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -23,18 +24,18 @@ namespace tsb {
 namespace {
 
 constexpr int BM = 128;        // UMMA M (cta_group::1)
-constexpr int BK = 64;         // 64 bf16 = one 128-byte swizzle row
+constexpr int KATOM = 64;      // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kThreads = 192;
+constexpr int kThreads = 224;  // warp 0: A producer, 1: MMA issuer + TMEM owner, 2: B producer, 3..6: epilogue
 constexpr int kMaxStages = 8;
-constexpr uint32_t kABytes = BM * BK * 2;   // 16 KiB per stage
 
 struct TcParams {
     int M, N, K, BN;
+    int BK;                    // K elements per pipeline stage: 64 or 128
     int num_kblocks, kblocks_per_split;
     int a_major, b_major;
     uint32_t idesc;
-    uint32_t b_bytes;
+    uint32_t a_bytes, b_bytes; // per stage
     int stages;
     uint32_t tmem_cols;
     void *out;
@@ -43,10 +44,19 @@ struct TcParams {
     const __nv_bfloat16 *A_prev;
     DropoutSpec drop;
     int training;
+    unsigned long long *dbg;   // optional trace buffer (test hook), or nullptr
 };
 
 // ------------------------------------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// One lane of a converged warp; unlike `lane == 0` it keeps operands in uniform registers, so UTMALDG / UTCHMMA
+// are issued directly instead of through per-lane "unique value" loops.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -113,10 +123,16 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 //   [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout=2 (SWIZZLE_128B)
 //   K-major : rows of 128 B, 8-row groups SBO = 1024 B apart (LBO unused, 1)
 //   MN-major: 64-element MN atoms LBO = BK*128 B apart, 8-row K groups SBO = 1024 B apart
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, int major) {
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, int major, int BK) {
     const uint64_t lbo = (major == TC_MAJOR_K) ? 1u : (uint32_t)(BK * 128) >> 4;
     const uint64_t sbo = 1024u >> 4;
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (lbo << 16) | (sbo << 32) | (1ull << 46) | (2ull << 61);
+}
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
 }
 
 template <int EPI>
@@ -129,14 +145,23 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     __shared__ uint32_t tmem_base_slot;
 
     uint8_t *tiles = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    const uint32_t stage_bytes = kABytes + p.b_bytes;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t stage_bytes = p.a_bytes + p.b_bytes;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role id
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * p.BN;
     const int kb_begin = blockIdx.z * p.kblocks_per_split;
     const int kb_end = min(p.num_kblocks, kb_begin + p.kblocks_per_split);
+    const int katoms = p.BK / KATOM;
+    unsigned long long *dbg = (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg : nullptr;
+    unsigned long long cta_t0 = 0;
+    if (dbg && threadIdx.x == 0) dbg[0] = clock64();
+    if (p.dbg && threadIdx.x == 0) {   // all CTAs: earliest / latest start on the global timer (ns)
+        cta_t0 = global_ns();
+        atomicMin(&p.dbg[60], cta_t0);
+        atomicMax(&p.dbg[62], cta_t0);
+    }
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }   // A + B producers arrive
         mbar_init(&tmem_full_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_a)) : "memory");
@@ -147,106 +172,149 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
+    if (dbg && threadIdx.x == 0) dbg[1] = clock64();
 
-    if (warp == 0 && lane == 0) {
-        // ===================== TMA producer =====================
+    if (warp == 0) {
+        // ===================== TMA producer, operand A (whole warp loops; one elected lane issues) =====================
         int s = 0;
         uint32_t phase = 0;
         for (int kb = kb_begin; kb < kb_end; ++kb) {
-            mbar_wait(&empty_bar[s], phase ^ 1);
-            uint8_t *sa = tiles + (size_t)s * stage_bytes, *sb = sa + kABytes;
-            mbar_expect_tx(&full_bar[s], stage_bytes);
-            const int k0 = kb * BK;
-            if (p.a_major == TC_MAJOR_K) {
-                tma_load_2d(&tma_a, &full_bar[s], sa, k0, m0);                      // box 64(K) x 128(M)
-            } else {
-                tma_load_2d(&tma_a, &full_bar[s], sa, m0, k0);                      // two boxes 64(M) x 64(K)
-                tma_load_2d(&tma_a, &full_bar[s], sa + BK * 128, m0 + 64, k0);
+            if (elect_one()) {
+                mbar_wait(&empty_bar[s], phase ^ 1);
+                uint8_t *sa = tiles + (size_t)s * stage_bytes;
+                mbar_expect_tx(&full_bar[s], p.a_bytes);
+                const int k0 = kb * p.BK;
+                if (p.a_major == TC_MAJOR_K) {
+                    for (int a = 0; a < katoms; ++a)                                   // boxes 64(K) x 128(M), one per K atom
+                        tma_load_2d(&tma_a, &full_bar[s], sa + (size_t)a * BM * 128, k0 + a * KATOM, m0);
+                } else {
+                    tma_load_2d(&tma_a, &full_bar[s], sa, m0, k0);                     // two boxes 64(M) x BK(K)
+                    tma_load_2d(&tma_a, &full_bar[s], sa + (size_t)p.BK * 128, m0 + 64, k0);
+                }
+                if (dbg && kb - kb_begin < 8) dbg[40 + (kb - kb_begin)] = clock64();
             }
-            if (p.b_major == TC_MAJOR_K) {
-                tma_load_2d(&tma_b, &full_bar[s], sb, k0, n0);                      // box 64(K) x BN(N)
-            } else {
-                for (int j = 0; j * 64 < p.BN; ++j)                                 // boxes 64(N) x 64(K)
-                    tma_load_2d(&tma_b, &full_bar[s], sb + (size_t)j * BK * 128, n0 + j * 64, k0);
-            }
+            __syncwarp();
             if (++s == p.stages) { s = 0; phase ^= 1; }
         }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 2) {
+        // ===================== TMA producer, operand B =====================
+        int s = 0;
+        uint32_t phase = 0;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+            if (elect_one()) {
+                mbar_wait(&empty_bar[s], phase ^ 1);
+                uint8_t *sb = tiles + (size_t)s * stage_bytes + p.a_bytes;
+                mbar_expect_tx(&full_bar[s], p.b_bytes);
+                const int k0 = kb * p.BK;
+                if (p.b_major == TC_MAJOR_K) {
+                    for (int a = 0; a < katoms; ++a)                                   // boxes 64(K) x BN(N), one per K atom
+                        tma_load_2d(&tma_b, &full_bar[s], sb + (size_t)a * p.BN * 128, k0 + a * KATOM, n0);
+                } else {
+                    for (int j = 0; j * 64 < p.BN; ++j)                                // boxes 64(N) x BK(K)
+                        tma_load_2d(&tma_b, &full_bar[s], sb + (size_t)j * p.BK * 128, n0 + j * 64, k0);
+                }
+            }
+            __syncwarp();
+            if (++s == p.stages) { s = 0; phase ^= 1; }
+        }
+    } else if (warp == 1) {
         // ===================== MMA issuer =====================
         int s = 0;
         uint32_t phase = 0;
-        const uint32_t a_step = (p.a_major == TC_MAJOR_K) ? (UMMA_K * 2) >> 4 : (UMMA_K * 128) >> 4;
-        const uint32_t b_step = (p.b_major == TC_MAJOR_K) ? (UMMA_K * 2) >> 4 : (UMMA_K * 128) >> 4;
         for (int kb = kb_begin; kb < kb_end; ++kb) {
-            mbar_wait(&full_bar[s], phase);
-            tc_fence_after();
-            const uint32_t sa = smem_u32(tiles + (size_t)s * stage_bytes);
-            const uint64_t adesc = make_desc(sa, p.a_major), bdesc = make_desc(sa + kABytes, p.b_major);
+            if (elect_one()) {
+                mbar_wait(&full_bar[s], phase);
+                tc_fence_after();
+                if (dbg && kb - kb_begin < 16) dbg[8 + (kb - kb_begin)] = clock64();
+                const uint32_t sa = smem_u32(tiles + (size_t)s * stage_bytes), sb = sa + p.a_bytes;
+                for (int a = 0; a < katoms; ++a) {
+                    // K-major: K atom `a` is its own [rows x 128 B] block; MN-major: 64 more K rows further down
+                    const uint32_t a_at = (p.a_major == TC_MAJOR_K) ? sa + a * (BM * 128) : sa + a * (KATOM * 128);
+                    const uint32_t b_at = (p.b_major == TC_MAJOR_K) ? sb + a * (p.BN * 128) : sb + a * (KATOM * 128);
+                    const uint64_t adesc = make_desc(a_at, p.a_major, p.BK), bdesc = make_desc(b_at, p.b_major, p.BK);
+                    const uint32_t a_step = (p.a_major == TC_MAJOR_K) ? (UMMA_K * 2) >> 4 : (UMMA_K * 128) >> 4;
+                    const uint32_t b_step = (p.b_major == TC_MAJOR_K) ? (UMMA_K * 2) >> 4 : (UMMA_K * 128) >> 4;
 #pragma unroll
-            for (int k = 0; k < BK / UMMA_K; ++k)
-                umma_bf16(tmem_base, adesc + (uint64_t)(k * a_step), bdesc + (uint64_t)(k * b_step), p.idesc,
-                          (kb > kb_begin || k > 0) ? 1u : 0u);
-            umma_commit(&empty_bar[s]);          // frees the smem stage when these MMAs retire
+                    for (int k = 0; k < KATOM / UMMA_K; ++k)
+                        umma_bf16(tmem_base, adesc + (uint64_t)(k * a_step), bdesc + (uint64_t)(k * b_step), p.idesc,
+                                  (kb > kb_begin || a > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);                          // frees the smem stage when these MMAs retire
+                if (kb == kb_end - 1) umma_commit(&tmem_full_bar);   // accumulator complete
+                if (dbg && kb - kb_begin < 16) dbg[24 + (kb - kb_begin)] = clock64();
+            }
+            __syncwarp();
             if (++s == p.stages) { s = 0; phase ^= 1; }
         }
-        if (kb_begin < kb_end) umma_commit(&tmem_full_bar);   // accumulator complete
-    } else if (warp >= 2) {
-        // ===================== epilogue: TMEM -> registers -> global =====================
+    } else if (warp >= 3) {
+        // ===================== epilogue: TMEM -> registers -> smem (transpose) -> coalesced global =====================
         const int q = warp & 3;                  // TMEM lane quarter this warp may read
-        const int row = m0 + q * 32 + lane;
         const bool has_k = kb_begin < kb_end;    // an empty split range contributes zeros
         if (has_k) { mbar_wait(&tmem_full_bar, 0); tc_fence_after(); }
-        const bool row_ok = row < p.M;
-        for (int c = 0; c < p.BN; c += 16) {
-            float v[16];
+        if (dbg && warp == 3 && lane == 0) dbg[6] = clock64();
+        // every pipeline stage has been consumed by now: reuse the tile memory as a 4 KiB staging block per warp
+        float4 *stage = reinterpret_cast<float4 *>(tiles + (size_t)(warp - 3) * 4096);
+        const int sub_row = lane >> 3, piece = lane & 7;     // phase-2 mapping: 4 rows x 8 float4 per instruction
+        for (int c = 0; c < p.BN; c += 32) {
+            float v[32];
             if (has_k) {
-                tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);   // warp-collective: no early exit
+                tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, *reinterpret_cast<float(*)[16]>(&v[0]));
+                if (c + 16 < p.BN)
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c + 16), *reinterpret_cast<float(*)[16]>(&v[16]));
             } else {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] = 0.0f;
+                for (int j = 0; j < 32; ++j) v[j] = 0.0f;
             }
-            const int n = n0 + c;
-            if (!row_ok || n >= p.N) continue;
-            const bool full = (n + 16 <= p.N);
-            if (EPI == TC_EPI_STORE_F32) {
-                float *o = reinterpret_cast<float *>(p.out) + (int64_t)blockIdx.z * p.split_stride + (int64_t)row * p.ldo + n;
-                if (full && (p.ldo & 3) == 0) {
+            // phase 1: lane = row; 16-byte pieces XOR-swizzled by row so both phases are bank-conflict free
 #pragma unroll
-                    for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4 *>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            for (int j = 0; j < 8; ++j)
+                stage[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            __syncwarp();
+            // phase 2: 8 consecutive lanes cover 128 contiguous bytes of one output row
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int rr = i * 4 + sub_row;
+                const int row = m0 + q * 32 + rr;
+                const int n = n0 + c + piece * 4;
+                float4 t = stage[rr * 8 + (piece ^ (rr & 7))];
+                if (row >= p.M || n >= p.N || c + piece * 4 >= p.BN) continue;
+                float w[4] = {t.x, t.y, t.z, t.w};
+                const int nv = min(4, p.N - n);
+                if (EPI == TC_EPI_STORE_F32) {
+                    float *o = reinterpret_cast<float *>(p.out) + (int64_t)blockIdx.z * p.split_stride + (int64_t)row * p.ldo + n;
+                    if (nv == 4 && (p.ldo & 3) == 0) *reinterpret_cast<float4 *>(o) = t;
+                    else for (int j = 0; j < nv; ++j) o[j] = w[j];
                 } else {
-                    for (int j = 0; j < 16 && n + j < p.N; ++j) o[j] = v[j];
-                }
-            } else {
-                __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(p.out) + (int64_t)row * p.ldo + n;
-                if (EPI == TC_EPI_FWD) {
-                    // Linear bias, Dropout, ReLU (mlp.py:14-16), all in fp32 on the accumulator
+                    __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(p.out) + (int64_t)row * p.ldo + n;
+                    if (EPI == TC_EPI_FWD) {
+                        // Linear bias, Dropout, ReLU (mlp.py:14-16), all in fp32 on the accumulator
+                        float keep[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+                        if (p.training) p.drop.factor4((int64_t)row, n, p.N, keep);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        if (n + j < p.N) {
-                            float u = v[j] + p.bias[n + j];
-                            if (p.training) u *= p.drop.factor(row, n + j, p.N);
-                            v[j] = fmaxf(u, 0.0f);
-                        }
+                        for (int j = 0; j < 4; ++j)
+                            if (j < nv) w[j] = fmaxf((w[j] + p.bias[n + j]) * keep[j], 0.0f);
+                    } else {
+                        // dH = dA * relu'(A_prev) / (1-p): A_prev > 0 implies the unit was kept
+                        const __nv_bfloat16 *ap = p.A_prev + (int64_t)row * p.ldo + n;
+                        const float sc = p.training ? p.drop.scale : 1.0f;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (j < nv) w[j] = (__bfloat162float(ap[j]) > 0.0f) ? w[j] * sc : 0.0f;
                     }
-                } else {
-                    // dH = dA * relu'(A_prev) / (1-p): A_prev > 0 implies the unit was kept
-                    const __nv_bfloat16 *ap = p.A_prev + (int64_t)row * p.ldo + n;
-                    const float sc = p.training ? p.drop.scale : 1.0f;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        if (n + j < p.N) v[j] = (__bfloat162float(ap[j]) > 0.0f) ? v[j] * sc : 0.0f;
-                }
-                if (full && (p.ldo & 7) == 0) {
-                    __nv_bfloat162 h[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                    *reinterpret_cast<uint4 *>(o) = *reinterpret_cast<uint4 *>(&h[0]);
-                    *reinterpret_cast<uint4 *>(o + 8) = *reinterpret_cast<uint4 *>(&h[4]);
-                } else {
-                    for (int j = 0; j < 16 && n + j < p.N; ++j) o[j] = __float2bfloat16_rn(v[j]);
+                    if (nv == 4 && (p.ldo & 3) == 0) {
+                        __nv_bfloat162 lo = __floats2bfloat162_rn(w[0], w[1]), hi = __floats2bfloat162_rn(w[2], w[3]);
+                        uint2 pk;
+                        pk.x = *reinterpret_cast<uint32_t *>(&lo);
+                        pk.y = *reinterpret_cast<uint32_t *>(&hi);
+                        *reinterpret_cast<uint2 *>(o) = pk;
+                    } else {
+                        for (int j = 0; j < nv; ++j) o[j] = __float2bfloat16_rn(w[j]);
+                    }
                 }
             }
+            __syncwarp();
         }
+        if (dbg && warp == 3 && lane == 0) dbg[7] = clock64();
     }
     __syncwarp();
     tc_fence_before();
@@ -254,6 +322,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, p.tmem_cols);
+    }
+    if (p.dbg && threadIdx.x == 0) {
+        const unsigned long long t = global_ns();
+        atomicMax(&p.dbg[61], t);
+        atomicMax(&p.dbg[63], t - cta_t0);                 // slowest CTA (ns)
     }
 }
 
@@ -314,21 +387,27 @@ int get_map(const void *ptr, uint64_t inner, uint64_t outer, uint64_t pitch_elem
     return TS_OK;
 }
 
-// Tile width: among widths that waste <= 12.5 % of the columns, the one with the best wave efficiency
-// (CTAs / (waves * SMs)), ties to the wider tile.
-int pick_bn(int M, int N, int splits, int sm_count) {
+// Tile width from a small cost model fitted to in-kernel clock traces on B200 (cycles per CTA):
+//   ~2000 prologue + per 64 K-elements max(2*BN tensor time, issue cadence: ~440 with 128-wide stages, ~684 with
+//   64-wide stages) + ~12 per output column of epilogue; total = waves * per-CTA. Widths that would pad the
+//   problem by more than 12.5 % are not considered.
+int pick_bn(int M, int N, int K, int splits, int sm_count) {
     static const int cand[] = {256, 224, 192, 160, 128, 112, 96, 80, 64, 48, 32, 16};
+    if (const char *f = getenv("TSB_FORCE_BN")) return atoi(f);   // experiments
     const int tiles_m = (M + BM - 1) / BM;
+    const long k64 = ((K + KATOM - 1) / KATOM + splits - 1) / splits;
     int best = 16;
-    double best_eff = -1.0;
+    double best_cost = 1e30;
     for (int bn : cand) {
         const int tiles_n = (N + bn - 1) / bn;
         const int waste = tiles_n * bn - N;
         if (waste * 8 > N && bn > 16) continue;
         const long ctas = (long)tiles_m * tiles_n * splits;
         const long waves = (ctas + sm_count - 1) / sm_count;
-        const double eff = (double)ctas / (double)(waves * sm_count) * (double)N / (double)(tiles_n * bn);
-        if (eff > best_eff + 1e-9) { best_eff = eff; best = bn; }
+        const double cadence = bn <= 128 ? 440.0 : 684.0;
+        const double per_cta = 2000.0 + (double)k64 * (2.0 * bn > cadence ? 2.0 * bn : cadence) + 12.0 * bn;
+        const double cost = (double)waves * per_cta;
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = bn; }
     }
     return best;
 }
@@ -338,21 +417,27 @@ int pick_bn(int M, int N, int splits, int sm_count) {
 int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     TS_REQUIRE(a.M >= 1 && a.N >= 1 && a.K >= 1, TS_E_INVALID, "tc gemm: bad shape %d x %d x %d", a.M, a.N, a.K);
     TS_REQUIRE(a.splits >= 1 && (a.splits == 1 || a.epi == TC_EPI_STORE_F32), TS_E_INVALID, "split-K needs the fp32 store epilogue");
+    TS_REQUIRE(a.k_chunk % KATOM == 0, TS_E_INVALID, "tc gemm: k_chunk %d is not a multiple of %d", a.k_chunk, KATOM);
     TcParams p{};
     p.M = a.M; p.N = a.N; p.K = a.K;
     p.a_major = a.a_major; p.b_major = a.b_major;
-    p.num_kblocks = (a.K + BK - 1) / BK;
-    TS_REQUIRE(a.k_chunk % BK == 0, TS_E_INVALID, "tc gemm: k_chunk %d is not a multiple of %d", a.k_chunk, BK);
-    p.kblocks_per_split = a.k_chunk > 0 ? a.k_chunk / BK : (p.num_kblocks + a.splits - 1) / a.splits;
     const int splits = a.splits;
-    TS_REQUIRE((long)splits * p.kblocks_per_split >= p.num_kblocks, TS_E_INVALID, "tc gemm: %d splits of %d k-blocks do not cover K=%d",
-               splits, p.kblocks_per_split, a.K);
-    p.BN = pick_bn(a.M, a.N, splits, sm_count);
+    p.BN = pick_bn(a.M, a.N, a.K, splits, sm_count);
+    // K range per split in elements (a multiple of 64), then K per pipeline stage: 128 for narrow tiles, where the
+    // per-stage issue overhead (~300 cycles of barrier + TMA issue) dominates, 64 for wide ones (MMA-bound)
+    const int k_atoms = (a.K + KATOM - 1) / KATOM;
+    const int atoms_per_split = a.k_chunk > 0 ? a.k_chunk / KATOM : (k_atoms + splits - 1) / splits;
+    TS_REQUIRE((long)splits * atoms_per_split >= k_atoms, TS_E_INVALID, "tc gemm: %d splits of %d K-atoms do not cover K=%d", splits,
+               atoms_per_split, a.K);
+    p.BK = (p.BN <= 128 && k_atoms >= 2 && (splits == 1 || atoms_per_split % 2 == 0)) ? 128 : 64;
+    p.num_kblocks = (a.K + p.BK - 1) / p.BK;
+    p.kblocks_per_split = (atoms_per_split * KATOM + p.BK - 1) / p.BK;   // split boundaries stay stage-aligned
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.a_major << 15) | ((uint32_t)a.b_major << 16) |
               ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-    p.b_bytes = (a.b_major == TC_MAJOR_K) ? (uint32_t)p.BN * 128u : (uint32_t)((p.BN + 63) / 64) * (BK * 128);
-    p.b_bytes = (p.b_bytes + 1023u) & ~1023u;
-    const uint32_t stage = kABytes + p.b_bytes;
+    p.a_bytes = (uint32_t)BM * (uint32_t)p.BK * 2u;
+    p.b_bytes = (a.b_major == TC_MAJOR_K) ? (uint32_t)p.BN * (uint32_t)p.BK * 2u
+                                          : (uint32_t)((p.BN + 63) / 64) * (uint32_t)(p.BK * 128);
+    const uint32_t stage = p.a_bytes + p.b_bytes;     // always a multiple of 1024
     p.stages = (int)((200u * 1024u) / stage);
     if (p.stages > kMaxStages) p.stages = kMaxStages;
     if (p.stages > p.kblocks_per_split) p.stages = p.kblocks_per_split < 2 ? 2 : p.kblocks_per_split;
@@ -360,17 +445,20 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     while ((int)p.tmem_cols < p.BN) p.tmem_cols <<= 1;
     p.out = a.out; p.ldo = a.ldo; p.split_stride = a.split_stride;
     p.bias = a.bias; p.A_prev = a.A_prev; p.drop = a.drop; p.training = a.training;
+    p.dbg = a.dbg;
 
     CUtensorMap ma, mb;
     int rc;
-    if (a.a_major == TC_MAJOR_K) rc = get_map(a.A, (uint64_t)a.K, (uint64_t)a.M, (uint64_t)a.lda, BK, BM, &ma);
-    else rc = get_map(a.A, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, 64, BK, &ma);
+    if (a.a_major == TC_MAJOR_K) rc = get_map(a.A, (uint64_t)a.K, (uint64_t)a.M, (uint64_t)a.lda, KATOM, BM, &ma);
+    else rc = get_map(a.A, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, 64, (uint32_t)p.BK, &ma);
     if (rc) return rc;
-    if (a.b_major == TC_MAJOR_K) rc = get_map(a.B, (uint64_t)a.K, (uint64_t)a.N, (uint64_t)a.ldb, BK, (uint32_t)p.BN, &mb);
-    else rc = get_map(a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb, 64, BK, &mb);
+    if (a.b_major == TC_MAJOR_K) rc = get_map(a.B, (uint64_t)a.K, (uint64_t)a.N, (uint64_t)a.ldb, KATOM, (uint32_t)p.BN, &mb);
+    else rc = get_map(a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb, 64, (uint32_t)p.BK, &mb);
     if (rc) return rc;
 
-    const size_t smem = (size_t)p.stages * stage + 1024;
+    size_t smem = (size_t)p.stages * stage;
+    if (smem < 4 * 4096) smem = 4 * 4096;             // the epilogue's staging blocks
+    smem += 1024;
     dim3 grid((a.N + p.BN - 1) / p.BN, (a.M + BM - 1) / BM, splits);
 #define TS_TC_LAUNCH(E)                                                                                             \
     do {                                                                                                            \
