@@ -120,7 +120,7 @@ int32_t ts_mlp_sync_weights(ts_mlp *m, void *stream);
  *   inputs       [B, dims[0]] row-major, dtype `inputs_dtype` (the handler's Flatten is a view)
  *   targets      [B] int64 in [0, classes)
  *   masks        HOST array of (n_dims-2) device pointers to uint8 keep-masks [B, hidden_l] (values 0/1), or
- *                NULL to draw the masks in-kernel from Philox4x32-10 keyed by (`seed`, optimizer step, layer)
+ *                NULL to draw the masks in-kernel from a counter-based hash keyed by (`seed`, optimizer step, layer)
  *   predictions  [B] int64 out
  *   record       one ts_batch_record out (its .loss is the returned loss tensor)
  */
@@ -186,6 +186,9 @@ const char *ts_profile_kind_name(int32_t kind);
 int32_t ts_test_gemm_bf16(const void *A, int32_t a_major, int64_t lda, const void *B, int32_t b_major, int64_t ldb, int32_t M,
                           int32_t N, int32_t K, float *out, int64_t ldo, int32_t splits, int64_t split_stride,
                           uint64_t *debug_clocks /* 32 x u64 device buffer for an in-kernel clock trace, or NULL */, void *stream);
+
+/* Test hook: 32 clock64 samples taken by CTA 0 of the most recent fused forward+head launch (HOST buffer); synchronises. */
+int32_t ts_test_fused_trace(uint64_t *out /*HOST, 32 entries*/);
 
 /* number of kernels this library has launched on the calling process so far (bench.py's gpu_launches) */
 int64_t ts_launch_count(void);

@@ -169,10 +169,10 @@ class OracleMLP:
         n = len(self.weights)
         gw, gb = [None] * n, [None] * n
         scale = np.float32(1.0) / np.float32(1.0 - self.dropout)
-        # last layer: the CUDA head kernel keeps dz in fp32 (no bf16 rounding)
+        # last layer: dW and db use the fp32 dz; the tensor-core dA = dZ W contracts the bf16-rounded dz
         gw[-1] = dz.T @ acts[-1]
         gb[-1] = dz.sum(axis=0)
-        da = dz @ rnd(self.weights[-1])
+        da = rnd(dz) @ rnd(self.weights[-1])
         for l in range(n - 2, -1, -1):
             g = _act_grad(pre[l], acts[l + 1], self.activation)
             if masks is not None and self.dropout > 0.0:

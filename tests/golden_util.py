@@ -102,7 +102,7 @@ def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weight
     SGD must satisfy it everywhere. Adam divides the step by sqrt(v): an element whose gradient is
     itself at round-off level (|g| near eps = 1e-8) moves by up to `lr` per step in a direction that
     depends on summation order, in the reference as much as here. For Adam at most 1e-3 of the
-    elements of a tensor may therefore leave the band, and none by more than lr * steps (the hard
+    elements of a tensor (or 2 elements of a small one) may therefore leave the band, and none by more than lr * steps (the hard
     bound on any Adam trajectory difference)."""
     for i, (g, w) in enumerate(zip(got, want)):
         g = np.asarray(g, dtype=np.float64); w = np.asarray(w, dtype=np.float64)
@@ -113,5 +113,5 @@ def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weight
         if not adam:
             assert not bad.any(), f'{what}[{i}]: {bad.sum()} elements off, max |d|={dev.max():.3e}'
         else:
-            assert bad.mean() <= 1e-3, f'{what}[{i}]: {bad.sum()}/{bad.size} elements off (tol {tol})'
+            assert bad.sum() <= max(2, 1e-3 * bad.size), f'{what}[{i}]: {bad.sum()}/{bad.size} elements off (tol {tol})'
             assert dev.max() <= lr * steps + 1e-9, f'{what}[{i}]: max |d|={dev.max():.3e} beyond lr*steps'

@@ -62,59 +62,43 @@ __device__ __forceinline__ float gelu_grad_f(float u) {
     return cdf + u * pdf;
 }
 
-// Philox4x32-10 (Salmon et al. 2011): counter (c0..c3), key (k0,k1) -> 4 x 32 random bits.
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
-    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
-        const uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
-        k.x += W0;
-        k.y += W1;
-    }
-    return c;
+// Counter-based dropout generator. One 32-bit hash (Wellons' "lowbias32" finaliser: xorshift-multiply rounds with
+// full avalanche) of (row, column pair, key) yields two 16-bit uniforms, i.e. the keep decisions of two neighbouring
+// hidden units; key = f(seed, optimizer step, layer) is mixed on the host. Stateless, so forward and backward (and
+// every kernel variant) regenerate the same mask from the element index alone.
+__host__ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352du;
+    x ^= x >> 15; x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
 }
-
-// Keep-decision for element `idx` of hidden layer `layer` at optimizer step `step`: one Philox call
-// covers 4 consecutive elements, so neighbouring threads recompute the same block (cheap, stateless).
-__device__ __forceinline__ bool philox_keep(uint64_t seed, uint32_t step, uint32_t layer, uint64_t idx, float p) {
-    const uint64_t blk = idx >> 2;
-    const uint4 r = philox4x32_10(make_uint4((uint32_t)blk, (uint32_t)(blk >> 32), step, layer),
-                                  make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
-    const uint32_t lane = (uint32_t)(idx & 3);
-    const uint32_t bits = lane == 0 ? r.x : lane == 1 ? r.y : lane == 2 ? r.z : r.w;
-    // uniform in [0,1): keep when u >= p
-    return (float)(bits >> 8) * (1.0f / 16777216.0f) >= p;
+__device__ __forceinline__ uint32_t dropout_bits(uint32_t key, int64_t row, int colpair) {
+    return hash32(((uint32_t)row * 0x9E3779B1u) ^ ((uint32_t)((uint64_t)row >> 32) * 0xC2B2AE3Du) ^ ((uint32_t)colpair * 0x85EBCA6Bu) ^ key);
 }
 
 // How the dropout keep-mask of a hidden layer is obtained.
 struct DropoutSpec {
     const uint8_t *mask;  // [B, H] 0/1 bytes, or nullptr
-    uint64_t seed;
-    uint32_t step;
-    uint32_t layer;
-    float p;      // drop probability; 0 => disabled
-    float scale;  // 1/(1-p)
+    uint32_t key;         // hash32-mixed (seed, optimizer step, layer)
+    uint32_t thresh;      // drop when the 16-bit uniform is below round(p * 65536)
+    float p;              // drop probability; 0 => disabled
+    float scale;          // 1/(1-p)
     __device__ __forceinline__ float factor(int64_t row, int col, int H) const {
         if (p <= 0.0f) return 1.0f;
-        const int64_t idx = row * (int64_t)H + col;
-        const bool keep = mask ? (mask[idx] != 0) : philox_keep(seed, step, layer, (uint64_t)idx, p);
+        bool keep;
+        if (mask) keep = mask[row * (int64_t)H + col] != 0;
+        else keep = ((dropout_bits(key, row, col >> 1) >> ((col & 1) * 16)) & 0xFFFFu) >= thresh;
         return keep ? scale : 0.0f;
     }
-    // Four consecutive columns starting at a multiple of 4 (one Philox call covers them when H % 4 == 0).
+    // four consecutive columns starting at a multiple of 4
     __device__ __forceinline__ void factor4(int64_t row, int col, int H, float (&f)[4]) const {
         if (p <= 0.0f) { f[0] = f[1] = f[2] = f[3] = 1.0f; return; }
-        const int64_t idx = row * (int64_t)H + col;
-        if (mask == nullptr && (idx & 3) == 0) {
-            const uint64_t blk = (uint64_t)idx >> 2;
-            const uint4 r = philox4x32_10(make_uint4((uint32_t)blk, (uint32_t)(blk >> 32), step, layer),
-                                          make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
-            const float k = 1.0f / 16777216.0f;
-            f[0] = ((float)(r.x >> 8) * k >= p) ? scale : 0.0f;
-            f[1] = ((float)(r.y >> 8) * k >= p) ? scale : 0.0f;
-            f[2] = ((float)(r.z >> 8) * k >= p) ? scale : 0.0f;
-            f[3] = ((float)(r.w >> 8) * k >= p) ? scale : 0.0f;
+        if (mask == nullptr && (col & 3) == 0) {
+            const uint32_t b0 = dropout_bits(key, row, col >> 1), b1 = dropout_bits(key, row, (col >> 1) + 1);
+            f[0] = ((b0 & 0xFFFFu) >= thresh) ? scale : 0.0f;
+            f[1] = ((b0 >> 16) >= thresh) ? scale : 0.0f;
+            f[2] = ((b1 & 0xFFFFu) >= thresh) ? scale : 0.0f;
+            f[3] = ((b1 >> 16) >= thresh) ? scale : 0.0f;
         } else {
 #pragma unroll
             for (int j = 0; j < 4; ++j) f[j] = (col + j < H) ? factor(row, col + j, H) : 0.0f;

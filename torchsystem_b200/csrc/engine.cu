@@ -24,9 +24,9 @@ void set_error(const char *fmt, ...) {
 static inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
 // ---- optional per-kernel timing: CUDA events recorded on the launching stream around each launch.
-enum { K_CAST = 0, K_FWD_GEMM, K_HEAD, K_HEAD_WGRAD, K_COLSUM, K_DW_GEMM, K_DX_GEMM, K_OPT, K_COUNT };
+enum { K_CAST = 0, K_FWD_GEMM, K_HEAD, K_HEAD_WGRAD, K_COLSUM, K_DW_GEMM, K_DX_GEMM, K_OPT, K_FUSED, K_COUNT };
 static const char *const kKindNames[K_COUNT] = {"cast_bf16", "fwd_gemm", "head", "head_wgrad", "colsum",
-                                                "dw_gemm",   "dx_gemm",  "optimizer"};
+                                                "dw_gemm",   "dx_gemm",  "optimizer", "fused_fwd_head"};
 struct ProfPair { int kind; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfPair> g_prof;
@@ -85,8 +85,9 @@ struct ts_mlp {
     float *partials = nullptr;
     int64_t partial_off[2 * kMaxLayers] = {0}, partial_stride[2 * kMaxLayers] = {0};
     __nv_bfloat16 *x_bf16 = nullptr, *shadow = nullptr;
-    int64_t shadow_off[kMaxLayers] = {0};
+    int64_t shadow_off[kMaxLayers] = {0};   // hidden-layer weights, dense [out][in]; last layer: [16][in], rows >= classes zero
     int64_t shadow_total = 0;
+    bool fused = false;                     // one hidden layer of a width the fused kernel takes
 
     int hidden_layers() const { return n_layers - 1; }
     int classes() const { return dims[n_layers]; }
@@ -125,7 +126,7 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
     m->dh[1] = (L > 2) ? c.take(Bm * maxH * (int64_t)m->elem()) : nullptr;
     int64_t pfloats = 0;
     for (int t = 0; t < m->n_tensors; ++t) {
-        m->partial_stride[t] = round_up(m->cnt[t], 4);
+        m->partial_stride[t] = round_up(m->cnt[t], 4) + 32;   // +128 B: successive partials of an element fall into different L2 slices
         m->partial_off[t] = pfloats;
         if (m->max_split[t] > 1) pfloats += (int64_t)m->max_split[t] * m->partial_stride[t];
     }
@@ -149,10 +150,10 @@ int splits_for(int64_t B, int max_split, int granule, int *k_chunk) {
 DropoutSpec drop_spec(const ts_mlp *m, const uint8_t *const *masks, uint64_t seed, int layer, bool training) {
     DropoutSpec d;
     d.mask = (masks && training) ? masks[layer] : nullptr;
-    d.seed = seed;
-    d.step = (uint32_t)m->step;
-    d.layer = (uint32_t)layer;
+    d.key = hash32(hash32((uint32_t)seed ^ 0x9E3779B9u) ^ hash32((uint32_t)(seed >> 32) + 0x7F4A7C15u) ^
+                   hash32((uint32_t)m->step * 0x85EBCA6Bu + (uint32_t)layer + 1u));
     d.p = training ? m->p : 0.0f;
+    d.thresh = (uint32_t)((double)d.p * 65536.0 + 0.5);
     d.scale = training ? m->scale : 1.0f;
     return d;
 }
@@ -237,7 +238,7 @@ int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, c
         o.t[t].offset = m->off[t]; o.t[t].count = m->cnt[t];
         o.t[t].partial_off = m->partial_off[t]; o.t[t].partial_stride = m->partial_stride[t];
         const int l = t / 2;
-        o.t[t].shadow_off = (m->prec == TS_PREC_BF16 && t % 2 == 0 && l < m->n_layers - 1) ? m->shadow_off[l] : -1;
+        o.t[t].shadow_off = (m->prec == TS_PREC_BF16 && t % 2 == 0) ? m->shadow_off[l] : -1;
         o.t[t].nsplit = nsplit ? nsplit[t] : 0;
         any_partial |= o.t[t].nsplit > 0;
     }
@@ -263,6 +264,38 @@ int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, c
     return launch_optimizer(o, m->n_chunks, st);
 }
 
+// One-hidden-layer bf16 aggregates: cast (if needed) + ONE kernel for forward, loss, argmax and, when `train`,
+// dZ / A / dH (fused_mlp.cu).
+int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks, uint64_t seed,
+                  bool train, int64_t *pred, ts_batch_record *rec, const void **a0_out, cudaStream_t st) {
+    const void *a0 = x;
+    if (x_dtype == TS_DT_F32) {
+        ProfScope ps(K_CAST, st);
+        int rc = launch_cast_bf16((const float *)x, m->x_bf16, B * m->dims[0], st);
+        if (rc) return rc;
+        a0 = m->x_bf16;
+    } else {
+        TS_REQUIRE(x_dtype == TS_DT_BF16, TS_E_INVALID, "unknown inputs dtype %d", x_dtype);
+    }
+    *a0_out = a0;
+    FusedMlpArgs f{};
+    f.X = (const __nv_bfloat16 *)a0;
+    f.W1 = m->shadow + m->shadow_off[0];
+    f.W2p = m->shadow + m->shadow_off[1];
+    f.b1 = m->params + m->off[1];
+    f.b2 = m->params + m->off[3];
+    f.y = y; f.B = B; f.D = m->dims[0]; f.H = m->dims[1]; f.C = m->dims[2];
+    f.pred = pred;
+    f.dz = train ? m->dz : nullptr;
+    f.A_out = train ? (__nv_bfloat16 *)m->acts[0] : nullptr;
+    f.dH_out = train ? (__nv_bfloat16 *)m->dh[0] : nullptr;
+    f.drop = drop_spec(m, masks, seed, 0, train);
+    f.training = train && m->p > 0.0f;
+    f.partials = m->head_partials; f.ticket = m->ticket; f.record = rec;
+    ProfScope ps(K_FUSED, st);
+    return launch_fused_mlp(f, st);
+}
+
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
              uint64_t seed, int64_t *pred, ts_batch_record *rec, cudaStream_t st, bool update) {
     int rc = check_ready(m, B, update);
@@ -272,22 +305,40 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     const int L = m->n_layers;
     const bool bf16 = m->prec == TS_PREC_BF16;
     const void *a0 = nullptr, *a_last = nullptr;
-    rc = forward_hidden(m, x, x_dtype, B, masks, seed, true, &a0, &a_last, st);
-    if (rc) return rc;
-
-    HeadArgs h{};
-    fill_head(m, h, a_last, y, B, pred, rec);
-    h.dz = m->dz; h.dH = m->dh[0];
-    h.U_prev = m->upre[L - 2];
-    h.drop = drop_spec(m, masks, seed, L - 2, true);
-    { ProfScope ps(K_HEAD, st); rc = launch_head(h, m->sm_count, st); }
-    if (rc) return rc;
+    if (m->fused) {
+        rc = fused_forward(m, x, x_dtype, y, B, masks, seed, true, pred, rec, &a0, st);
+        if (rc) return rc;
+        a_last = m->acts[0];
+    } else {
+        rc = forward_hidden(m, x, x_dtype, B, masks, seed, true, &a0, &a_last, st);
+        if (rc) return rc;
+        HeadArgs h{};
+        fill_head(m, h, a_last, y, B, pred, rec);
+        h.dz = m->dz; h.dH = m->dh[0];
+        h.U_prev = m->upre[L - 2];
+        h.drop = drop_spec(m, masks, seed, L - 2, true);
+        { ProfScope ps(K_HEAD, st); rc = launch_head(h, m->sm_count, st); }
+        if (rc) return rc;
+    }
 
     int nsplit[2 * kMaxLayers] = {0};
-    {   // last layer: dW = dz^T a_last, db = colsum(dz)
+    const int64_t row_blocks = (B + 127) / 128;
+    const bool small = m->classes() <= 16 && row_blocks <= kMaxRowBlocks;   // one launch for dW_last, db_last, db of the last hidden layer
+    if (small) {
+        const int tw = 2 * (L - 1), tb = tw + 1, th = 2 * (L - 2) + 1;
+        const bool direct = row_blocks == 1;
+        float *wp = direct ? m->grads + m->off[tw] : m->partials + m->partial_off[tw];
+        float *bp = direct ? m->grads + m->off[tb] : m->partials + m->partial_off[tb];
+        float *hp = direct ? m->grads + m->off[th] : m->partials + m->partial_off[th];
+        ProfScope ps(K_HEAD_WGRAD, st);
+        rc = launch_small_grads(a_last, m->dh[0], bf16, m->dz, B, m->dims[L - 1], m->dims[L], wp, m->partial_stride[tw], bp,
+                                m->partial_stride[tb], hp, m->partial_stride[th], st);
+        if (rc) return rc;
+        nsplit[tw] = nsplit[tb] = nsplit[th] = direct ? 0 : (int)row_blocks;
+    } else {   // last layer: dW = dz^T a_last, db = colsum(dz)
         const int tw = 2 * (L - 1), tb = tw + 1;
         int kc;
-        const int S = splits_for(B, m->max_split[tw], 1, &kc);
+        const int S = splits_for(B, kMaxSplits, 1, &kc);
         float *wp = S > 1 ? m->partials + m->partial_off[tw] : m->grads + m->off[tw];
         float *bp = S > 1 ? m->partials + m->partial_off[tb] : m->grads + m->off[tb];
         ProfScope ps(K_HEAD_WGRAD, st);
@@ -302,9 +353,9 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         const void *dHl = m->dh[cur];
         const void *a_prev = (l == 0) ? a0 : m->acts[l - 1];
         const int tw = 2 * l, tb = tw + 1;
-        {   // db_l = colsum(dH_l)
+        if (!(small && l == L - 2)) {   // db_l = colsum(dH_l) (the last hidden layer's came with the small-gradient launch)
             int kc;
-            const int S = splits_for(B, m->max_split[tb], 1, &kc);
+            const int S = splits_for(B, kMaxSplits, 1, &kc);
             float *bp = S > 1 ? m->partials + m->partial_off[tb] : m->grads + m->off[tb];
             ProfScope ps(K_COLSUM, st);
             rc = launch_colsum(dHl, bf16, B, out, bp, m->partial_stride[tb], S, st);
@@ -413,11 +464,13 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
         const int64_t tiles = ((outw + 127) / 128) * ((in + 127) / 128);
         int64_t s = sms / tiles;   // one wave of CTAs
         s = s < 1 ? 1 : (s > kMaxSplits ? kMaxSplits : s);
-        m->max_split[2 * l] = (l == m->n_layers - 1) ? kMaxSplits : (int)s;
-        m->max_split[2 * l + 1] = kMaxSplits;
-        if (l < m->n_layers - 1) { m->shadow_off[l] = so; so += round_up(in * outw, 128); }
+        m->max_split[2 * l] = (l == m->n_layers - 1) ? kMaxRowBlocks : (int)s;
+        m->max_split[2 * l + 1] = (l >= m->n_layers - 2) ? kMaxRowBlocks : kMaxSplits;
+        m->shadow_off[l] = so;
+        so += round_up(in * (l < m->n_layers - 1 ? outw : 16), 128);
     }
     m->shadow_total = so;
+    m->fused = precision == TS_PREC_BF16 && m->n_layers == 2 && fused_mlp_supported(dims[0], dims[1], dims[2]);
     m->total = o;
     m->n_chunks = o / kChunk;
     m->chunk_tensor_host.assign((size_t)m->n_chunks, -1);
@@ -489,7 +542,8 @@ int32_t ts_mlp_sync_weights(ts_mlp *m, void *stream) {
     if (m->prec != TS_PREC_BF16) return TS_OK;
     TS_REQUIRE(m->params && m->ws_set, TS_E_STATE, "bind parameters and workspace before ts_mlp_sync_weights");
     TS_CUDA_CHECK(cudaSetDevice(m->device));
-    for (int l = 0; l < m->n_layers - 1; ++l) {
+    TS_CUDA_CHECK(cudaMemsetAsync(m->shadow, 0, (size_t)m->shadow_total * 2, (cudaStream_t)stream));   // padded class rows stay zero
+    for (int l = 0; l < m->n_layers; ++l) {
         int rc = launch_cast_bf16(m->params + m->off[2 * l], m->shadow + m->shadow_off[l], m->cnt[2 * l], (cudaStream_t)stream);
         if (rc) return rc;
     }
@@ -520,6 +574,8 @@ int32_t ts_eval_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const 
     TS_REQUIRE(inputs && targets && predictions && record, TS_E_INVALID, "null inputs/targets/predictions/record pointer");
     TS_CUDA_CHECK(cudaSetDevice(m->device));
     const void *a0 = nullptr, *a_last = nullptr;
+    if (m->fused)
+        return fused_forward(m, inputs, inputs_dtype, targets, batch, nullptr, 0, false, predictions, record, &a0, (cudaStream_t)stream);
     rc = forward_hidden(m, inputs, inputs_dtype, batch, nullptr, 0, false, &a0, &a_last, (cudaStream_t)stream);
     if (rc) return rc;
     HeadArgs h{};
@@ -569,6 +625,12 @@ int32_t ts_test_gemm_bf16(const void *A, int32_t a_major, int64_t lda, const voi
     g.splits = splits; g.k_chunk = 0; g.split_stride = split_stride;
     g.dbg = (unsigned long long *)debug_clocks;
     return launch_tc_gemm(g, sms, (cudaStream_t)stream);
+}
+
+int32_t ts_test_fused_trace(uint64_t *out) {
+    TS_REQUIRE(out, TS_E_INVALID, "null argument");
+    TS_CUDA_CHECK(cudaDeviceSynchronize());
+    return read_fused_trace((unsigned long long *)out);
 }
 
 int32_t ts_profile_begin(void) {

@@ -1,0 +1,456 @@
+// Fused forward + head (+ backward to dH) for the one-hidden-layer aggregate -- the shape the reference ships
+// (examples/tinysys/main.py:60: MLP(784, 256, 10)). One CTA owns 128 batch rows and the FULL hidden width, so
+// a whole row of the network lives on chip from the input tile to the loss:
+//
+//   H  = X W1^T                     tcgen05.mma, X and W1 tiles by TMA, accumulator in TMEM (cols 0..H)
+//   A  = relu(dropout(H + b1))      epilogue threads (one row each), written as bf16 into a swizzled smem tile
+//   Z  = A W2^T                     tcgen05.mma again: that smem tile IS a valid K-major operand; Z -> TMEM cols 256..271
+//   loss, argmax, dZ                per-row softmax in registers; loss sum / correct count reduced warp->CTA->grid
+//   dA = dZ W2                      third tcgen05.mma (K = 16 padded classes), overwrites TMEM cols 0..H
+//   dH = dA * relu'(A) / (1-p)      epilogue threads, bf16, coalesced store
+//
+// classifier.py:22-27 (forward, loss), :31-35 (fit), :37-39 (evaluate); mlp.py:14-17; metrics.py:14-15.
+// Restrictions (else the engine uses the layer-by-layer path): hidden width 64, 128 or 256,
+// at most 16 classes, ReLU, bf16 mode.
+#include "tc_common.cuh"
+
+namespace tsb {
+
+using namespace tc;
+
+namespace {
+
+constexpr int kThreads = 352;   // warp 0: X producer, 1: MMA issuer + TMEM owner, 2: W1/W2 producer, 3..10: epilogue
+constexpr int kEpiThreads = 256; // two warps per TMEM lane quarter, each owning half of the hidden columns
+constexpr int kMaxStages = 6;
+constexpr int CP = 16;          // classes padded to one UMMA N / K step
+constexpr int kZCol = 256;      // TMEM column of the logits accumulator
+
+struct FusedParams {
+    int B, D, H, C;
+    int num_kblocks, stages;
+    uint32_t b_bytes;
+    uint32_t idesc_main, idesc_z, idesc_da;
+    const float *b1, *b2;
+    const int64_t *y;
+    int64_t *pred;
+    float *dz;                 // [B, C] fp32 (training) or nullptr
+    __nv_bfloat16 *A_out;      // [B, H] (training) or nullptr
+    __nv_bfloat16 *dH_out;     // [B, H] (training) or nullptr
+    DropoutSpec drop;
+    int training;
+    HeadPartial *partials;
+    unsigned int *ticket;
+    ts_batch_record *record;
+};
+
+// clock64 trace of CTA 0 of the most recent launch (read back by the ts_test_fused_trace hook)
+__device__ unsigned long long g_fused_trace[32];
+#define TRACE(i) do { if (blockIdx.x == 0) g_fused_trace[i] = clock64(); } while (0)
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+template <bool TRAIN>
+__global__ void __launch_bounds__(kThreads, 1)
+fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w1,
+                 const __grid_constant__ CUtensorMap tma_w2, const FusedParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kMaxStages];
+    __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
+    __shared__ __align__(8) uint64_t h_full_bar, w2_full_bar, a_ready_bar, z_full_bar, dz_ready_bar, da_full_bar;
+    __shared__ uint32_t tmem_base_slot;
+    __shared__ float s_loss[4];
+    __shared__ int s_corr[4];
+    __shared__ bool s_last;
+
+    uint8_t *tiles = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t a_bytes = BM * 128;                       // one 64-wide K atom of X: 128 rows x 128 B
+    const uint32_t stage_bytes = a_bytes + p.b_bytes;
+    const int atoms = p.H / KATOM;                           // 64-column atoms of the hidden width
+    uint8_t *a_stage = tiles;                                // after the main loop: A (then dH) tile, atoms x 16 KiB
+    uint8_t *dz_tile = tiles + (size_t)atoms * a_bytes;      // 128 rows x 128 B, first 32 B of each row used
+    uint8_t *w2_tile = tiles + (size_t)p.stages * stage_bytes;           // atoms x [16 rows x 128 B]
+    float *b1s = reinterpret_cast<float *>(w2_tile + (size_t)atoms * 2048);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * BM;
+    if (threadIdx.x == 0) TRACE(0);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&h_full_bar, 1);
+        mbar_init(&w2_full_bar, 1);
+        mbar_init(&a_ready_bar, kEpiThreads);
+        mbar_init(&z_full_bar, 1);
+        mbar_init(&dz_ready_bar, 128);
+        mbar_init(&da_full_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_x)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_w1)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_w2)) : "memory");
+    }
+    if (warp == 1) tmem_alloc(&tmem_base_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+    if (threadIdx.x == 0) TRACE(1);
+
+    if (warp == 0) {
+        // ===================== TMA producer: X tiles (A operand) =====================
+        int s = 0;
+        uint32_t phase = 0;
+        for (int kb = 0; kb < p.num_kblocks; ++kb) {
+            if (elect_one()) {
+                mbar_wait(&empty_bar[s], phase ^ 1);
+                mbar_expect_tx(&full_bar[s], a_bytes);
+                tma_load_2d(&tma_x, &full_bar[s], tiles + (size_t)s * stage_bytes, kb * KATOM, m0);
+            }
+            __syncwarp();
+            if (++s == p.stages) { s = 0; phase ^= 1; }
+        }
+    } else if (warp == 2) {
+        // ===================== TMA producer: W2 tile once, then W1 tiles (B operand) =====================
+        if (elect_one()) {
+            mbar_expect_tx(&w2_full_bar, (uint32_t)atoms * 2048u);
+            for (int a = 0; a < atoms; ++a) tma_load_2d(&tma_w2, &w2_full_bar, w2_tile + (size_t)a * 2048, a * KATOM, 0);
+        }
+        __syncwarp();
+        int s = 0;
+        uint32_t phase = 0;
+        for (int kb = 0; kb < p.num_kblocks; ++kb) {
+            if (elect_one()) {
+                mbar_wait(&empty_bar[s], phase ^ 1);
+                mbar_expect_tx(&full_bar[s], p.b_bytes);
+                tma_load_2d(&tma_w1, &full_bar[s], tiles + (size_t)s * stage_bytes + a_bytes, kb * KATOM, 0);
+            }
+            __syncwarp();
+            if (++s == p.stages) { s = 0; phase ^= 1; }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        int s = 0;
+        uint32_t phase = 0;
+        for (int kb = 0; kb < p.num_kblocks; ++kb) {
+            if (elect_one()) {
+                mbar_wait(&full_bar[s], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(tiles + (size_t)s * stage_bytes);
+                const uint64_t adesc = make_desc(sa, TC_MAJOR_K, KATOM), bdesc = make_desc(sa + a_bytes, TC_MAJOR_K, KATOM);
+#pragma unroll
+                for (int k = 0; k < KATOM / UMMA_K; ++k)
+                    umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc_main, (kb > 0 || k > 0) ? 1u : 0u);
+                umma_commit(&empty_bar[s]);
+                if (kb == p.num_kblocks - 1) umma_commit(&h_full_bar);
+                if (kb == 0) TRACE(2);
+                if (kb == p.num_kblocks - 1) TRACE(3);
+            }
+            __syncwarp();
+            if (++s == p.stages) { s = 0; phase ^= 1; }
+        }
+        if (elect_one()) {
+            // ---- Z = A W2^T : A tile written by the epilogue threads (K-major, `atoms` atoms), W2 tile K-major (N = 16)
+            mbar_wait(&w2_full_bar, 0);
+            mbar_wait(&a_ready_bar, 0);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(a_stage), sw = smem_u32(w2_tile);
+            for (int a = 0; a < atoms; ++a) {
+                const uint64_t adesc = make_desc(sa + a * a_bytes, TC_MAJOR_K, KATOM);
+                const uint64_t bdesc = make_desc(sw + a * 2048, TC_MAJOR_K, KATOM);
+#pragma unroll
+                for (int k = 0; k < KATOM / UMMA_K; ++k)
+                    umma_bf16(tmem_base + kZCol, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc_z, (a > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(&z_full_bar);
+            TRACE(6);
+            if (TRAIN) {
+                // ---- dA = dZ W2 : dZ tile K-major with K = 16; the same W2 tile read as an MN-major operand
+                //      (K = 16 class rows, N atoms of 64 columns 2 KiB apart)
+                mbar_wait(&dz_ready_bar, 0);
+                tc_fence_after();
+                umma_bf16(tmem_base, make_desc(smem_u32(dz_tile), TC_MAJOR_K, KATOM), make_desc(sw, TC_MAJOR_MN, CP), p.idesc_da, 0u);
+                umma_commit(&da_full_bar);
+                TRACE(10);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== epilogue warps: thread = (batch row, half of the hidden columns) =====================
+        const int q = warp & 3;                          // TMEM lane quarter
+        const int half = (warp - 3) >> 2;                // which half of the hidden columns
+        const int r_local = q * 32 + lane;               // row within the 128-row tile == TMEM lane
+        const int64_t row = (int64_t)m0 + r_local;
+        const bool row_ok = row < p.B;
+        const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+        const int et = threadIdx.x - 96;                 // 0..255
+        const int cbeg = half * (p.H >> 1), cend = cbeg + (p.H >> 1);
+        for (int i = et; i < p.H; i += kEpiThreads) b1s[i] = p.b1[i];
+        named_bar_sync(1, kEpiThreads);
+
+        // ---- A = relu(dropout(H + b1)) -> bf16 -> swizzled K-major tile
+        uint32_t sign[4] = {0, 0, 0, 0};
+        if (elect_one()) mbar_wait(&h_full_bar, 0);
+        __syncwarp();
+        tc_fence_after();
+        if (et == 0) TRACE(4);
+#pragma unroll 1
+        for (int c0 = cbeg; c0 < cend; c0 += 32) {
+            float v[32];
+            tmem_ld16(t_lane + (uint32_t)c0, *reinterpret_cast<float(*)[16]>(&v[0]));
+            tmem_ld16(t_lane + (uint32_t)(c0 + 16), *reinterpret_cast<float(*)[16]>(&v[16]));
+            uint32_t bits = 0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                float keep[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+                if (TRAIN && p.training && row_ok) p.drop.factor4(row, c0 + j, p.H, keep);
+                const float4 bb = *reinterpret_cast<const float4 *>(&b1s[c0 + j]);
+                const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float a = round_bf16(fmaxf((v[j + i] + bv[i]) * keep[i], 0.0f));
+                    v[j + i] = a;
+                    bits |= (a > 0.0f ? 1u : 0u) << (j + i);
+                }
+            }
+            const int ci = (c0 - cbeg) >> 5;
+            if (ci == 0) sign[0] = bits; else if (ci == 1) sign[1] = bits; else if (ci == 2) sign[2] = bits; else sign[3] = bits;
+            uint8_t *rowp = a_stage + (size_t)(c0 >> 6) * a_bytes + (size_t)r_local * 128;
+            const int cbase = (c0 & 63) >> 3;            // first 16-byte chunk of this 32-column group: 0 or 4
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                uint4 pk;
+                pk.x = pack_bf16(v[8 * t], v[8 * t + 1]);
+                pk.y = pack_bf16(v[8 * t + 2], v[8 * t + 3]);
+                pk.z = pack_bf16(v[8 * t + 4], v[8 * t + 5]);
+                pk.w = pack_bf16(v[8 * t + 6], v[8 * t + 7]);
+                *reinterpret_cast<uint4 *>(rowp + (((cbase + t) ^ (r_local & 7)) << 4)) = pk;
+            }
+        }
+        fence_proxy_async_smem();          // the tensor core reads this tile through the async proxy
+        tc_fence_before();
+        mbar_arrive(&a_ready_bar);
+        if (et == 0) TRACE(5);
+
+        // ---- coalesced copy of this warp's rows x columns of a bf16 tile held in a_stage to a global [B, H] matrix
+        const int npieces = p.H >> 4;                    // 16-byte pieces per row in this warp's column half (4, 8 or 16)
+        const int np_shift = 31 - __clz(npieces);
+        auto copy_out = [&](__nv_bfloat16 *dst) {
+            for (int idx = lane; idx < 32 * npieces; idx += 32) {
+                const int rr = q * 32 + (idx >> np_shift);
+                const int pc = half * npieces + (idx & (npieces - 1));   // piece index within the full row
+                const uint4 t = *reinterpret_cast<const uint4 *>(a_stage + (size_t)(pc >> 3) * a_bytes + (size_t)rr * 128 + (((pc & 7) ^ (rr & 7)) << 4));
+                if ((int64_t)m0 + rr < p.B) *reinterpret_cast<uint4 *>(dst + ((int64_t)m0 + rr) * p.H + pc * 8) = t;
+            }
+        };
+        if (TRAIN && p.A_out != nullptr) {
+            __syncwarp();
+            copy_out(p.A_out);                           // dW2 = dZ^T A reads it
+        }
+        if (et == 0) TRACE(7);
+
+        float loss_acc = 0.0f;
+        int corr_acc = 0;
+        if (half == 0) {
+            // ---- logits, cross-entropy, argmax, dZ (classifier.py:27,35): one row per thread, all in registers.
+            //      bf16 mode tolerates the fast exp/log (ex2/lg2.approx, ~2 ulp); argmax is taken on the raw logits.
+            const int yy = row_ok ? (int)p.y[row] : 0;            // issued before the wait: latency hidden behind the logits MMA
+            float b2v[CP];
+#pragma unroll
+            for (int c = 0; c < CP; ++c) b2v[c] = (c < p.C) ? p.b2[c] : 0.0f;
+            if (elect_one()) mbar_wait(&z_full_bar, 0);
+            __syncwarp();
+            tc_fence_after();
+            if (et == 0) TRACE(8);
+            float z[CP];
+            tmem_ld16(t_lane + (uint32_t)kZCol, z);
+#pragma unroll
+            for (int c = 0; c < CP; ++c) z[c] = (c < p.C) ? z[c] + b2v[c] : 0.0f;
+            float mx = z[0];
+            int arg = 0;
+#pragma unroll
+            for (int c = 1; c < CP; ++c)
+                if (c < p.C && z[c] > mx) { mx = z[c]; arg = c; }      // strict '>': first maximum wins (torch.argmax)
+            float e[CP];
+            float ssum = 0.0f;
+#pragma unroll
+            for (int c = 0; c < CP; ++c) { e[c] = (c < p.C) ? __expf(z[c] - mx) : 0.0f; ssum += e[c]; }
+            const float lse = mx + __logf(ssum);
+            const float inv_sum = 1.0f / ssum;
+            float zy = 0.0f;
+#pragma unroll
+            for (int c = 0; c < CP; ++c)
+                if (c == yy) zy = z[c];
+            float row_loss = lse - zy;
+            if (yy < 0 || yy >= p.C) row_loss = __int_as_float(0x7fc00000);
+            loss_acc = row_ok ? row_loss : 0.0f;
+            corr_acc = (row_ok && arg == yy) ? 1 : 0;
+            if (row_ok) p.pred[row] = arg;
+
+            if (TRAIN) {
+                const float inv_B = 1.0f / (float)p.B;
+                float dzv[CP];
+#pragma unroll
+                for (int c = 0; c < CP; ++c)
+                    dzv[c] = (c < p.C && row_ok) ? (e[c] * inv_sum - (c == yy ? 1.0f : 0.0f)) * inv_B : 0.0f;
+                if (p.dz != nullptr && row_ok) {
+#pragma unroll
+                    for (int c = 0; c < CP; ++c)
+                        if (c < p.C) p.dz[row * p.C + c] = dzv[c];
+                }
+                // dZ tile: K-major, 16 bf16 (two 16-byte chunks) per row
+                uint8_t *drow = dz_tile + (size_t)r_local * 128;
+                uint4 c0v, c1v;
+                c0v.x = pack_bf16(dzv[0], dzv[1]);   c0v.y = pack_bf16(dzv[2], dzv[3]);
+                c0v.z = pack_bf16(dzv[4], dzv[5]);   c0v.w = pack_bf16(dzv[6], dzv[7]);
+                c1v.x = pack_bf16(dzv[8], dzv[9]);   c1v.y = pack_bf16(dzv[10], dzv[11]);
+                c1v.z = pack_bf16(dzv[12], dzv[13]); c1v.w = pack_bf16(dzv[14], dzv[15]);
+                *reinterpret_cast<uint4 *>(drow + ((0 ^ (r_local & 7)) << 4)) = c0v;
+                *reinterpret_cast<uint4 *>(drow + ((1 ^ (r_local & 7)) << 4)) = c1v;
+                fence_proxy_async_smem();
+                tc_fence_before();
+                mbar_arrive(&dz_ready_bar);
+                if (et == 0) TRACE(9);
+            }
+        } else if (TRAIN) {
+            // the other half of the warps must not overwrite the A tile before the logits MMA has read it
+            if (elect_one()) mbar_wait(&z_full_bar, 0);
+            __syncwarp();
+        }
+
+        if (TRAIN) {
+            // ---- dH = dA * relu'(A) / (1-p) -> bf16 -> staged in this warp's part of the (now free) A tile
+            if (elect_one()) mbar_wait(&da_full_bar, 0);
+            __syncwarp();
+            tc_fence_after();
+            if (et == 0) TRACE(11);
+            const float sc = p.training ? p.drop.scale : 1.0f;
+#pragma unroll 1
+            for (int c0 = cbeg; c0 < cend; c0 += 32) {
+                float v[32];
+                tmem_ld16(t_lane + (uint32_t)c0, *reinterpret_cast<float(*)[16]>(&v[0]));
+                tmem_ld16(t_lane + (uint32_t)(c0 + 16), *reinterpret_cast<float(*)[16]>(&v[16]));
+                const int ci = (c0 - cbeg) >> 5;
+                const uint32_t bits = ci == 0 ? sign[0] : ci == 1 ? sign[1] : ci == 2 ? sign[2] : sign[3];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = ((bits >> j) & 1u) ? v[j] * sc : 0.0f;
+                uint8_t *rowp = a_stage + (size_t)(c0 >> 6) * a_bytes + (size_t)r_local * 128;
+                const int cbase = (c0 & 63) >> 3;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    uint4 pk;
+                    pk.x = pack_bf16(v[8 * t], v[8 * t + 1]);
+                    pk.y = pack_bf16(v[8 * t + 2], v[8 * t + 3]);
+                    pk.z = pack_bf16(v[8 * t + 4], v[8 * t + 5]);
+                    pk.w = pack_bf16(v[8 * t + 6], v[8 * t + 7]);
+                    *reinterpret_cast<uint4 *>(rowp + (((cbase + t) ^ (r_local & 7)) << 4)) = pk;
+                }
+            }
+            __syncwarp();
+            if (p.dH_out != nullptr) copy_out(p.dH_out);
+        }
+        if (et == 0) TRACE(12);
+
+        // ---- loss sum / correct count: warp -> CTA -> grid (last CTA finalises in a fixed order)
+        if (half == 0) {
+            loss_acc = warp_sum(loss_acc);
+            corr_acc = warp_sum(corr_acc);
+            if (lane == 0) { s_loss[q] = loss_acc; s_corr[q] = corr_acc; }
+            named_bar_sync(2, 128);
+            if (q == 3 && lane == 0) {
+                p.partials[blockIdx.x].loss_sum = s_loss[0] + s_loss[1] + s_loss[2] + s_loss[3];
+                p.partials[blockIdx.x].correct = s_corr[0] + s_corr[1] + s_corr[2] + s_corr[3];
+                __threadfence();
+                s_last = (atomicAdd(p.ticket, 1u) == gridDim.x - 1);
+            }
+            named_bar_sync(2, 128);
+            if (s_last && q == 3) {
+                __threadfence();
+                float l = 0.0f;
+                int c = 0;
+                for (int b = lane; b < (int)gridDim.x; b += 32) {
+                    const volatile HeadPartial *hp = p.partials + b;
+                    l += hp->loss_sum;
+                    c += hp->correct;
+                }
+                l = warp_sum(l);
+                c = warp_sum(c);
+                if (lane == 0) {
+                    p.record->loss = l / (float)p.B;
+                    p.record->n_correct = c;
+                    p.record->n_rows = (int32_t)p.B;
+                    p.record->reserved = 0;
+                    *p.ticket = 0u;
+                }
+            }
+        }
+    }
+    __syncwarp();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+    if (threadIdx.x == 0) TRACE(13);
+}
+
+}  // namespace
+
+int read_fused_trace(unsigned long long *out_host) {
+    TS_CUDA_CHECK(cudaMemcpyFromSymbol(out_host, g_fused_trace, sizeof(unsigned long long) * 32));
+    return TS_OK;
+}
+
+bool fused_mlp_supported(int D, int H, int C) { return (H == 64 || H == 128 || H == 256) && C >= 1 && C <= CP && D % 8 == 0; }
+
+int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st) {
+    TS_REQUIRE(fused_mlp_supported(a.D, a.H, a.C), TS_E_UNSUPPORTED, "fused MLP kernel: unsupported shape D=%d H=%d C=%d", a.D, a.H, a.C);
+    TS_REQUIRE(a.B >= 1, TS_E_INVALID, "fused MLP kernel: batch %lld", (long long)a.B);
+    FusedParams p{};
+    p.B = (int)a.B; p.D = a.D; p.H = a.H; p.C = a.C;
+    p.num_kblocks = (a.D + KATOM - 1) / KATOM;
+    p.b_bytes = (uint32_t)a.H * 128u;
+    const uint32_t stage = BM * 128 + p.b_bytes;
+    const int atoms = a.H / KATOM;
+    const uint32_t alias_need = (uint32_t)atoms * BM * 128 + BM * 128;      // A tile + dZ tile reuse the stage memory
+    p.stages = (int)((190u * 1024u) / stage);
+    if (p.stages > kMaxStages) p.stages = kMaxStages;
+    while ((uint32_t)p.stages * stage < alias_need) ++p.stages;
+    p.idesc_main = make_idesc(BM, a.H, TC_MAJOR_K, TC_MAJOR_K);
+    p.idesc_z = make_idesc(BM, CP, TC_MAJOR_K, TC_MAJOR_K);
+    p.idesc_da = make_idesc(BM, a.H, TC_MAJOR_K, TC_MAJOR_MN);
+    p.b1 = a.b1; p.b2 = a.b2; p.y = a.y; p.pred = a.pred; p.dz = a.dz; p.A_out = a.A_out; p.dH_out = a.dH_out;
+    p.drop = a.drop; p.training = a.training;
+    p.partials = a.partials; p.ticket = a.ticket; p.record = a.record;
+
+    CUtensorMap mx, mw1, mw2;
+    int rc = get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, BM, &mx);
+    if (rc) return rc;
+    rc = get_map(a.W1, (uint64_t)a.D, (uint64_t)a.H, (uint64_t)a.D, KATOM, (uint32_t)a.H, &mw1);
+    if (rc) return rc;
+    rc = get_map(a.W2p, (uint64_t)a.H, (uint64_t)CP, (uint64_t)a.H, KATOM, CP, &mw2);
+    if (rc) return rc;
+
+    const int grid = (int)((a.B + BM - 1) / BM);
+    TS_REQUIRE(grid <= kMaxHeadBlocks, TS_E_TOO_LARGE, "fused MLP kernel: batch %lld needs %d CTAs, more than the %d partial slots",
+               (long long)a.B, grid, kMaxHeadBlocks);
+    const size_t smem = (size_t)p.stages * stage + (size_t)atoms * 2048 + (size_t)a.H * 4 + 1024 + 64;
+    const bool train = a.dH_out != nullptr || a.dz != nullptr;
+    static bool attr_set[2][64] = {{false}};
+    int dev = 0;
+    TS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!attr_set[train][dev & 63]) {
+        if (train) TS_CUDA_CHECK(cudaFuncSetAttribute(fused_mlp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        else TS_CUDA_CHECK(cudaFuncSetAttribute(fused_mlp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        attr_set[train][dev & 63] = true;
+    }
+    if (train) fused_mlp_kernel<true><<<grid, kThreads, smem, st>>>(mx, mw1, mw2, p);
+    else fused_mlp_kernel<false><<<grid, kThreads, smem, st>>>(mx, mw1, mw2, p);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+}  // namespace tsb

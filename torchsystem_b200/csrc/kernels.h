@@ -8,7 +8,8 @@ namespace tsb {
 constexpr int kMaxLayers = 8;          // dense layers per aggregate
 constexpr int kMaxClasses = 32;        // width of the last layer handled by the fused head kernel
 constexpr int kChunk = 1024;           // flat-buffer alignment of every parameter tensor (elements)
-constexpr int kMaxSplits = 32;         // split-K partials per tensor
+constexpr int kMaxSplits = 32;         // split-K partials per weight tensor
+constexpr int kMaxRowBlocks = 128;     // 128-row blocks whose small-gradient partials are kept apart (larger batches: more rows per block is not supported -> fallback kernels)
 constexpr int kMaxHeadBlocks = 1024;   // head-kernel grid cap (partials buffer size)
 
 // ---------------------------------------------------------------- fp32 SIMT GEMM (precision mode F32)
@@ -63,6 +64,11 @@ int launch_head(const HeadArgs &a, int sm_count, cudaStream_t st);
 // dW_last[c,k] = sum_r dz[r,c] * A[r,k], db_last[c] = sum_r dz[r,c]; `splits` row ranges -> partials
 int launch_head_wgrad(const void *A, int a_is_bf16, const float *dz, int64_t B, int K, int C, float *w_partial,
                       int64_t w_stride, float *b_partial, int64_t b_stride, int splits, cudaStream_t st);
+
+// dW_last, db_last and the last hidden layer's db in one launch; one partial per 128-row block (ceil(B/128) of them)
+int launch_small_grads(const void *A, const void *dH, int is_bf16, const float *dz, int64_t B, int K, int C, float *w_partial,
+                       int64_t w_stride, float *bl_partial, int64_t bl_stride, float *bh_partial, int64_t bh_stride,
+                       cudaStream_t st);
 
 // column sums of X[B,H] (float or bf16) over `splits` row ranges -> partial[s*stride + h]
 int launch_colsum(const void *X, int is_bf16, int64_t B, int H, float *partial, int64_t stride, int splits,
@@ -129,5 +135,27 @@ struct TcGemmArgs {
     unsigned long long *dbg;       // optional device buffer of 32 clock64 samples from CTA (0,0,0)
 };
 int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st);
+
+// ---------------------------------------------------------------- fused one-hidden-layer forward + head (fused_mlp.cu)
+struct FusedMlpArgs {
+    const __nv_bfloat16 *X;     // [B, D] bf16
+    const __nv_bfloat16 *W1;    // [H, D] bf16 shadow of layer-0 weight
+    const __nv_bfloat16 *W2p;   // [16, H] bf16 shadow of the last weight, rows >= C zero
+    const float *b1, *b2;
+    const int64_t *y;
+    int64_t B;
+    int D, H, C;
+    int64_t *pred;
+    float *dz;                  // training outputs (nullptr for evaluate)
+    __nv_bfloat16 *A_out, *dH_out;
+    DropoutSpec drop;
+    int training;
+    HeadPartial *partials;
+    unsigned int *ticket;
+    ts_batch_record *record;
+};
+bool fused_mlp_supported(int D, int H, int C);
+int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st);
+int read_fused_trace(unsigned long long *out_host);   // 32 clock64 samples of CTA 0 of the last launch
 
 }  // namespace tsb

@@ -206,6 +206,11 @@ __global__ void __launch_bounds__(256) head_kernel(HeadArgs p) {
                     if (c < C) p.dz[r * C + c] = dzv[c];
             }
             if (dH != nullptr) {
+                // bf16 mode: dA = dZ W contracts the bf16-rounded dZ, like the tensor-core path (fused_mlp.cu)
+                if (p.round_w_bf16) {
+#pragma unroll
+                    for (int c = 0; c < MAXC; ++c) dzv[c] = round_bf16(dzv[c]);
+                }
                 for (int k = lane * 4; k < K; k += 128) {
                     float d[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
@@ -360,6 +365,108 @@ int launch_head_wgrad(const void *A, int a_is_bf16, const float *dz, int64_t B, 
 }
 
 // =====================================================================================
+// Small gradients of the last two layers in one launch, from what the head left behind:
+//   dW_last[c,k] = sum_r dz[r,c] * A[r,k]     db_last[c] = sum_r dz[r,c]     db_hidden[k] = sum_r dH[r,k]
+// A CTA covers 128 rows x 128 hidden columns in two passes: thread = (row group g of 8, column quad), so every
+// thread has 8 row loads of A and of dH in flight at once; the 8 row groups are then folded through shared memory in a fixed
+// order and the CTA writes one partial per output (row block s = blockIdx.y).
+// =====================================================================================
+template <typename T, int MAXC>
+__global__ void __launch_bounds__(256) small_grads_kernel(const T *__restrict__ A, const T *__restrict__ dH,
+                                                          const float *__restrict__ dz, int64_t B, int K, int C,
+                                                          float *__restrict__ w_partial, int64_t w_stride,
+                                                          float *__restrict__ bl_partial, int64_t bl_stride,
+                                                          float *__restrict__ bh_partial, int64_t bh_stride) {
+    constexpr int ROWS = 128;                                  // rows per CTA = rows per partial
+    __shared__ __align__(16) float sdz[ROWS][MAXC];
+    __shared__ __align__(16) float red[MAXC + 1][128];         // [output][column]; row MAXC holds db_hidden
+    const int g = threadIdx.x >> 5, quad = threadIdx.x & 31;
+    const int k = blockIdx.x * 128 + quad * 4;
+    const int64_t r0 = (int64_t)blockIdx.y * ROWS;
+    for (int i = threadIdx.x; i < ROWS * MAXC; i += 256) {
+        const int rr = i / MAXC, c = i % MAXC;
+        sdz[rr][c] = (r0 + rr < B && c < C) ? dz[(r0 + rr) * C + c] : 0.0f;
+    }
+    __syncthreads();
+    float acc[4][MAXC];
+    float accb[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) acc[j][c] = 0.0f;
+    if (k < K) {
+#pragma unroll 1
+        for (int pass = 0; pass < ROWS / 64; ++pass) {
+            float a[8][4], h[8][4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {                      // 16 independent 8-byte loads in flight per thread
+                const int64_t r = r0 + pass * 64 + i * 8 + g;
+                if (r < B) { load4<T>(A + r * K + k, a[i]); load4<T>(dH + r * K + k, h[i]); }
+                else { a[i][0] = a[i][1] = a[i][2] = a[i][3] = 0.0f; h[i][0] = h[i][1] = h[i][2] = h[i][3] = 0.0f; }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int rr = pass * 64 + i * 8 + g;
+                float d[MAXC];
+#pragma unroll
+                for (int c = 0; c < MAXC; c += 4) {
+                    const float4 t = *reinterpret_cast<const float4 *>(&sdz[rr][c]);
+                    d[c] = t.x; d[c + 1] = t.y; d[c + 2] = t.z; d[c + 3] = t.w;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    accb[j] += h[i][j];
+#pragma unroll
+                    for (int c = 0; c < MAXC; ++c) acc[j][c] = fmaf(d[c], a[i][j], acc[j][c]);
+                }
+            }
+        }
+    }
+    // fold the 8 row groups into shared memory one after the other (fixed order -> bit-reproducible);
+    // each thread touches one float4 per output row: conflict-free
+    for (int gg = 0; gg < 8; ++gg) {
+        if (g == gg) {
+#pragma unroll
+            for (int c = 0; c <= MAXC; ++c) {
+                float4 *slot = reinterpret_cast<float4 *>(&red[c][quad * 4]);
+                float4 t = (gg == 0) ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : *slot;
+                if (c < MAXC) { t.x += acc[0][c]; t.y += acc[1][c]; t.z += acc[2][c]; t.w += acc[3][c]; }
+                else { t.x += accb[0]; t.y += accb[1]; t.z += accb[2]; t.w += accb[3]; }
+                *slot = t;
+            }
+        }
+        __syncthreads();
+    }
+    for (int o = threadIdx.x; o < 128 * (MAXC + 1); o += 256) {
+        const int col = o & 127, c = o >> 7;
+        const int kk = blockIdx.x * 128 + col;
+        if (kk >= K) continue;
+        if (c < C) w_partial[(int64_t)blockIdx.y * w_stride + (int64_t)c * K + kk] = red[c][col];
+        else if (c == MAXC) bh_partial[(int64_t)blockIdx.y * bh_stride + kk] = red[c][col];
+    }
+    if (blockIdx.x == 0 && threadIdx.x < C) {
+        float sum = 0.0f;
+        for (int rr = 0; rr < ROWS; ++rr) sum += sdz[rr][threadIdx.x];
+        bl_partial[(int64_t)blockIdx.y * bl_stride + threadIdx.x] = sum;
+    }
+}
+
+int launch_small_grads(const void *A, const void *dH, int is_bf16, const float *dz, int64_t B, int K, int C, float *w_partial,
+                       int64_t w_stride, float *bl_partial, int64_t bl_stride, float *bh_partial, int64_t bh_stride,
+                       cudaStream_t st) {
+    TS_REQUIRE(C <= 16, TS_E_UNSUPPORTED, "small-gradient kernel handles at most 16 classes");
+    dim3 grid((K + 127) / 128, (unsigned)((B + 127) / 128));
+    if (is_bf16)
+        small_grads_kernel<__nv_bfloat16, 16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)A, (const __nv_bfloat16 *)dH, dz, B, K, C, w_partial,
+                                                                    w_stride, bl_partial, bl_stride, bh_partial, bh_stride);
+    else
+        small_grads_kernel<float, 16><<<grid, 256, 0, st>>>((const float *)A, (const float *)dH, dz, B, K, C, w_partial, w_stride,
+                                                            bl_partial, bl_stride, bh_partial, bh_stride);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// =====================================================================================
 // Column sums (hidden-layer bias gradients): thread per column, `splits` row ranges.
 // =====================================================================================
 template <typename T>
@@ -404,14 +511,26 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
     float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     if (d.nsplit > 0) {
         const float *q = p.partials + d.partial_off + j0;
-        if (n == 4) {   // partial_stride is a multiple of 4 and partial_off 16-byte aligned
-            for (int s = 0; s < d.nsplit; ++s) {
-                const float4 v = *reinterpret_cast<const float4 *>(q + (int64_t)s * d.partial_stride);
-                g[0] += v.x; g[1] += v.y; g[2] += v.z; g[3] += v.w;
-            }
-        } else {
-            for (int s = 0; s < d.nsplit; ++s)
-                for (int e = 0; e < n; ++e) g[e] += q[(int64_t)s * d.partial_stride + e];
+        // Always whole float4 loads: partial rows are padded past `count`, so the tail thread may read (and ignore)
+        // up to three floats of padding. Eight loads are in flight per round; a scalar, one-load-per-iteration
+        // tail would serialise a memory round trip per partial. The sum order (s ascending) is fixed.
+        int s = 0;
+        for (; s + 8 <= d.nsplit; s += 8) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const float4 *>(q + (int64_t)(s + u) * d.partial_stride);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { g[0] += v[u].x; g[1] += v[u].y; g[2] += v[u].z; g[3] += v[u].w; }
+        }
+        if (s < d.nsplit) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                v[u] = (s + u < d.nsplit) ? *reinterpret_cast<const float4 *>(q + (int64_t)(s + u) * d.partial_stride)
+                                          : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (s + u < d.nsplit) { g[0] += v[u].x; g[1] += v[u].y; g[2] += v[u].z; g[3] += v[u].w; }
         }
         for (int e = 0; e < n; ++e) p.grads[i0 + e] = g[e];
     } else {
