@@ -169,8 +169,9 @@ class OracleMLP:
         n = len(self.weights)
         gw, gb = [None] * n, [None] * n
         scale = np.float32(1.0) / np.float32(1.0 - self.dropout)
-        # last layer: dW and db use the fp32 dz; the tensor-core dA = dZ W contracts the bf16-rounded dz
-        gw[-1] = dz.T @ acts[-1]
+        # last layer: every tensor-core contraction takes the bf16-rounded dz (dW = dZ^T A, dA = dZ W);
+        # the bias gradient sums the fp32 dz
+        gw[-1] = rnd(dz).T @ acts[-1]
         gb[-1] = dz.sum(axis=0)
         da = rnd(dz) @ rnd(self.weights[-1])
         for l in range(n - 2, -1, -1):
@@ -178,8 +179,8 @@ class OracleMLP:
             if masks is not None and self.dropout > 0.0:
                 g = g * (masks[l].astype(np.float32) * scale)
             dh = (da * g).astype(np.float32)
-            gb[l] = dh.sum(axis=0)
             dhr = rnd(dh)
+            gb[l] = dhr.sum(axis=0)          # column sums of the stored (bf16 in tensor-core mode) dH
             gw[l] = dhr.T @ acts[l]
             if l > 0:
                 da = dhr @ rnd(self.weights[l])

@@ -287,8 +287,14 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     f.y = y; f.B = B; f.D = m->dims[0]; f.H = m->dims[1]; f.C = m->dims[2];
     f.pred = pred;
     f.dz = train ? m->dz : nullptr;
-    f.A_out = train ? (__nv_bfloat16 *)m->acts[0] : nullptr;
+    const bool fuse_grads = train && fused_grads_supported(m->dims[1], m->dims[2], B);
+    f.A_out = (train && !fuse_grads) ? (__nv_bfloat16 *)m->acts[0] : nullptr;
     f.dH_out = train ? (__nv_bfloat16 *)m->dh[0] : nullptr;
+    if (fuse_grads) {   // dW_last, db_last, db_hidden partials per 128-row CTA, straight from the tensor cores
+        f.w2_partial = m->partials + m->partial_off[2]; f.w2_stride = m->partial_stride[2];
+        f.b2_partial = m->partials + m->partial_off[3]; f.b2_stride = m->partial_stride[3];
+        f.b1_partial = m->partials + m->partial_off[1]; f.b1_stride = m->partial_stride[1];
+    }
     f.drop = drop_spec(m, masks, seed, 0, train);
     f.training = train && m->p > 0.0f;
     f.partials = m->head_partials; f.ticket = m->ticket; f.record = rec;
@@ -324,7 +330,10 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     int nsplit[2 * kMaxLayers] = {0};
     const int64_t row_blocks = (B + 127) / 128;
     const bool small = m->classes() <= 16 && row_blocks <= kMaxRowBlocks;   // one launch for dW_last, db_last, db of the last hidden layer
-    if (small) {
+    const bool in_kernel = m->fused && fused_grads_supported(m->dims[1], m->dims[2], B);   // the fused kernel already left them
+    if (in_kernel) {
+        nsplit[2] = nsplit[3] = nsplit[1] = (int)row_blocks;
+    } else if (small) {
         const int tw = 2 * (L - 1), tb = tw + 1, th = 2 * (L - 2) + 1;
         const bool direct = row_blocks == 1;
         float *wp = direct ? m->grads + m->off[tw] : m->partials + m->partial_off[tw];
@@ -353,7 +362,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         const void *dHl = m->dh[cur];
         const void *a_prev = (l == 0) ? a0 : m->acts[l - 1];
         const int tw = 2 * l, tb = tw + 1;
-        if (!(small && l == L - 2)) {   // db_l = colsum(dH_l) (the last hidden layer's came with the small-gradient launch)
+        if (!((small || in_kernel) && l == L - 2)) {   // db_l = colsum(dH_l) (the last hidden layer's came with the small-gradient launch)
             int kc;
             const int S = splits_for(B, kMaxSplits, 1, &kc);
             float *bp = S > 1 ? m->partials + m->partial_off[tb] : m->grads + m->off[tb];

@@ -25,6 +25,7 @@ constexpr int kEpiThreads = 256; // two warps per TMEM lane quarter, each owning
 constexpr int kMaxStages = 6;
 constexpr int CP = 16;          // classes padded to one UMMA N / K step
 constexpr int kZCol = 256;      // TMEM column of the logits accumulator
+constexpr int kGCol = 272;      // TMEM columns of the gradient partials: dW2^T at +0/+16, db1 at +32/+48
 
 struct FusedParams {
     int B, D, H, C;
@@ -37,6 +38,10 @@ struct FusedParams {
     float *dz;                 // [B, C] fp32 (training) or nullptr
     __nv_bfloat16 *A_out;      // [B, H] (training) or nullptr
     __nv_bfloat16 *dH_out;     // [B, H] (training) or nullptr
+    // per-CTA gradient partials computed on the tensor cores (training, H >= 128, C <= 15), else nullptr
+    float *w2_partial, *b2_partial, *b1_partial;
+    int64_t w2_stride, b2_stride, b1_stride;
+    uint32_t idesc_g;
     DropoutSpec drop;
     int training;
     HeadPartial *partials;
@@ -60,7 +65,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kMaxStages];
     __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
-    __shared__ __align__(8) uint64_t h_full_bar, w2_full_bar, a_ready_bar, z_full_bar, dz_ready_bar, da_full_bar;
+    __shared__ __align__(8) uint64_t h_full_bar, w2_full_bar, a_ready_bar, z_full_bar, dz_ready_bar, da_full_bar, dh_ready_bar, g_full_bar;
+    __shared__ float s_db2[4][CP];
     __shared__ uint32_t tmem_base_slot;
     __shared__ float s_loss[4];
     __shared__ int s_corr[4];
@@ -71,7 +77,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     const uint32_t stage_bytes = a_bytes + p.b_bytes;
     const int atoms = p.H / KATOM;                           // 64-column atoms of the hidden width
     uint8_t *a_stage = tiles;                                // after the main loop: A (then dH) tile, atoms x 16 KiB
-    uint8_t *dz_tile = tiles + (size_t)atoms * a_bytes;      // 128 rows x 128 B, first 32 B of each row used
+    uint8_t *dh_stage = tiles + (size_t)atoms * a_bytes;     // dH tile, same layout (kept apart from A: both feed the gradient MMAs)
+    uint8_t *dz_tile = tiles + (size_t)2 * atoms * a_bytes;  // 128 rows x 128 B, first 32 B of each row used
     uint8_t *w2_tile = tiles + (size_t)p.stages * stage_bytes;           // atoms x [16 rows x 128 B]
     float *b1s = reinterpret_cast<float *>(w2_tile + (size_t)atoms * 2048);
 
@@ -87,6 +94,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         mbar_init(&z_full_bar, 1);
         mbar_init(&dz_ready_bar, 128);
         mbar_init(&da_full_bar, 1);
+        mbar_init(&dh_ready_bar, kEpiThreads);
+        mbar_init(&g_full_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_x)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_w1)) : "memory");
@@ -174,6 +183,24 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 umma_bf16(tmem_base, make_desc(smem_u32(dz_tile), TC_MAJOR_K, KATOM), make_desc(sw, TC_MAJOR_MN, CP), p.idesc_da, 0u);
                 umma_commit(&da_full_bar);
                 TRACE(10);
+                if (p.w2_partial != nullptr) {
+                    // ---- per-CTA gradient partials, contraction over this CTA's 128 batch rows (K = rows, 8 steps):
+                    //        dW2^T[h, c] = sum_r A[r, h] dZ[r, c]           TMEM cols 272.. (one 16-column block per 128 hidden units)
+                    //        db1[h]      = sum_r dH[r, h] * 1              = column 15 of dH^T dZ', dZ' column 15 being 1 -> cols 304..
+                    //      The A / dH tiles are read as MN-major operands (M = hidden), the dZ tile as an MN-major B (N = 16).
+                    mbar_wait(&dh_ready_bar, 0);
+                    tc_fence_after();
+                    const uint32_t sd = smem_u32(dz_tile), sh = smem_u32(dh_stage);
+                    for (int mh = 0; mh < p.H / 128; ++mh) {
+#pragma unroll
+                        for (int k = 0; k < BM / UMMA_K; ++k) {
+                            const uint64_t bdesc = make_desc(sd + k * 2048, TC_MAJOR_MN, BM);
+                            umma_bf16(tmem_base + kGCol + 16 * mh, make_desc(sa + (2 * mh) * a_bytes + k * 2048, TC_MAJOR_MN, BM), bdesc, p.idesc_g, k > 0 ? 1u : 0u);
+                            umma_bf16(tmem_base + kGCol + 32 + 16 * mh, make_desc(sh + (2 * mh) * a_bytes + k * 2048, TC_MAJOR_MN, BM), bdesc, p.idesc_g, k > 0 ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(&g_full_bar);
+                }
             }
         }
         __syncwarp();
@@ -237,17 +264,17 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         // ---- coalesced copy of this warp's rows x columns of a bf16 tile held in a_stage to a global [B, H] matrix
         const int npieces = p.H >> 4;                    // 16-byte pieces per row in this warp's column half (4, 8 or 16)
         const int np_shift = 31 - __clz(npieces);
-        auto copy_out = [&](__nv_bfloat16 *dst) {
+        auto copy_out = [&](__nv_bfloat16 *dst, const uint8_t *tile) {
             for (int idx = lane; idx < 32 * npieces; idx += 32) {
                 const int rr = q * 32 + (idx >> np_shift);
                 const int pc = half * npieces + (idx & (npieces - 1));   // piece index within the full row
-                const uint4 t = *reinterpret_cast<const uint4 *>(a_stage + (size_t)(pc >> 3) * a_bytes + (size_t)rr * 128 + (((pc & 7) ^ (rr & 7)) << 4));
+                const uint4 t = *reinterpret_cast<const uint4 *>(tile + (size_t)(pc >> 3) * a_bytes + (size_t)rr * 128 + (((pc & 7) ^ (rr & 7)) << 4));
                 if ((int64_t)m0 + rr < p.B) *reinterpret_cast<uint4 *>(dst + ((int64_t)m0 + rr) * p.H + pc * 8) = t;
             }
         };
         if (TRAIN && p.A_out != nullptr) {
             __syncwarp();
-            copy_out(p.A_out);                           // dW2 = dZ^T A reads it
+            copy_out(p.A_out, a_stage);                  // dW2 = dZ^T A reads it when the gradient partials are not fused
         }
         if (et == 0) TRACE(7);
 
@@ -300,6 +327,15 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                     for (int c = 0; c < CP; ++c)
                         if (c < p.C) p.dz[row * p.C + c] = dzv[c];
                 }
+                if (p.w2_partial != nullptr) {
+                    // db2[c] = sum_r dz[r, c]: warp shuffle, then the four quarters through shared memory
+#pragma unroll
+                    for (int c = 0; c < CP; ++c) {
+                        const float t = warp_sum(dzv[c]);
+                        if (lane == 0) s_db2[q][c] = t;
+                    }
+                    dzv[CP - 1] = row_ok ? 1.0f : 0.0f;      // the "ones" column that turns dH^T dZ' into column sums of dH
+                }
                 // dZ tile: K-major, 16 bf16 (two 16-byte chunks) per row
                 uint8_t *drow = dz_tile + (size_t)r_local * 128;
                 uint4 c0v, c1v;
@@ -336,7 +372,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 const uint32_t bits = ci == 0 ? sign[0] : ci == 1 ? sign[1] : ci == 2 ? sign[2] : sign[3];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = ((bits >> j) & 1u) ? v[j] * sc : 0.0f;
-                uint8_t *rowp = a_stage + (size_t)(c0 >> 6) * a_bytes + (size_t)r_local * 128;
+                uint8_t *rowp = dh_stage + (size_t)(c0 >> 6) * a_bytes + (size_t)r_local * 128;
                 const int cbase = (c0 & 63) >> 3;
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
@@ -348,8 +384,29 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                     *reinterpret_cast<uint4 *>(rowp + (((cbase + t) ^ (r_local & 7)) << 4)) = pk;
                 }
             }
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(&dh_ready_bar);
             __syncwarp();
-            if (p.dH_out != nullptr) copy_out(p.dH_out);
+            if (p.dH_out != nullptr) copy_out(p.dH_out, dh_stage);
+
+            if (p.w2_partial != nullptr) {
+                // ---- gradient partials: TMEM lane = hidden unit; this warp group owns hidden units [128*half, 128*half+128)
+                if (elect_one()) mbar_wait(&g_full_bar, 0);
+                __syncwarp();
+                tc_fence_after();
+                if (half < p.H / 128) {
+                    const int h = half * 128 + r_local;
+                    float gw[CP], gb[CP];
+                    tmem_ld16(t_lane + (uint32_t)(kGCol + 16 * half), gw);
+                    tmem_ld16(t_lane + (uint32_t)(kGCol + 32 + 16 * half), gb);
+                    float *wp = p.w2_partial + (int64_t)blockIdx.x * p.w2_stride + h;
+#pragma unroll
+                    for (int c = 0; c < CP; ++c)
+                        if (c < p.C) wp[(int64_t)c * p.H] = gw[c];
+                    p.b1_partial[(int64_t)blockIdx.x * p.b1_stride + h] = gb[CP - 1];
+                }
+            }
         }
         if (et == 0) TRACE(12);
 
@@ -359,6 +416,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             corr_acc = warp_sum(corr_acc);
             if (lane == 0) { s_loss[q] = loss_acc; s_corr[q] = corr_acc; }
             named_bar_sync(2, 128);
+            if (TRAIN && p.w2_partial != nullptr && q == 0 && lane < p.C)      // s_db2 was filled before this barrier
+                p.b2_partial[(int64_t)blockIdx.x * p.b2_stride + lane] = (s_db2[0][lane] + s_db2[1][lane]) + (s_db2[2][lane] + s_db2[3][lane]);
             if (q == 3 && lane == 0) {
                 p.partials[blockIdx.x].loss_sum = s_loss[0] + s_loss[1] + s_loss[2] + s_loss[3];
                 p.partials[blockIdx.x].correct = s_corr[0] + s_corr[1] + s_corr[2] + s_corr[3];
@@ -415,13 +474,19 @@ int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st) {
     p.b_bytes = (uint32_t)a.H * 128u;
     const uint32_t stage = BM * 128 + p.b_bytes;
     const int atoms = a.H / KATOM;
-    const uint32_t alias_need = (uint32_t)atoms * BM * 128 + BM * 128;      // A tile + dZ tile reuse the stage memory
+    const uint32_t alias_need = 2u * (uint32_t)atoms * BM * 128 + BM * 128;   // A tile + dH tile + dZ tile reuse the stage memory
     p.stages = (int)((190u * 1024u) / stage);
     if (p.stages > kMaxStages) p.stages = kMaxStages;
     while ((uint32_t)p.stages * stage < alias_need) ++p.stages;
     p.idesc_main = make_idesc(BM, a.H, TC_MAJOR_K, TC_MAJOR_K);
     p.idesc_z = make_idesc(BM, CP, TC_MAJOR_K, TC_MAJOR_K);
     p.idesc_da = make_idesc(BM, a.H, TC_MAJOR_K, TC_MAJOR_MN);
+    p.idesc_g = make_idesc(BM, CP, TC_MAJOR_MN, TC_MAJOR_MN);
+    const bool fuse_grads = a.w2_partial != nullptr;
+    TS_REQUIRE(!fuse_grads || (a.H >= 128 && a.C < CP && a.b1_partial && a.b2_partial), TS_E_INVALID,
+               "fused gradient partials need H >= 128, C <= 15 and all three partial buffers");
+    p.w2_partial = a.w2_partial; p.b2_partial = a.b2_partial; p.b1_partial = a.b1_partial;
+    p.w2_stride = a.w2_stride; p.b2_stride = a.b2_stride; p.b1_stride = a.b1_stride;
     p.b1 = a.b1; p.b2 = a.b2; p.y = a.y; p.pred = a.pred; p.dz = a.dz; p.A_out = a.A_out; p.dH_out = a.dH_out;
     p.drop = a.drop; p.training = a.training;
     p.partials = a.partials; p.ticket = a.ticket; p.record = a.record;

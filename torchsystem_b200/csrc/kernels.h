@@ -148,6 +148,9 @@ struct FusedMlpArgs {
     int64_t *pred;
     float *dz;                  // training outputs (nullptr for evaluate)
     __nv_bfloat16 *A_out, *dH_out;
+    // optional: per-CTA partials of dW_last [C][H], db_last [C], db_hidden [H] computed in-kernel (H >= 128, C <= 15)
+    float *w2_partial, *b2_partial, *b1_partial;
+    int64_t w2_stride, b2_stride, b1_stride;
     DropoutSpec drop;
     int training;
     HeadPartial *partials;
@@ -155,6 +158,7 @@ struct FusedMlpArgs {
     ts_batch_record *record;
 };
 bool fused_mlp_supported(int D, int H, int C);
+inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }
 int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st);
 int read_fused_trace(unsigned long long *out_host);   // 32 clock64 samples of CTA 0 of the last launch
 

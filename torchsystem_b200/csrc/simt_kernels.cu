@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(128) head_wgrad_kernel(const T *__restrict__ A
             for (int rr = 0; rr < nr; ++rr) {
                 const float a = to_f32(A[(rt + rr) * K + k]);
 #pragma unroll
-                for (int c = 0; c < MAXC; ++c) acc[c] = fmaf(sdz[rr][c], a, acc[c]);
+                for (int c = 0; c < MAXC; ++c) acc[c] = fmaf(sizeof(T) == 2 ? round_bf16(sdz[rr][c]) : sdz[rr][c], a, acc[c]);
             }
         }
         if (blockIdx.x == 0 && threadIdx.x < C)
@@ -379,7 +379,8 @@ __global__ void __launch_bounds__(256) small_grads_kernel(const T *__restrict__ 
                                                           float *__restrict__ bh_partial, int64_t bh_stride) {
     constexpr int ROWS = 128;                                  // rows per CTA = rows per partial
     __shared__ __align__(16) float sdz[ROWS][MAXC];
-    __shared__ __align__(16) float red[MAXC + 1][128];         // [output][column]; row MAXC holds db_hidden
+    extern __shared__ __align__(16) float red_dyn[];            // [8 row groups][MAXC + 1 outputs][128 columns]; output MAXC = db_hidden
+    float(*red)[MAXC + 1][128] = reinterpret_cast<float(*)[MAXC + 1][128]>(red_dyn);
     const int g = threadIdx.x >> 5, quad = threadIdx.x & 31;
     const int k = blockIdx.x * 128 + quad * 4;
     const int64_t r0 = (int64_t)blockIdx.y * ROWS;
@@ -413,6 +414,10 @@ __global__ void __launch_bounds__(256) small_grads_kernel(const T *__restrict__ 
                     const float4 t = *reinterpret_cast<const float4 *>(&sdz[rr][c]);
                     d[c] = t.x; d[c + 1] = t.y; d[c + 2] = t.z; d[c + 3] = t.w;
                 }
+                if (sizeof(T) == 2) {   // bf16 mode: the weight-gradient contraction takes the bf16-rounded dZ (as on the tensor cores)
+#pragma unroll
+                    for (int c = 0; c < MAXC; ++c) d[c] = round_bf16(d[c]);
+                }
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     accb[j] += h[i][j];
@@ -422,32 +427,33 @@ __global__ void __launch_bounds__(256) small_grads_kernel(const T *__restrict__ 
             }
         }
     }
-    // fold the 8 row groups into shared memory one after the other (fixed order -> bit-reproducible);
-    // each thread touches one float4 per output row: conflict-free
-    for (int gg = 0; gg < 8; ++gg) {
-        if (g == gg) {
+    // every warp parks its accumulators, then all threads fold the 8 row groups in a fixed order (bit-reproducible)
 #pragma unroll
-            for (int c = 0; c <= MAXC; ++c) {
-                float4 *slot = reinterpret_cast<float4 *>(&red[c][quad * 4]);
-                float4 t = (gg == 0) ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : *slot;
-                if (c < MAXC) { t.x += acc[0][c]; t.y += acc[1][c]; t.z += acc[2][c]; t.w += acc[3][c]; }
-                else { t.x += accb[0]; t.y += accb[1]; t.z += accb[2]; t.w += accb[3]; }
-                *slot = t;
-            }
-        }
-        __syncthreads();
+    for (int c = 0; c <= MAXC; ++c) {
+        float4 t;
+        if (c < MAXC) t = make_float4(acc[0][c], acc[1][c], acc[2][c], acc[3][c]);
+        else t = make_float4(accb[0], accb[1], accb[2], accb[3]);
+        *reinterpret_cast<float4 *>(&red[g][c][quad * 4]) = t;
     }
+    __syncthreads();
     for (int o = threadIdx.x; o < 128 * (MAXC + 1); o += 256) {
         const int col = o & 127, c = o >> 7;
+        float v[8];
+#pragma unroll
+        for (int gg = 0; gg < 8; ++gg) v[gg] = red[gg][c][col];
+        const float sum = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
         const int kk = blockIdx.x * 128 + col;
         if (kk >= K) continue;
-        if (c < C) w_partial[(int64_t)blockIdx.y * w_stride + (int64_t)c * K + kk] = red[c][col];
-        else if (c == MAXC) bh_partial[(int64_t)blockIdx.y * bh_stride + kk] = red[c][col];
+        if (c < C) w_partial[(int64_t)blockIdx.y * w_stride + (int64_t)c * K + kk] = sum;
+        else if (c == MAXC) bh_partial[(int64_t)blockIdx.y * bh_stride + kk] = sum;
     }
-    if (blockIdx.x == 0 && threadIdx.x < C) {
-        float sum = 0.0f;
-        for (int rr = 0; rr < ROWS; ++rr) sum += sdz[rr][threadIdx.x];
-        bl_partial[(int64_t)blockIdx.y * bl_stride + threadIdx.x] = sum;
+    if (blockIdx.x == 0 && g == 0) {
+        // db_last: lanes split the 128 rows four ways per class, then shuffle-fold (fixed order)
+        for (int c = 0; c < C; ++c) {
+            float part = (sdz[quad][c] + sdz[quad + 32][c]) + (sdz[quad + 64][c] + sdz[quad + 96][c]);
+            part = warp_sum(part);
+            if (quad == 0) bl_partial[(int64_t)blockIdx.y * bl_stride + c] = part;
+        }
     }
 }
 
@@ -456,11 +462,20 @@ int launch_small_grads(const void *A, const void *dH, int is_bf16, const float *
                        cudaStream_t st) {
     TS_REQUIRE(C <= 16, TS_E_UNSUPPORTED, "small-gradient kernel handles at most 16 classes");
     dim3 grid((K + 127) / 128, (unsigned)((B + 127) / 128));
+    const size_t smem = 8 * 17 * 128 * sizeof(float);
+    static bool attr_set[2][64] = {{false}};
+    int dev = 0;
+    TS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!attr_set[is_bf16 ? 1 : 0][dev & 63]) {
+        if (is_bf16) TS_CUDA_CHECK(cudaFuncSetAttribute(small_grads_kernel<__nv_bfloat16, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        else TS_CUDA_CHECK(cudaFuncSetAttribute(small_grads_kernel<float, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set[is_bf16 ? 1 : 0][dev & 63] = true;
+    }
     if (is_bf16)
-        small_grads_kernel<__nv_bfloat16, 16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)A, (const __nv_bfloat16 *)dH, dz, B, K, C, w_partial,
+        small_grads_kernel<__nv_bfloat16, 16><<<grid, 256, smem, st>>>((const __nv_bfloat16 *)A, (const __nv_bfloat16 *)dH, dz, B, K, C, w_partial,
                                                                     w_stride, bl_partial, bl_stride, bh_partial, bh_stride);
     else
-        small_grads_kernel<float, 16><<<grid, 256, 0, st>>>((const float *)A, (const float *)dH, dz, B, K, C, w_partial, w_stride,
+        small_grads_kernel<float, 16><<<grid, 256, smem, st>>>((const float *)A, (const float *)dH, dz, B, K, C, w_partial, w_stride,
                                                             bl_partial, bl_stride, bh_partial, bh_stride);
     TS_LAUNCH_CHECK();
     return TS_OK;
