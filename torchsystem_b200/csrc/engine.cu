@@ -286,8 +286,8 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     f.b2 = m->params + m->off[3];
     f.y = y; f.B = B; f.D = m->dims[0]; f.H = m->dims[1]; f.C = m->dims[2];
     f.pred = pred;
-    f.dz = train ? m->dz : nullptr;
     const bool fuse_grads = train && fused_grads_supported(m->dims[1], m->dims[2], B);
+    f.dz = (train && !fuse_grads) ? m->dz : nullptr;      // fp32 dZ in global memory is only read by the SIMT gradient kernels
     f.A_out = (train && !fuse_grads) ? (__nv_bfloat16 *)m->acts[0] : nullptr;
     f.dH_out = train ? (__nv_bfloat16 *)m->dh[0] : nullptr;
     if (fuse_grads) {   // dW_last, db_last, db_hidden partials per 128-row CTA, straight from the tensor cores
@@ -299,7 +299,7 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     f.training = train && m->p > 0.0f;
     f.partials = m->head_partials; f.ticket = m->ticket; f.record = rec;
     ProfScope ps(K_FUSED, st);
-    return launch_fused_mlp(f, st);
+    return launch_fused_mlp(f, m->sm_count, st);
 }
 
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,

@@ -12,6 +12,8 @@
 // classifier.py:22-27 (forward, loss), :31-35 (fit), :37-39 (evaluate); mlp.py:14-17; metrics.py:14-15.
 // Restrictions (else the engine uses the layer-by-layer path): hidden width 64, 128 or 256,
 // at most 16 classes, ReLU, bf16 mode.
+#include <cstdlib>
+
 #include "tc_common.cuh"
 
 namespace tsb {
@@ -29,6 +31,7 @@ constexpr int kGCol = 272;      // TMEM columns of the gradient partials: dW2^T 
 
 struct FusedParams {
     int B, D, H, C;
+    int ns, BN;                // CTAs per cluster splitting the hidden width, hidden columns per CTA (H / ns)
     int num_kblocks, stages;
     uint32_t b_bytes;
     uint32_t idesc_main, idesc_z, idesc_da;
@@ -51,7 +54,20 @@ struct FusedParams {
 
 // clock64 trace of CTA 0 of the most recent launch (read back by the ts_test_fused_trace hook)
 __device__ unsigned long long g_fused_trace[32];
-#define TRACE(i) do { if (blockIdx.x == 0) g_fused_trace[i] = clock64(); } while (0)
+#define TRACE(i) do { if (blockIdx.x < 2) g_fused_trace[16 * blockIdx.x + (i)] = clock64(); } while (0)
+
+// thread-block-cluster helpers (the hidden width of one 128-row slab is split over `ns` CTAs)
+__device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;" ::: "memory"); }
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t local_saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
@@ -75,15 +91,20 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     uint8_t *tiles = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t a_bytes = BM * 128;                       // one 64-wide K atom of X: 128 rows x 128 B
     const uint32_t stage_bytes = a_bytes + p.b_bytes;
-    const int atoms = p.H / KATOM;                           // 64-column atoms of the hidden width
+    const int atoms = p.BN / KATOM;                          // 64-column atoms of this CTA's share of the hidden width
     uint8_t *a_stage = tiles;                                // after the main loop: A (then dH) tile, atoms x 16 KiB
     uint8_t *dh_stage = tiles + (size_t)atoms * a_bytes;     // dH tile, same layout (kept apart from A: both feed the gradient MMAs)
     uint8_t *dz_tile = tiles + (size_t)2 * atoms * a_bytes;  // 128 rows x 128 B, first 32 B of each row used
     uint8_t *w2_tile = tiles + (size_t)p.stages * stage_bytes;           // atoms x [16 rows x 128 B]
     float *b1s = reinterpret_cast<float *>(w2_tile + (size_t)atoms * 2048);
+    float *zbuf = b1s + p.BN;                                // [ns][128 rows][16] partial logits of every CTA of the cluster (ns > 1)
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * BM;
+    const int ns = p.ns;
+    const uint32_t rank = ns > 1 ? cluster_rank() : 0u;       // which slice of the hidden width
+    const int slab = blockIdx.x / ns;                         // which 128 batch rows
+    const int m0 = slab * BM;
+    const int n0 = (int)rank * p.BN;
     if (threadIdx.x == 0) TRACE(0);
 
     if (threadIdx.x == 0) {
@@ -106,8 +127,10 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
+    if (ns > 1) { cluster_arrive(); cluster_wait(); }          // every CTA of the cluster is running: its shared memory may be written
     if (threadIdx.x == 0) TRACE(1);
 
+    if (ns > 1 && warp < 3) cluster_arrive();                  // phase 1 (logit exchange): these warps only have to have arrived
     if (warp == 0) {
         // ===================== TMA producer: X tiles (A operand) =====================
         int s = 0;
@@ -125,7 +148,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         // ===================== TMA producer: W2 tile once, then W1 tiles (B operand) =====================
         if (elect_one()) {
             mbar_expect_tx(&w2_full_bar, (uint32_t)atoms * 2048u);
-            for (int a = 0; a < atoms; ++a) tma_load_2d(&tma_w2, &w2_full_bar, w2_tile + (size_t)a * 2048, a * KATOM, 0);
+            for (int a = 0; a < atoms; ++a) tma_load_2d(&tma_w2, &w2_full_bar, w2_tile + (size_t)a * 2048, n0 + a * KATOM, 0);
         }
         __syncwarp();
         int s = 0;
@@ -134,7 +157,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             if (elect_one()) {
                 mbar_wait(&empty_bar[s], phase ^ 1);
                 mbar_expect_tx(&full_bar[s], p.b_bytes);
-                tma_load_2d(&tma_w1, &full_bar[s], tiles + (size_t)s * stage_bytes + a_bytes, kb * KATOM, 0);
+                tma_load_2d(&tma_w1, &full_bar[s], tiles + (size_t)s * stage_bytes + a_bytes, kb * KATOM, n0);
             }
             __syncwarp();
             if (++s == p.stages) { s = 0; phase ^= 1; }
@@ -191,7 +214,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                     mbar_wait(&dh_ready_bar, 0);
                     tc_fence_after();
                     const uint32_t sd = smem_u32(dz_tile), sh = smem_u32(dh_stage);
-                    for (int mh = 0; mh < p.H / 128; ++mh) {
+                    for (int mh = 0; mh < (p.BN + 127) / 128; ++mh) {   // a 64-wide slice still issues M = 128: lanes 64.. are ignored
 #pragma unroll
                         for (int k = 0; k < BM / UMMA_K; ++k) {
                             const uint64_t bdesc = make_desc(sd + k * 2048, TC_MAJOR_MN, BM);
@@ -213,8 +236,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         const bool row_ok = row < p.B;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         const int et = threadIdx.x - 96;                 // 0..255
-        const int cbeg = half * (p.H >> 1), cend = cbeg + (p.H >> 1);
-        for (int i = et; i < p.H; i += kEpiThreads) b1s[i] = p.b1[i];
+        const int cbeg = half * (p.BN >> 1), cend = cbeg + (p.BN >> 1);     // local columns
+        for (int i = et; i < p.BN; i += kEpiThreads) b1s[i] = p.b1[n0 + i];
         named_bar_sync(1, kEpiThreads);
 
         // ---- A = relu(dropout(H + b1)) -> bf16 -> swizzled K-major tile
@@ -232,7 +255,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
                 float keep[4] = {1.0f, 1.0f, 1.0f, 1.0f};
-                if (TRAIN && p.training && row_ok) p.drop.factor4(row, c0 + j, p.H, keep);
+                if (TRAIN && p.training && row_ok) p.drop.factor4(row, n0 + c0 + j, p.H, keep);
                 const float4 bb = *reinterpret_cast<const float4 *>(&b1s[c0 + j]);
                 const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
@@ -262,14 +285,14 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         if (et == 0) TRACE(5);
 
         // ---- coalesced copy of this warp's rows x columns of a bf16 tile held in a_stage to a global [B, H] matrix
-        const int npieces = p.H >> 4;                    // 16-byte pieces per row in this warp's column half (4, 8 or 16)
+        const int npieces = p.BN >> 4;                   // 16-byte pieces per row in this warp's column half (4, 8 or 16)
         const int np_shift = 31 - __clz(npieces);
         auto copy_out = [&](__nv_bfloat16 *dst, const uint8_t *tile) {
             for (int idx = lane; idx < 32 * npieces; idx += 32) {
                 const int rr = q * 32 + (idx >> np_shift);
                 const int pc = half * npieces + (idx & (npieces - 1));   // piece index within the full row
                 const uint4 t = *reinterpret_cast<const uint4 *>(tile + (size_t)(pc >> 3) * a_bytes + (size_t)rr * 128 + (((pc & 7) ^ (rr & 7)) << 4));
-                if ((int64_t)m0 + rr < p.B) *reinterpret_cast<uint4 *>(dst + ((int64_t)m0 + rr) * p.H + pc * 8) = t;
+                if ((int64_t)m0 + rr < p.B) *reinterpret_cast<uint4 *>(dst + ((int64_t)m0 + rr) * p.H + n0 + pc * 8) = t;
             }
         };
         if (TRAIN && p.A_out != nullptr) {
@@ -293,6 +316,30 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             if (et == 0) TRACE(8);
             float z[CP];
             tmem_ld16(t_lane + (uint32_t)kZCol, z);
+            if (ns > 1) {
+                // every CTA holds the logits of its slice of the hidden units only: all-gather the partial logits
+                // through distributed shared memory, then every CTA adds them up in the same (rank) order
+                const uint32_t mine = smem_u32(zbuf + ((size_t)rank * BM + r_local) * CP);
+                for (int t = 0; t < ns; ++t) {
+                    const uint32_t dst = map_to_rank(mine, (uint32_t)t);
+#pragma unroll
+                    for (int c = 0; c < CP; c += 4) st_cluster_v4(dst + c * 4, z[c], z[c + 1], z[c + 2], z[c + 3]);
+                }
+                if (et == 0) TRACE(14);
+                cluster_arrive();
+                cluster_wait();
+                if (et == 0) TRACE(15);
+#pragma unroll
+                for (int c = 0; c < CP; ++c) z[c] = 0.0f;
+                for (int t = 0; t < ns; ++t) {
+                    const float4 *src = reinterpret_cast<const float4 *>(zbuf + ((size_t)t * BM + r_local) * CP);
+#pragma unroll
+                    for (int c = 0; c < CP; c += 4) {
+                        const float4 v4 = src[c >> 2];
+                        z[c] += v4.x; z[c + 1] += v4.y; z[c + 2] += v4.z; z[c + 3] += v4.w;
+                    }
+                }
+            }
 #pragma unroll
             for (int c = 0; c < CP; ++c) z[c] = (c < p.C) ? z[c] + b2v[c] : 0.0f;
             float mx = z[0];
@@ -314,7 +361,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             if (yy < 0 || yy >= p.C) row_loss = __int_as_float(0x7fc00000);
             loss_acc = row_ok ? row_loss : 0.0f;
             corr_acc = (row_ok && arg == yy) ? 1 : 0;
-            if (row_ok) p.pred[row] = arg;
+            if (row_ok && rank == 0) p.pred[row] = arg;
 
             if (TRAIN) {
                 const float inv_B = 1.0f / (float)p.B;
@@ -322,20 +369,15 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 #pragma unroll
                 for (int c = 0; c < CP; ++c)
                     dzv[c] = (c < p.C && row_ok) ? (e[c] * inv_sum - (c == yy ? 1.0f : 0.0f)) * inv_B : 0.0f;
-                if (p.dz != nullptr && row_ok) {
+                if (p.dz != nullptr && row_ok && rank == 0) {
 #pragma unroll
                     for (int c = 0; c < CP; ++c)
                         if (c < p.C) p.dz[row * p.C + c] = dzv[c];
                 }
-                if (p.w2_partial != nullptr) {
-                    // db2[c] = sum_r dz[r, c]: warp shuffle, then the four quarters through shared memory
+                float db2v[CP];
 #pragma unroll
-                    for (int c = 0; c < CP; ++c) {
-                        const float t = warp_sum(dzv[c]);
-                        if (lane == 0) s_db2[q][c] = t;
-                    }
-                    dzv[CP - 1] = row_ok ? 1.0f : 0.0f;      // the "ones" column that turns dH^T dZ' into column sums of dH
-                }
+                for (int c = 0; c < CP; ++c) db2v[c] = dzv[c];
+                if (p.w2_partial != nullptr) dzv[CP - 1] = row_ok ? 1.0f : 0.0f;   // the "ones" column that turns dH^T dZ' into column sums of dH
                 // dZ tile: K-major, 16 bf16 (two 16-byte chunks) per row
                 uint8_t *drow = dz_tile + (size_t)r_local * 128;
                 uint4 c0v, c1v;
@@ -349,11 +391,17 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 tc_fence_before();
                 mbar_arrive(&dz_ready_bar);
                 if (et == 0) TRACE(9);
+                if (p.w2_partial != nullptr && rank == 0) {
+                    // db2[c] = sum_r dz[r, c] (fp32), off the critical path: the dA MMA is already running
+#pragma unroll
+                    for (int c = 0; c < CP; ++c) {
+                        const float t = warp_sum(db2v[c]);
+                        if (lane == 0) s_db2[q][c] = t;
+                    }
+                }
             }
-        } else if (TRAIN) {
-            // the other half of the warps must not overwrite the A tile before the logits MMA has read it
-            if (elect_one()) mbar_wait(&z_full_bar, 0);
-            __syncwarp();
+        } else if (ns > 1) {
+            cluster_arrive();                            // phase 1: nothing to exchange from these warps
         }
 
         if (TRAIN) {
@@ -395,41 +443,41 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 if (elect_one()) mbar_wait(&g_full_bar, 0);
                 __syncwarp();
                 tc_fence_after();
-                if (half < p.H / 128) {
-                    const int h = half * 128 + r_local;
+                if (half * 128 + r_local < p.BN) {
+                    const int h = n0 + half * 128 + r_local;
                     float gw[CP], gb[CP];
                     tmem_ld16(t_lane + (uint32_t)(kGCol + 16 * half), gw);
                     tmem_ld16(t_lane + (uint32_t)(kGCol + 32 + 16 * half), gb);
-                    float *wp = p.w2_partial + (int64_t)blockIdx.x * p.w2_stride + h;
+                    float *wp = p.w2_partial + (int64_t)slab * p.w2_stride + h;
 #pragma unroll
                     for (int c = 0; c < CP; ++c)
                         if (c < p.C) wp[(int64_t)c * p.H] = gw[c];
-                    p.b1_partial[(int64_t)blockIdx.x * p.b1_stride + h] = gb[CP - 1];
+                    p.b1_partial[(int64_t)slab * p.b1_stride + h] = gb[CP - 1];
                 }
             }
         }
         if (et == 0) TRACE(12);
 
         // ---- loss sum / correct count: warp -> CTA -> grid (last CTA finalises in a fixed order)
-        if (half == 0) {
+        if (half == 0 && rank == 0) {
             loss_acc = warp_sum(loss_acc);
             corr_acc = warp_sum(corr_acc);
             if (lane == 0) { s_loss[q] = loss_acc; s_corr[q] = corr_acc; }
             named_bar_sync(2, 128);
             if (TRAIN && p.w2_partial != nullptr && q == 0 && lane < p.C)      // s_db2 was filled before this barrier
-                p.b2_partial[(int64_t)blockIdx.x * p.b2_stride + lane] = (s_db2[0][lane] + s_db2[1][lane]) + (s_db2[2][lane] + s_db2[3][lane]);
+                p.b2_partial[(int64_t)slab * p.b2_stride + lane] = (s_db2[0][lane] + s_db2[1][lane]) + (s_db2[2][lane] + s_db2[3][lane]);
             if (q == 3 && lane == 0) {
-                p.partials[blockIdx.x].loss_sum = s_loss[0] + s_loss[1] + s_loss[2] + s_loss[3];
-                p.partials[blockIdx.x].correct = s_corr[0] + s_corr[1] + s_corr[2] + s_corr[3];
+                p.partials[slab].loss_sum = s_loss[0] + s_loss[1] + s_loss[2] + s_loss[3];
+                p.partials[slab].correct = s_corr[0] + s_corr[1] + s_corr[2] + s_corr[3];
                 __threadfence();
-                s_last = (atomicAdd(p.ticket, 1u) == gridDim.x - 1);
+                s_last = (atomicAdd(p.ticket, 1u) == gridDim.x / ns - 1);
             }
             named_bar_sync(2, 128);
             if (s_last && q == 3) {
                 __threadfence();
                 float l = 0.0f;
                 int c = 0;
-                for (int b = lane; b < (int)gridDim.x; b += 32) {
+                for (int b = lane; b < (int)gridDim.x / ns; b += 32) {
                     const volatile HeadPartial *hp = p.partials + b;
                     l += hp->loss_sum;
                     c += hp->correct;
@@ -447,6 +495,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         }
     }
     __syncwarp();
+    if (ns > 1 && (warp < 3 || ((warp - 3) >> 2) == 1)) cluster_wait();   // complete phase 1 for the warps that only arrived
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -465,22 +514,35 @@ int read_fused_trace(unsigned long long *out_host) {
 
 bool fused_mlp_supported(int D, int H, int C) { return (H == 64 || H == 128 || H == 256) && C >= 1 && C <= CP && D % 8 == 0; }
 
-int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st) {
+int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     TS_REQUIRE(fused_mlp_supported(a.D, a.H, a.C), TS_E_UNSUPPORTED, "fused MLP kernel: unsupported shape D=%d H=%d C=%d", a.D, a.H, a.C);
     TS_REQUIRE(a.B >= 1, TS_E_INVALID, "fused MLP kernel: batch %lld", (long long)a.B);
     FusedParams p{};
     p.B = (int)a.B; p.D = a.D; p.H = a.H; p.C = a.C;
+    const int slabs = (int)((a.B + BM - 1) / BM);
+    TS_REQUIRE(slabs <= kMaxHeadBlocks, TS_E_TOO_LARGE, "fused MLP kernel: batch %lld needs %d row slabs, more than the %d partial slots",
+               (long long)a.B, slabs, kMaxHeadBlocks);
+    // Split the hidden width of each 128-row slab over a cluster of ns CTAs while the whole grid still fits in one
+    // wave: small batches would otherwise leave most SMs idle (batch 4096 = 32 slabs -> 4 x 32 = 128 CTAs).
+    p.ns = 1;
+    if (const char *f = getenv("TSB_FUSED_NS")) p.ns = atoi(f);
+    else
+        for (int ns = 4; ns >= 2; ns >>= 1)
+            if (a.H / ns >= KATOM && slabs * ns <= sm_count) { p.ns = ns; break; }
+    TS_REQUIRE(p.ns == 1 || p.ns == 2 || p.ns == 4, TS_E_INVALID, "cluster size %d", p.ns);
+    TS_REQUIRE(a.H / p.ns >= KATOM, TS_E_INVALID, "cluster size %d leaves fewer than 64 hidden columns per CTA", p.ns);
+    p.BN = a.H / p.ns;
     p.num_kblocks = (a.D + KATOM - 1) / KATOM;
-    p.b_bytes = (uint32_t)a.H * 128u;
+    p.b_bytes = (uint32_t)p.BN * 128u;
     const uint32_t stage = BM * 128 + p.b_bytes;
-    const int atoms = a.H / KATOM;
+    const int atoms = p.BN / KATOM;
     const uint32_t alias_need = 2u * (uint32_t)atoms * BM * 128 + BM * 128;   // A tile + dH tile + dZ tile reuse the stage memory
-    p.stages = (int)((190u * 1024u) / stage);
+    p.stages = (int)((160u * 1024u) / stage);
     if (p.stages > kMaxStages) p.stages = kMaxStages;
     while ((uint32_t)p.stages * stage < alias_need) ++p.stages;
-    p.idesc_main = make_idesc(BM, a.H, TC_MAJOR_K, TC_MAJOR_K);
+    p.idesc_main = make_idesc(BM, p.BN, TC_MAJOR_K, TC_MAJOR_K);
     p.idesc_z = make_idesc(BM, CP, TC_MAJOR_K, TC_MAJOR_K);
-    p.idesc_da = make_idesc(BM, a.H, TC_MAJOR_K, TC_MAJOR_MN);
+    p.idesc_da = make_idesc(BM, p.BN, TC_MAJOR_K, TC_MAJOR_MN);
     p.idesc_g = make_idesc(BM, CP, TC_MAJOR_MN, TC_MAJOR_MN);
     const bool fuse_grads = a.w2_partial != nullptr;
     TS_REQUIRE(!fuse_grads || (a.H >= 128 && a.C < CP && a.b1_partial && a.b2_partial), TS_E_INVALID,
@@ -494,16 +556,14 @@ int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st) {
     CUtensorMap mx, mw1, mw2;
     int rc = get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, BM, &mx);
     if (rc) return rc;
-    rc = get_map(a.W1, (uint64_t)a.D, (uint64_t)a.H, (uint64_t)a.D, KATOM, (uint32_t)a.H, &mw1);
+    rc = get_map(a.W1, (uint64_t)a.D, (uint64_t)a.H, (uint64_t)a.D, KATOM, (uint32_t)p.BN, &mw1);
     if (rc) return rc;
     rc = get_map(a.W2p, (uint64_t)a.H, (uint64_t)CP, (uint64_t)a.H, KATOM, CP, &mw2);
     if (rc) return rc;
 
-    const int grid = (int)((a.B + BM - 1) / BM);
-    TS_REQUIRE(grid <= kMaxHeadBlocks, TS_E_TOO_LARGE, "fused MLP kernel: batch %lld needs %d CTAs, more than the %d partial slots",
-               (long long)a.B, grid, kMaxHeadBlocks);
-    const size_t smem = (size_t)p.stages * stage + (size_t)atoms * 2048 + (size_t)a.H * 4 + 1024 + 64;
-    const bool train = a.dH_out != nullptr || a.dz != nullptr;
+    const size_t smem = (size_t)p.stages * stage + (size_t)atoms * 2048 + (size_t)p.BN * 4 +
+                        (p.ns > 1 ? (size_t)p.ns * BM * CP * 4 : 0) + 1024 + 64;
+    const bool train = a.dH_out != nullptr;
     static bool attr_set[2][64] = {{false}};
     int dev = 0;
     TS_CUDA_CHECK(cudaGetDevice(&dev));
@@ -512,8 +572,20 @@ int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st) {
         else TS_CUDA_CHECK(cudaFuncSetAttribute(fused_mlp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_set[train][dev & 63] = true;
     }
-    if (train) fused_mlp_kernel<true><<<grid, kThreads, smem, st>>>(mx, mw1, mw2, p);
-    else fused_mlp_kernel<false><<<grid, kThreads, smem, st>>>(mx, mw1, mw2, p);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(slabs * p.ns));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)p.ns;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (train) TS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, fused_mlp_kernel<true>, mx, mw1, mw2, p));
+    else TS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, fused_mlp_kernel<false>, mx, mw1, mw2, p));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }

@@ -159,7 +159,7 @@ struct FusedMlpArgs {
 };
 bool fused_mlp_supported(int D, int H, int C);
 inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }
-int launch_fused_mlp(const FusedMlpArgs &a, cudaStream_t st);
+int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st);
 int read_fused_trace(unsigned long long *out_host);   // 32 clock64 samples of CTA 0 of the last launch
 
 }  // namespace tsb
