@@ -161,7 +161,19 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
-        dist.init_process_group('nccl', device_id=dev)
+        # keep stdout to the single JSON line: NCCL prints its version banner there on first use
+        os.environ.setdefault('NCCL_DEBUG', 'WARN')
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group('nccl', device_id=dev)
+            dist.all_reduce(torch.zeros(1, device=dev))
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     n = args.batches * BATCH
     g = torch.Generator(device=dev).manual_seed(1234 + rank)

@@ -1,0 +1,82 @@
+"""Data-parallel path on real GPUs (needs >= 2 devices; skipped otherwise): two ranks over NCCL, each fitting its half
+of every global batch through B200Classifier (dp_mode 'p2p': gradient sum inside the optimizer kernel over peer
+mappings; 'nccl': ts_fit_backward -> all-reduce -> ts_opt_apply), must reproduce the single-process oracle fed the full batch;
+B200Metrics.compute() sums the counters of both ranks."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, precision, dp_mode, out):
+    import torch.distributed as dist
+    from torch import nn
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+    from torchsystem_b200 import B200Classifier, B200Metrics, MLP
+    from tests.test_gpu_parity import synthetic, seeded_init
+    dims, B = [784, 256, 10], 1024
+    x, y = synthetic(B * 3)
+    if precision == 'bf16':
+        x = x.bfloat16().float()
+    init = seeded_init(dims, seed=rank, bf16=precision == 'bf16')      # different per rank: the broadcast must fix it
+    net = MLP(784, 256, 10, dropout=0.0, activation=nn.ReLU())
+    with torch.no_grad():
+        for p, w in zip([q for lin in net.linears() for q in (lin.weight, lin.bias)], init):
+            p.copy_(torch.from_numpy(w))
+    model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
+                           device=f'cuda:{rank}', max_batch=B, dp_mode=dp_mode)
+    assert (model._p2p is not None) == (dp_mode == 'p2p')
+    metrics = B200Metrics(device=f'cuda:{rank}', log_every=0)
+    half = B // world
+    for s in range(3):
+        lo = s * B + rank * half
+        xb, yb = x[lo:lo + half].cuda(), y[lo:lo + half].cuda()
+        p, l = model.fit(xb, yb)
+        metrics.update(s + 1, l, p, yb)
+    counters = metrics.counters()
+    if rank == 0:
+        np.savez(out, *[q.detach().cpu().numpy() for lin in net.linears() for q in (lin.weight, lin.bias)],
+                 counters=np.array(counters, dtype=np.float64))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
+@pytest.mark.parametrize('dp_mode', ['p2p', 'nccl'])
+@pytest.mark.parametrize('precision,tol', [('f32', 1e-5), ('bf16', 1e-2)])
+def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, tol, dp_mode):
+    import torch.multiprocessing as mp
+    from oracle import mlp_numpy as onp
+    from tests.test_gpu_parity import synthetic, seeded_init
+    from tests.golden_util import assert_params_close
+    out = str(tmp_path / 'rank0.npz')
+    mp.spawn(_worker, args=(2, _free_port(), precision, dp_mode, out), nprocs=2, join=True)
+    dims, B = [784, 256, 10], 1024
+    x, y = synthetic(B * 3)
+    if precision == 'bf16':
+        x = x.bfloat16().float()
+    init = seeded_init(dims, seed=0, bf16=precision == 'bf16')
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=precision == 'bf16')
+    correct, total = 0, 0
+    for s in range(3):
+        xb, yb = x[s * B:(s + 1) * B].numpy(), y[s * B:(s + 1) * B].numpy()
+        p, _ = oracle.evaluate(xb, yb)
+        correct += int((p == yb).sum()); total += B
+        oracle.fit(xb, yb, None)
+    got = np.load(out)
+    assert_params_close([got[f'arr_{i}'] for i in range(4)], oracle.parameters(), tol, adam=False)
+    loss_sum, n_batches, n_correct, n_total = got['counters']
+    assert (n_batches, n_total) == (6, total)
+    assert abs(n_correct - correct) <= (0 if precision == 'f32' else 3)

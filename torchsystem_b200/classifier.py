@@ -49,10 +49,13 @@ class B200Classifier(Aggregate):
     precision   'bf16' (tcgen05 tensor cores, fp32 accumulate; parity 1e-2) or 'f32' (SIMT; parity 1e-5)
     dropout_seed  key of the in-kernel Philox dropout masks (pass `masks=` to `fit` to supply them instead)
     process_group  torch.distributed group for data-parallel training (default: the world, if initialised)
+    dp_mode     'p2p': every rank's optimizer kernel reads all ranks' gradients over NVLink peer mappings (no separate
+                collective); 'nccl': ts_fit_backward -> NCCL all-reduce -> ts_opt_apply
     """
 
     def __init__(self, nn: nn.Module, criterion: nn.Module, optimizer: torch.optim.Optimizer, *, precision: str = 'bf16',
-                 device: str | torch.device = 'cuda', max_batch: int = 4096, dropout_seed: int = 42, process_group=None):
+                 device: str | torch.device = 'cuda', max_batch: int = 4096, dropout_seed: int = 42, process_group=None,
+                 dp_mode: str = 'p2p'):
         super().__init__()
         _check_criterion(criterion)
         spec = inspect_mlp(nn)
@@ -77,9 +80,12 @@ class B200Classifier(Aggregate):
         step = self._adopt_optimizer_state(kind)
         self.engine.bind_optimizer(kind, step=step, **hyper)
         self._dp = parallel.DataParallel(process_group)
+        self._p2p = None
         if self._dp.world > 1:
             self._dp.broadcast_(self.engine.params)          # same initial weights on every rank
             self.engine.sync_weights()
+            if dp_mode == 'p2p':
+                self._p2p = parallel.bind_peer_gradients(self.engine, self._params, self._dp)
 
     # ------------------------------------------------------------------ identity / hooks
     @property
@@ -141,6 +147,8 @@ class B200Classifier(Aggregate):
             self._refresh_hyper()
         if self._dp.world == 1:
             return self.engine.fit(inputs, targets, masks, self.dropout_seed)
+        if self._p2p is not None:      # gradient all-reduce folded into the optimizer kernel over NVLink peer mappings
+            return self.engine.fit(inputs, targets, masks, self.dropout_seed + self._dp.rank)
         out = self.engine.fit(inputs, targets, masks, self.dropout_seed + self._dp.rank, update=False)
         self._dp.all_reduce_sum_(self.engine.grads)
         self.engine.apply(1.0 / self._dp.world)

@@ -89,6 +89,11 @@ struct ts_mlp {
     int64_t shadow_total = 0;
     bool fused = false;                     // one hidden layer of a width the fused kernel takes
 
+    // data parallel over peer-mapped memory (ts_dp_bind)
+    int dp_world = 1, dp_rank = 0;
+    float *dp_grads[2][kMaxRanks] = {{nullptr}};
+    uint32_t *dp_flags[kMaxRanks] = {nullptr};
+
     int hidden_layers() const { return n_layers - 1; }
     int classes() const { return dims[n_layers]; }
     size_t elem() const { return prec == TS_PREC_BF16 ? 2 : 4; }
@@ -302,6 +307,35 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     return launch_fused_mlp(f, m->sm_count, st);
 }
 
+// Data-parallel update: the cross-rank gradient sum happens inside the optimizer kernel, over peer mappings.
+int run_dp_optimizer(ts_mlp *m, cudaStream_t st) {
+    OptArgs o{};
+    o.n_tensors = m->n_tensors;
+    for (int t = 0; t < m->n_tensors; ++t) {
+        o.t[t].offset = m->off[t]; o.t[t].count = m->cnt[t];
+        o.t[t].shadow_off = (m->prec == TS_PREC_BF16 && t % 2 == 0) ? m->shadow_off[t / 2] : -1;
+        o.t[t].nsplit = 0;
+    }
+    o.params = m->params; o.grads = m->grads; o.exp_avg = m->exp_avg; o.exp_avg_sq = m->exp_avg_sq;
+    o.partials = m->partials; o.shadow = m->shadow; o.chunk_tensor = m->d_chunk_tensor;
+    o.kind = m->opt_kind; o.update = 1; o.grad_scale = 1.0f / (float)m->dp_world;
+    const int parity = (int)(m->step & 1);
+    m->step += 1;
+    const double b1 = m->hyper.beta1, b2 = m->hyper.beta2;
+    o.lr = (float)m->hyper.lr;
+    o.beta1 = (float)b1; o.beta2 = (float)b2; o.eps = (float)m->hyper.eps;
+    o.one_minus_beta1 = (float)(1.0 - b1); o.one_minus_beta2 = (float)(1.0 - b2);
+    if (m->opt_kind == TS_OPT_ADAM) {
+        o.step_size = (float)(m->hyper.lr / (1.0 - pow(b1, (double)m->step)));
+        o.bc2_sqrt = (float)sqrt(1.0 - pow(b2, (double)m->step));
+    }
+    DpArgs dp{};
+    dp.world = m->dp_world; dp.rank = m->dp_rank; dp.step = (uint32_t)m->step;
+    for (int r = 0; r < m->dp_world; ++r) { dp.grads[r] = m->dp_grads[parity][r]; dp.flags[r] = m->dp_flags[r]; }
+    ProfScope ps(K_OPT, st);
+    return launch_dp_optimizer(o, dp, m->n_chunks, st);
+}
+
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
              uint64_t seed, int64_t *pred, ts_batch_record *rec, cudaStream_t st, bool update) {
     int rc = check_ready(m, B, update);
@@ -310,6 +344,8 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     TS_CUDA_CHECK(cudaSetDevice(m->device));
     const int L = m->n_layers;
     const bool bf16 = m->prec == TS_PREC_BF16;
+    const bool dp = m->dp_world > 1 && update;
+    if (dp) m->grads = m->dp_grads[m->step & 1][m->dp_rank];     // this step's peer-visible gradient buffer
     const void *a0 = nullptr, *a_last = nullptr;
     if (m->fused) {
         rc = fused_forward(m, x, x_dtype, y, B, masks, seed, true, pred, rec, &a0, st);
@@ -420,7 +456,10 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
             cur ^= 1;
         }
     }
-    return run_optimizer(m, nsplit, update, 1.0f, st);
+    if (!dp) return run_optimizer(m, nsplit, update, 1.0f, st);
+    rc = run_optimizer(m, nsplit, false, 1.0f, st);          // fold the split partials into this rank's gradient
+    if (rc) return rc;
+    return run_dp_optimizer(m, st);
 }
 
 }  // namespace
@@ -522,6 +561,25 @@ int32_t ts_opt_bind(ts_mlp *m, int32_t kind, const ts_opt_hyper *hyper, float *e
 }
 
 int64_t ts_opt_step_count(const ts_mlp *m) { return m ? m->step : -1; }
+
+int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bufs, uint32_t *const *flag_bufs) {
+    TS_REQUIRE(m && grad_bufs && flag_bufs, TS_E_INVALID, "null argument");
+    TS_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, TS_E_INVALID, "rank %d of %d (at most %d ranks)", rank,
+               world, kMaxRanks);
+    for (int b = 0; b < 2; ++b)
+        for (int r = 0; r < world; ++r) {
+            TS_REQUIRE(grad_bufs[b * world + r] != nullptr && ((uintptr_t)grad_bufs[b * world + r] % 16) == 0, TS_E_INVALID,
+                       "gradient buffer %d of rank %d is null or not 16-byte aligned", b, r);
+            m->dp_grads[b][r] = grad_bufs[b * world + r];
+        }
+    for (int r = 0; r < world; ++r) {
+        TS_REQUIRE(flag_bufs[r] != nullptr, TS_E_INVALID, "flag array of rank %d is null", r);
+        m->dp_flags[r] = flag_bufs[r];
+    }
+    m->dp_world = world;
+    m->dp_rank = rank;
+    return TS_OK;
+}
 
 int64_t ts_mlp_workspace_bytes(const ts_mlp *m, int64_t max_batch) {
     if (!m || max_batch < 1) { set_error("ts_mlp_workspace_bytes: bad argument"); return TS_E_INVALID; }

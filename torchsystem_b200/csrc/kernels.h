@@ -98,6 +98,16 @@ struct OptArgs {
 };
 int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st);
 
+// data parallel: peer-mapped gradient buffers and flag arrays of every rank (this step's parity)
+constexpr int kMaxRanks = 8;
+struct DpArgs {
+    const float *grads[kMaxRanks];   // rank r's reduced gradient (flat layout), readable from this GPU
+    uint32_t *flags[kMaxRanks];      // rank r's flag array: entry q = last step whose gradient rank q has published
+    int world, rank;
+    uint32_t step;
+};
+int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cudaStream_t st);
+
 int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st);
 
 // ---------------------------------------------------------------- metrics

@@ -514,6 +514,29 @@ int launch_colsum(const void *X, int is_bf16, int64_t B, int H, float *partial, 
 // CPU path does (torch/optim/adam.py _single_tensor_adam, sgd.py _single_tensor_sgd), and
 // refreshes the bf16 shadow of weight matrices.
 // =====================================================================================
+// SGD / Adam on up to four consecutive elements, exactly as torch's single-tensor CPU path orders the operations.
+__device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc &d, int64_t i0, int64_t j0, int n, const float (&g)[4]) {
+    for (int e = 0; e < n; ++e) {
+        const int64_t i = i0 + e;
+        const float grad = g[e] * p.grad_scale;
+        float w = p.params[i];
+        if (p.kind == TS_OPT_SGD) {
+            w = w - p.lr * grad;                                   // param.add_(grad, alpha=-lr)
+        } else {
+            float m = p.exp_avg[i], v = p.exp_avg_sq[i];
+            m = m + p.one_minus_beta1 * (grad - m);                // exp_avg.lerp_(grad, 1 - beta1)
+            v = v * p.beta2;                                       // exp_avg_sq.mul_(beta2)
+            v = v + p.one_minus_beta2 * (grad * grad);             //   .addcmul_(grad, grad, value=1 - beta2)
+            const float denom = sqrtf(v) / p.bc2_sqrt + p.eps;     // (sqrt(v) / sqrt(bias_correction2)).add_(eps)
+            w = w - p.step_size * (m / denom);                     // param.addcdiv_(exp_avg, denom, value=-step_size)
+            p.exp_avg[i] = m;
+            p.exp_avg_sq[i] = v;
+        }
+        p.params[i] = w;
+        if (d.shadow_off >= 0 && p.shadow != nullptr) p.shadow[d.shadow_off + j0 + e] = __float2bfloat16_rn(w);
+    }
+}
+
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
     const int tix = p.chunk_tensor[blockIdx.x];
     if (tix < 0) return;
@@ -552,26 +575,59 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
         for (int e = 0; e < n; ++e) g[e] = p.grads[i0 + e];
     }
     if (!p.update) return;
+    apply_update(p, d, i0, j0, n, g);
+}
 
-    for (int e = 0; e < n; ++e) {
-        const int64_t i = i0 + e;
-        const float grad = g[e] * p.grad_scale;
-        float w = p.params[i];
-        if (p.kind == TS_OPT_SGD) {
-            w = w - p.lr * grad;                                   // param.add_(grad, alpha=-lr)
-        } else {
-            float m = p.exp_avg[i], v = p.exp_avg_sq[i];
-            m = m + p.one_minus_beta1 * (grad - m);                // exp_avg.lerp_(grad, 1 - beta1)
-            v = v * p.beta2;                                       // exp_avg_sq.mul_(beta2)
-            v = v + p.one_minus_beta2 * (grad * grad);             //   .addcmul_(grad, grad, value=1 - beta2)
-            const float denom = sqrtf(v) / p.bc2_sqrt + p.eps;     // (sqrt(v) / sqrt(bias_correction2)).add_(eps)
-            w = w - p.step_size * (m / denom);                     // param.addcdiv_(exp_avg, denom, value=-step_size)
-            p.exp_avg[i] = m;
-            p.exp_avg_sq[i] = v;
-        }
-        p.params[i] = w;
-        if (d.shadow_off >= 0 && p.shadow != nullptr) p.shadow[d.shadow_off + j0 + e] = __float2bfloat16_rn(w);
+// =====================================================================================
+// Data-parallel optimizer with the gradient all-reduce folded in (no separate collective). Every rank keeps its
+// reduced local gradient in a peer-mapped buffer (NVLink / NVSwitch); this kernel
+//   1. publishes "my gradient of step s is complete" by storing s into every rank's flag array (release, system scope),
+//   2. waits until the local flag array shows step s for every rank,
+//   3. reads the same chunk of all `world` gradient buffers straight over the peer mappings, sums them in rank
+//      order (identical order on every rank -> bit-identical replicas), scales by 1/world and applies SGD / Adam.
+// One-shot (every rank reads everything) is the right shape here: the whole gradient is well under 1 MB, so latency,
+// not bandwidth, is what the step pays. Buffers alternate with the step parity, so nobody overwrites a gradient a
+// peer may still be reading (a rank passes step s+1's wait only after every peer finished reading step s).
+// =====================================================================================
+__global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp) {
+    if (blockIdx.x == 0 && threadIdx.x < dp.world) {
+        __threadfence_system();                                   // the gradient written by the previous kernel is visible system-wide
+        volatile uint32_t *peer_flag = dp.flags[threadIdx.x] + dp.rank;
+        *peer_flag = dp.step;
     }
+    if (threadIdx.x < dp.world) {
+        const volatile uint32_t *mine = dp.flags[dp.rank] + threadIdx.x;
+        uint32_t spins = 0;
+        while ((int32_t)(*mine - dp.step) < 0) {
+            __nanosleep(64);
+            if (++spins > (1u << 25)) __trap();                  // a peer never arrived: fail loudly instead of hanging
+        }
+        __threadfence_system();
+    }
+    __syncthreads();
+
+    const int tix = p.chunk_tensor[blockIdx.x];
+    if (tix < 0) return;
+    const TensorDesc d = p.t[tix];
+    const int64_t i0 = (int64_t)blockIdx.x * kChunk + threadIdx.x * 4;
+    const int64_t j0 = i0 - d.offset;
+    if (j0 >= d.count) return;
+    const int n = (int)min((int64_t)4, d.count - j0);
+    float4 v[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)       // flat buffers are padded to whole chunks: the float4 is always in bounds
+        v[r] = (r < dp.world) ? __ldcv(reinterpret_cast<const float4 *>(dp.grads[r] + i0)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+        if (r < dp.world) { g[0] += v[r].x; g[1] += v[r].y; g[2] += v[r].z; g[3] += v[r].w; }
+    apply_update(p, d, i0, j0, n, g);
+}
+
+int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cudaStream_t st) {
+    dp_optimizer_kernel<<<(unsigned)n_chunks, 256, 0, st>>>(a, dp);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
 }
 
 int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st) {

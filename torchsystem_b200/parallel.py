@@ -43,3 +43,33 @@ class DataParallel:
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         v = t.tolist()
         return v[0], int(v[1]), int(v[2]), int(v[3])
+
+
+def bind_peer_gradients(engine, params, dp: DataParallel):
+    """Put the flat gradient buffers (two, alternating with the step parity) and a small flag array into torch
+    symmetric memory, exchange the peer mappings and hand them to the library (ts_dp_bind). Returns the objects
+    that must stay alive, or raises if the GPUs cannot map each other's memory."""
+    import ctypes as C
+    import torch.distributed._symmetric_memory as symm
+    from ._lib import lib, check
+    group = dp.group if dp.group is not None else dist.group.WORLD
+    dev, total = engine.device, engine.total
+    with torch.cuda.device(engine.index):
+        gbuf = symm.empty(2 * total, dtype=torch.float32, device=dev)
+        flags = symm.empty(64, dtype=torch.int32, device=dev)
+        gbuf.zero_()
+        flags.zero_()
+        hg = symm.rendezvous(gbuf, group)
+        hf = symm.rendezvous(flags, group)
+        torch.cuda.synchronize(engine.index)
+    dist.barrier(group=dp.group)
+    world = dp.world
+    gptrs = (C.c_void_p * (2 * world))(*[hg.buffer_ptrs[r] + b * total * 4 for b in (0, 1) for r in range(world)])
+    fptrs = (C.c_void_p * world)(*[hf.buffer_ptrs[r] for r in range(world)])
+    check(lib.ts_dp_bind(engine.handle, dp.rank, world, gptrs, fptrs), 'ts_dp_bind')
+    # param.grad keeps showing this rank's local mean gradient of even steps (buffer 0)
+    engine.grads = gbuf[:total]
+    for i, p in enumerate(params):
+        o, n = engine.offsets[i], p.numel()
+        p.grad = engine.grads[o:o + n].view(p.shape)
+    return gbuf, flags, hg, hf
