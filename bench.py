@@ -50,6 +50,7 @@ def parse():
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the cpu_baseline leg')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--skip-e2e', action='store_true', help='profiling runs only')
+    ap.add_argument('--skip-extras', action='store_true', help='skip the non-headline extra measurements')
     return ap.parse_args()
 
 
@@ -271,6 +272,35 @@ def main():
         'step_streaming_frac': step_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
     }
 
+    # ---- extras (not the headline): the same train step with the loader holding bf16 (what bf16 mode rounds the inputs
+    #      to anyway), and the validate handler at batch 65,536 (BASELINE.json configs[4]: HBM-bound evaluation)
+    extras = {}
+    if not args.skip_extras:
+        bf_loader = DeviceLoader(x, y, BATCH, device=dev, dtype=torch.bfloat16)
+        b_ms, _, _ = timed(bf_loader, args.steps, 2)
+        extras['train_bf16_resident_inputs'] = {'value': world * n * args.steps / (b_ms * 1e-3), 'unit': 'samples/s',
+                                                'note': 'DeviceLoader(dtype=bfloat16): no per-batch cast kernel, 1,584 B/sample streamed'}
+        del bf_loader
+        vb = 65536
+        val_loader = DeviceLoader(x, y, vb, device=dev)
+        results_v = []
+        def run_val():
+            training.service.handle('validate', model, val_loader, metrics); metrics.reset()
+        for _ in range(2):
+            run_val()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            run_val()
+        e1.record()
+        barrier()
+        v_ms = e0.elapsed_time(e1)
+        v_rate = n * args.steps / (v_ms * 1e-3)
+        extras['validate_batch65536'] = {'value': world * v_rate, 'unit': 'samples/s', 'per_gpu_streaming_gbs': v_rate * 3152 / 1e9,
+                                         'frac_of_hbm_peak': v_rate * 3152 / 1e9 / peak,
+                                         'note': 'validate handler (inference_mode, evaluate + fused metrics), fp32 inputs resident in HBM'}
+
     # ---- e2e: host buffers, H2D every step, result read back
     if args.skip_e2e:
         e2e = None
@@ -300,6 +330,7 @@ def main():
                        'parallelism': f'dp{world}', 'l2': f'inputs of one step ({n * 3136 / 1e9:.2f} GB per GPU) exceed the 126 MB L2',
                        'last_train_result': results[-1] if results else None},
             'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline, 'cpu_baseline': cpu,
+            'extras': extras,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -128,6 +128,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
     if (ns > 1) { cluster_arrive(); cluster_wait(); }          // every CTA of the cluster is running: its shared memory may be written
+    pdl_launch_dependents();
+    pdl_wait();          // the prologue above overlapped the predecessor's tail; global memory is touched from here on
     if (threadIdx.x == 0) TRACE(1);
 
     if (ns > 1 && warp < 3) cluster_arrive();                  // phase 1 (logit exchange): these warps only have to have arrived
@@ -572,20 +574,9 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
         else TS_CUDA_CHECK(cudaFuncSetAttribute(fused_mlp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_set[train][dev & 63] = true;
     }
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)(slabs * p.ns));
-    cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)p.ns;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    if (train) TS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, fused_mlp_kernel<true>, mx, mw1, mw2, p));
-    else TS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, fused_mlp_kernel<false>, mx, mw1, mw2, p));
+    const dim3 grid((unsigned)(slabs * p.ns));
+    if (train) TS_CUDA_CHECK(launch_pdl(fused_mlp_kernel<true>, grid, dim3(kThreads), smem, st, (unsigned)p.ns, mx, mw1, mw2, p));
+    else TS_CUDA_CHECK(launch_pdl(fused_mlp_kernel<false>, grid, dim3(kThreads), smem, st, (unsigned)p.ns, mx, mw1, mw2, p));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }

@@ -538,7 +538,9 @@ __device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc 
 }
 
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
-    const int tix = p.chunk_tensor[blockIdx.x];
+    pdl_launch_dependents();
+    const int tix = p.chunk_tensor[blockIdx.x];     // static map: may be read before the predecessor has finished
+    pdl_wait();
     if (tix < 0) return;
     const TensorDesc d = p.t[tix];
     const int64_t i0 = (int64_t)blockIdx.x * kChunk + threadIdx.x * 4;
@@ -590,6 +592,8 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
 // peer may still be reading (a rank passes step s+1's wait only after every peer finished reading step s).
 // =====================================================================================
 __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp) {
+    pdl_launch_dependents();
+    pdl_wait();
     if (blockIdx.x == 0 && threadIdx.x < dp.world) {
         __threadfence_system();                                   // the gradient written by the previous kernel is visible system-wide
         volatile uint32_t *peer_flag = dp.flags[threadIdx.x] + dp.rank;
@@ -625,19 +629,21 @@ __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp)
 }
 
 int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cudaStream_t st) {
-    dp_optimizer_kernel<<<(unsigned)n_chunks, 256, 0, st>>>(a, dp);
+    TS_CUDA_CHECK(launch_pdl(dp_optimizer_kernel, dim3((unsigned)n_chunks), dim3(256), 0, st, 1, a, dp));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
 
 int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st) {
-    optimizer_kernel<<<(unsigned)n_chunks, 256, 0, st>>>(a);
+    TS_CUDA_CHECK(launch_pdl(optimizer_kernel, dim3((unsigned)n_chunks), dim3(256), 0, st, 1, a));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
 
 // =====================================================================================
 __global__ void __launch_bounds__(256) cast_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int64_t n) {
+    pdl_launch_dependents();
+    pdl_wait();      // dst may still be read by a kernel of the previous step
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * 8;
     for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
         if (i + 8 <= n) {
@@ -657,7 +663,7 @@ int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream
     int64_t blocks = (n / 8 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     if (blocks < 1) blocks = 1;
-    cast_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, dst, n);
+    TS_CUDA_CHECK(launch_pdl(cast_bf16_kernel, dim3((unsigned)blocks), dim3(256), 0, st, 1, src, dst, n));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }

@@ -81,6 +81,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
+    pdl_launch_dependents();
+    pdl_wait();          // prologue above overlapped the predecessor's tail; operands and outputs are touched from here on
     if (dbg && threadIdx.x == 0) dbg[1] = clock64();
 
     if (warp == 0) {
@@ -382,7 +384,7 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
             TS_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024)); \
             attr_set[dev_ & 63] = true;                                                                             \
         }                                                                                                           \
-        tc_gemm_kernel<E><<<grid, kThreads, smem, st>>>(ma, mb, p);                                                 \
+        TS_CUDA_CHECK(launch_pdl(tc_gemm_kernel<E>, grid, dim3(kThreads), smem, st, 1, ma, mb, p));                 \
     } while (0)
     if (a.epi == TC_EPI_STORE_F32) TS_TC_LAUNCH(TC_EPI_STORE_F32);
     else if (a.epi == TC_EPI_FWD) TS_TC_LAUNCH(TC_EPI_FWD);
