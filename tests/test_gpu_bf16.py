@@ -89,3 +89,24 @@ def test_bf16_deep_net_and_bf16_inputs():
         assert (pr.cpu().numpy() != opr).mean() <= 2e-3
         assert l.item() == pytest.approx(float(ol), rel=1e-2)
     assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=1e-3, steps=2)
+
+
+def test_bf16_wide_hidden_layers_config4_shape_class():
+    """North-star config 4 shape class (wide hidden layers, generalised MLP) at a size the oracle finishes in seconds:
+    784 -> 1024 -> 1024 -> 10 exercises the 256-wide tcgen05 tiles, the MN-major dX / dW contractions without split-K
+    and the layer-by-layer path (the fused kernel only takes one hidden layer)."""
+    dims, p, B = [784, 1024, 1024, 10], 0.1, 1024
+    x, y = synthetic(B, seed=21)
+    x = x.bfloat16().float()
+    init = seeded_init(dims, bf16=True)
+    model, net = build_model(dims, p, 'relu', 'sgd', 0.05, init, 'bf16', max_batch=B)
+    assert not model.engine.spec.dims == [784, 256, 10]
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=True)
+    g = torch.Generator().manual_seed(5)
+    for s in range(2):
+        masks = [(torch.rand(B, h, generator=g) >= p).to(torch.uint8) for h in dims[1:-1]]
+        pr, l = model.fit(x.cuda(), y.cuda(), masks=[m.cuda() for m in masks])
+        opr, ol = oracle.fit(x.numpy(), y.numpy(), [m.numpy() for m in masks])
+        assert (pr.cpu().numpy() != opr).mean() <= 2e-3
+        assert l.item() == pytest.approx(float(ol), rel=1e-2)
+    assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=0.05, steps=2, adam=False)

@@ -516,24 +516,46 @@ int launch_colsum(const void *X, int is_bf16, int64_t B, int H, float *partial, 
 // =====================================================================================
 // SGD / Adam on up to four consecutive elements, exactly as torch's single-tensor CPU path orders the operations.
 __device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc &d, int64_t i0, int64_t j0, int n, const float (&g)[4]) {
-    for (int e = 0; e < n; ++e) {
-        const int64_t i = i0 + e;
+    // Whole float4 accesses (the flat buffers are padded to 1024-element chunks and i0 is a multiple of 4); all
+    // loads are issued before the first use, the padding lanes (e >= n) are written back unchanged.
+    const float4 w4 = *reinterpret_cast<const float4 *>(p.params + i0);
+    float4 m4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), v4 = m4;
+    const bool adam = p.kind != TS_OPT_SGD;
+    if (adam) {
+        m4 = *reinterpret_cast<const float4 *>(p.exp_avg + i0);
+        v4 = *reinterpret_cast<const float4 *>(p.exp_avg_sq + i0);
+    }
+    float w[4] = {w4.x, w4.y, w4.z, w4.w}, m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        if (e >= n) continue;
         const float grad = g[e] * p.grad_scale;
-        float w = p.params[i];
-        if (p.kind == TS_OPT_SGD) {
-            w = w - p.lr * grad;                                   // param.add_(grad, alpha=-lr)
+        if (!adam) {
+            w[e] = w[e] - p.lr * grad;                                     // param.add_(grad, alpha=-lr)
         } else {
-            float m = p.exp_avg[i], v = p.exp_avg_sq[i];
-            m = m + p.one_minus_beta1 * (grad - m);                // exp_avg.lerp_(grad, 1 - beta1)
-            v = v * p.beta2;                                       // exp_avg_sq.mul_(beta2)
-            v = v + p.one_minus_beta2 * (grad * grad);             //   .addcmul_(grad, grad, value=1 - beta2)
-            const float denom = sqrtf(v) / p.bc2_sqrt + p.eps;     // (sqrt(v) / sqrt(bias_correction2)).add_(eps)
-            w = w - p.step_size * (m / denom);                     // param.addcdiv_(exp_avg, denom, value=-step_size)
-            p.exp_avg[i] = m;
-            p.exp_avg_sq[i] = v;
+            m[e] = m[e] + p.one_minus_beta1 * (grad - m[e]);               // exp_avg.lerp_(grad, 1 - beta1)
+            v[e] = v[e] * p.beta2;                                         // exp_avg_sq.mul_(beta2)
+            v[e] = v[e] + p.one_minus_beta2 * (grad * grad);               //   .addcmul_(grad, grad, value=1 - beta2)
+            const float denom = sqrtf(v[e]) / p.bc2_sqrt + p.eps;          // (sqrt(v) / sqrt(bias_correction2)).add_(eps)
+            w[e] = w[e] - p.step_size * (m[e] / denom);                    // param.addcdiv_(exp_avg, denom, value=-step_size)
         }
-        p.params[i] = w;
-        if (d.shadow_off >= 0 && p.shadow != nullptr) p.shadow[d.shadow_off + j0 + e] = __float2bfloat16_rn(w);
+    }
+    *reinterpret_cast<float4 *>(p.params + i0) = make_float4(w[0], w[1], w[2], w[3]);
+    if (adam) {
+        *reinterpret_cast<float4 *>(p.exp_avg + i0) = make_float4(m[0], m[1], m[2], m[3]);
+        *reinterpret_cast<float4 *>(p.exp_avg_sq + i0) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    if (d.shadow_off >= 0 && p.shadow != nullptr) {
+        __nv_bfloat16 *sh = p.shadow + d.shadow_off + j0;
+        if (n == 4 && (((uintptr_t)sh) & 7) == 0) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(w[0], w[1]), hi = __floats2bfloat162_rn(w[2], w[3]);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t *>(&lo);
+            pk.y = *reinterpret_cast<uint32_t *>(&hi);
+            *reinterpret_cast<uint2 *>(sh) = pk;
+        } else {
+            for (int e = 0; e < n; ++e) sh[e] = __float2bfloat16_rn(w[e]);
+        }
     }
 }
 
@@ -572,9 +594,11 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
             for (int u = 0; u < 8; ++u)
                 if (s + u < d.nsplit) { g[0] += v[u].x; g[1] += v[u].y; g[2] += v[u].z; g[3] += v[u].w; }
         }
-        for (int e = 0; e < n; ++e) p.grads[i0 + e] = g[e];
+        if (n == 4) *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], g[1], g[2], g[3]);
+        else for (int e = 0; e < n; ++e) p.grads[i0 + e] = g[e];
     } else {
-        for (int e = 0; e < n; ++e) g[e] = p.grads[i0 + e];
+        const float4 t = *reinterpret_cast<const float4 *>(p.grads + i0);
+        g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
     }
     if (!p.update) return;
     apply_update(p, d, i0, j0, n, g);

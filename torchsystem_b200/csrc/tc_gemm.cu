@@ -181,7 +181,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             for (int j = 0; j < 8; ++j)
                 stage[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             __syncwarp();
-            // phase 2: 8 consecutive lanes cover 128 contiguous bytes of one output row
+            // phase 2: 8 consecutive lanes cover 128 contiguous bytes of one output row.
+            // Global operands of the epilogue (the layer's own output for ReLU') are fetched for all 8 row groups
+            // first: issue is in order, so a load used right away would cost a memory round trip per row group.
+            uint2 prev[8];
+            if (EPI == TC_EPI_ACTGRAD) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int row = m0 + q * 32 + i * 4 + sub_row;
+                    const int n = n0 + c + piece * 4;
+                    prev[i] = make_uint2(0u, 0u);
+                    if (row < p.M && n + 4 <= p.N && c + piece * 4 < p.BN && (p.ldo & 3) == 0)
+                        prev[i] = *reinterpret_cast<const uint2 *>(p.A_prev + (int64_t)row * p.ldo + n);
+                }
+            }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int rr = i * 4 + sub_row;
@@ -206,11 +219,18 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                             if (j < nv) w[j] = fmaxf((w[j] + p.bias[n + j]) * keep[j], 0.0f);
                     } else {
                         // dH = dA * relu'(A_prev) / (1-p): A_prev > 0 implies the unit was kept
-                        const __nv_bfloat16 *ap = p.A_prev + (int64_t)row * p.ldo + n;
                         const float sc = p.training ? p.drop.scale : 1.0f;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (j < nv) w[j] = (__bfloat162float(ap[j]) > 0.0f) ? w[j] * sc : 0.0f;
+                        if (nv == 4 && (p.ldo & 3) == 0) {
+                            const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162 *>(&prev[i].x);
+                            const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162 *>(&prev[i].y);
+                            w[0] = (__low2float(lo) > 0.0f) ? w[0] * sc : 0.0f;
+                            w[1] = (__high2float(lo) > 0.0f) ? w[1] * sc : 0.0f;
+                            w[2] = (__low2float(hi) > 0.0f) ? w[2] * sc : 0.0f;
+                            w[3] = (__high2float(hi) > 0.0f) ? w[3] * sc : 0.0f;
+                        } else {
+                            const __nv_bfloat16 *ap = p.A_prev + (int64_t)row * p.ldo + n;
+                            for (int j = 0; j < nv; ++j) w[j] = (__bfloat162float(ap[j]) > 0.0f) ? w[j] * sc : 0.0f;
+                        }
                     }
                     if (nv == 4 && (p.ldo & 3) == 0) {
                         __nv_bfloat162 lo = __floats2bfloat162_rn(w[0], w[1]), hi = __floats2bfloat162_rn(w[2], w[3]);
