@@ -215,3 +215,24 @@ def test_reference_suite_still_passes_with_this_package_imported(tmp_path):
                          capture_output=True, text=True, cwd=tmp_path)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
     assert '17 passed' in out.stdout, out.stdout[-500:]
+
+
+def test_device_loader_batches_shuffle_and_shards():
+    """Loader protocol (tinysys/domain.py:26-29) of DeviceLoader, exercised on the CPU device: ragged last batch,
+    drop_last, a seeded permutation that keeps inputs and targets paired, equal disjoint rank shards."""
+    from torchsystem_b200 import DeviceLoader
+    x = torch.arange(103, dtype=torch.float32).reshape(103, 1).repeat(1, 4)
+    y = torch.arange(103)
+    sizes = [xb.shape[0] for xb, _ in DeviceLoader(x, y, 32, device='cpu')]
+    assert sizes == [32, 32, 32, 7] and len(DeviceLoader(x, y, 32, device='cpu')) == 4
+    assert [xb.shape[0] for xb, _ in DeviceLoader(x, y, 32, device='cpu', drop_last=True)] == [32, 32, 32]
+    a = [(xb, yb) for xb, yb in DeviceLoader(x, y, 32, device='cpu', shuffle=True, seed=7)]
+    b = [(xb, yb) for xb, yb in DeviceLoader(x, y, 32, device='cpu', shuffle=True, seed=7)]
+    assert all(torch.equal(p[0], q[0]) and torch.equal(p[1], q[1]) for p, q in zip(a, b))
+    allx = torch.cat([p[0] for p in a]); ally = torch.cat([p[1] for p in a])
+    assert torch.equal(allx[:, 0].long(), ally) and sorted(ally.tolist()) == list(range(103)) and not torch.equal(ally, y)
+    shards = [DeviceLoader(x, y, 8, device='cpu', rank=r, world=4) for r in range(4)]
+    seen = [torch.cat([yb for _, yb in s]) for s in shards]
+    assert all(len(s) == 24 for s in seen) and len(set(torch.cat(seen).tolist())) == 96
+    xb, yb = next(iter(DeviceLoader(x, y, 8, device='cpu', dtype=torch.bfloat16)))
+    assert xb.dtype == torch.bfloat16 and yb.dtype == torch.int64 and xb.to('cpu') is xb      # .to(device) is a no-op

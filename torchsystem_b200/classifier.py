@@ -47,7 +47,7 @@ class B200Classifier(Aggregate):
     """Drop-in for the reference `Classifier(nn, criterion, optimizer)`.
 
     precision   'bf16' (tcgen05 tensor cores, fp32 accumulate; parity 1e-2) or 'f32' (SIMT; parity 1e-5)
-    dropout_seed  key of the in-kernel Philox dropout masks (pass `masks=` to `fit` to supply them instead)
+    dropout_seed  key of the in-kernel counter-based dropout masks (pass `masks=` to `fit` to supply them instead)
     process_group  torch.distributed group for data-parallel training (default: the world, if initialised)
     dp_mode     'p2p': every rank's optimizer kernel reads all ranks' gradients over NVLink peer mappings (no separate
                 collective); 'nccl': ts_fit_backward -> NCCL all-reduce -> ts_opt_apply
