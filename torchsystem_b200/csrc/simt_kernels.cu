@@ -615,24 +615,36 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
 // not bandwidth, is what the step pays. Buffers alternate with the step parity, so nobody overwrites a gradient a
 // peer may still be reading (a rank passes step s+1's wait only after every peer finished reading step s).
 // =====================================================================================
+__device__ __forceinline__ uint32_t global_ns32() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return (uint32_t)t;
+}
+
 __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp) {
     pdl_launch_dependents();
+    uint32_t *trace = dp.flags[dp.rank] + 16;          // spare words of this rank's flag array: a 4-point time trace (ns)
+    if (blockIdx.x == 1 && threadIdx.x == 0) trace[0] = global_ns32();
     pdl_wait();
+    if (blockIdx.x == 1 && threadIdx.x == 0) trace[1] = global_ns32();
     if (blockIdx.x == 0 && threadIdx.x < dp.world) {
-        __threadfence_system();                                   // the gradient written by the previous kernel is visible system-wide
-        volatile uint32_t *peer_flag = dp.flags[threadIdx.x] + dp.rank;
-        *peer_flag = dp.step;
+        // This rank's gradient was written by the previous kernel in the stream, so it is already visible to peers;
+        // a release store orders the flag behind it. (A full system fence here cost ~10 us per step.)
+        uint32_t *peer_flag = dp.flags[threadIdx.x] + dp.rank;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(peer_flag), "r"(dp.step) : "memory");
     }
     if (threadIdx.x < dp.world) {
-        const volatile uint32_t *mine = dp.flags[dp.rank] + threadIdx.x;
-        uint32_t spins = 0;
-        while ((int32_t)(*mine - dp.step) < 0) {
-            __nanosleep(64);
+        const uint32_t *mine = dp.flags[dp.rank] + threadIdx.x;
+        uint32_t spins = 0, seen;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+            if ((int32_t)(seen - dp.step) >= 0) break;
+            __nanosleep(32);
             if (++spins > (1u << 25)) __trap();                  // a peer never arrived: fail loudly instead of hanging
         }
-        __threadfence_system();
     }
     __syncthreads();
+    if (blockIdx.x == 1 && threadIdx.x == 0) trace[2] = global_ns32();
 
     const int tix = p.chunk_tensor[blockIdx.x];
     if (tix < 0) return;
@@ -649,7 +661,9 @@ __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp)
 #pragma unroll
     for (int r = 0; r < 8; ++r)
         if (r < dp.world) { g[0] += v[r].x; g[1] += v[r].y; g[2] += v[r].z; g[3] += v[r].w; }
+    if (blockIdx.x == 1 && threadIdx.x == 0) trace[3] = global_ns32();
     apply_update(p, d, i0, j0, n, g);
+    if (blockIdx.x == 1 && threadIdx.x == 0) trace[4] = global_ns32();
 }
 
 int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cudaStream_t st) {
