@@ -110,3 +110,26 @@ def test_bf16_wide_hidden_layers_config4_shape_class():
         assert (pr.cpu().numpy() != opr).mean() <= 2e-3
         assert l.item() == pytest.approx(float(ol), rel=1e-2)
     assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=0.05, steps=2, adam=False)
+
+
+def test_bf16_inkernel_cast_matches_cast_kernel(monkeypatch):
+    """fp32 batches converted inside the fused kernel (TSB200_INKERNEL_CAST=1 when the handle is created) must give the
+    same bits as the cast kernel in front of it: predictions, loss records and the weights after three steps."""
+    dims, p, B, steps = [784, 256, 10], 0.1, 4096, 3
+    x, y = synthetic(B * steps + 1000, seed=5)
+    init = seeded_init(dims, bf16=True)
+    outs = []
+    for flag in ('0', '1'):
+        monkeypatch.setenv('TSB200_INKERNEL_CAST', flag)
+        model, net = build_model(dims, p, 'relu', 'sgd', 1e-2, init, 'bf16', max_batch=B)
+        g = torch.Generator().manual_seed(42)
+        got = []
+        for s in range(steps):
+            mask = (torch.rand(B, dims[1], generator=g) >= p).to(torch.uint8)
+            pr, l = model.fit(x[s * B:(s + 1) * B].cuda(), y[s * B:(s + 1) * B].cuda(), masks=[mask.cuda()])
+            got += [pr.cpu(), l.cpu()]
+        pr, l = model.evaluate(x[steps * B:].cuda(), y[steps * B:].cuda())     # ragged last slab: 1000 rows
+        got += [pr.cpu(), l.cpu()] + [q.detach().cpu().clone() for q in net.parameters()]
+        outs.append(got)
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)

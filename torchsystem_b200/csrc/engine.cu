@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -57,6 +58,7 @@ struct ts_mlp {
     int prec = TS_PREC_F32;
     int device = 0;
     int sm_count = 148;
+    bool inkernel_cast = false;   // fp32 batches converted inside the fused kernel instead of by a cast kernel in front
 
     // flat parameter layout (torch order: W0, b0, W1, b1, ...)
     int n_tensors = 0;
@@ -274,17 +276,24 @@ int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, c
 int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks, uint64_t seed,
                   bool train, int64_t *pred, ts_batch_record *rec, const void **a0_out, cudaStream_t st) {
     const void *a0 = x;
-    if (x_dtype == TS_DT_F32) {
+    TS_REQUIRE(x_dtype == TS_DT_F32 || x_dtype == TS_DT_BF16, TS_E_INVALID, "unknown inputs dtype %d", x_dtype);
+    // fp32 batches: either a cast kernel in front, or (TSB200_INKERNEL_CAST=1 at ts_mlp_create) converted inside the fused kernel, which then
+    // also leaves the bf16 copy the dW1 GEMM reads
+    FusedMlpArgs f{};
+    if (x_dtype == TS_DT_F32 && m->inkernel_cast) {
+        f.X_f32 = (const float *)x;
+        f.x_bf16_out = train ? m->x_bf16 : nullptr;
+        a0 = m->x_bf16;
+    } else if (x_dtype == TS_DT_F32) {
         ProfScope ps(K_CAST, st);
         int rc = launch_cast_bf16((const float *)x, m->x_bf16, B * m->dims[0], st);
         if (rc) return rc;
         a0 = m->x_bf16;
+        f.X = m->x_bf16;
     } else {
-        TS_REQUIRE(x_dtype == TS_DT_BF16, TS_E_INVALID, "unknown inputs dtype %d", x_dtype);
+        f.X = (const __nv_bfloat16 *)x;
     }
     *a0_out = a0;
-    FusedMlpArgs f{};
-    f.X = (const __nv_bfloat16 *)a0;
     f.W1 = m->shadow + m->shadow_off[0];
     f.W2p = m->shadow + m->shadow_off[1];
     f.b1 = m->params + m->off[1];
@@ -502,6 +511,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     for (int i = 0; i < n_dims; ++i) m->dims[i] = dims[i];
     m->act = activation; m->p = dropout_p; m->scale = 1.0f / (float)(1.0 - (double)dropout_p);
     m->prec = precision; m->device = device; m->sm_count = sms;
+    if (const char *e = getenv("TSB200_INKERNEL_CAST")) m->inkernel_cast = atoi(e) != 0;
     m->n_tensors = 2 * m->n_layers;
     int64_t o = 0, so = 0;
     for (int l = 0; l < m->n_layers; ++l) {

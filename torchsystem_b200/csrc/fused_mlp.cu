@@ -25,6 +25,8 @@ namespace {
 constexpr int kThreads = 352;   // warp 0: X producer, 1: MMA issuer + TMEM owner, 2: W1/W2 producer, 3..10: epilogue
 constexpr int kEpiThreads = 256; // two warps per TMEM lane quarter, each owning half of the hidden columns
 constexpr int kMaxStages = 6;
+constexpr int kXStages = 4;      // most fp32 staging slots (32 KiB per 128 x 64 tile)
+constexpr uint32_t kXBytes = 128 * 64 * 4;
 constexpr int CP = 16;          // classes padded to one UMMA N / K step
 constexpr int kZCol = 256;      // TMEM column of the logits accumulator
 constexpr int kGCol = 272;      // TMEM columns of the gradient partials: dW2^T at +0/+16, db1 at +32/+48
@@ -32,7 +34,9 @@ constexpr int kGCol = 272;      // TMEM columns of the gradient partials: dW2^T 
 struct FusedParams {
     int B, D, H, C;
     int ns, BN;                // CTAs per cluster splitting the hidden width, hidden columns per CTA (H / ns)
-    int num_kblocks, stages;
+    int num_kblocks, stages, xstages;
+    int x_f32;                 // inputs are fp32: TMA them into a staging ring and convert to bf16 on chip
+    __nv_bfloat16 *x_bf16_out; // fp32 inputs + training: the bf16 copy the dW1 GEMM reads (written by cluster rank 0), or nullptr
     uint32_t b_bytes;
     uint32_t idesc_main, idesc_z, idesc_da;
     const float *b1, *b2;
@@ -69,6 +73,14 @@ __device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, f
     asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t *>(&h);
@@ -81,6 +93,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kMaxStages];
     __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
+    __shared__ __align__(8) uint64_t xf_full_bar[kXStages], xf_empty_bar[kXStages];
     __shared__ __align__(8) uint64_t h_full_bar, w2_full_bar, a_ready_bar, z_full_bar, dz_ready_bar, da_full_bar, dh_ready_bar, g_full_bar;
     __shared__ float s_db2[4][CP];
     __shared__ uint32_t tmem_base_slot;
@@ -98,6 +111,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     uint8_t *w2_tile = tiles + (size_t)p.stages * stage_bytes;           // atoms x [16 rows x 128 B]
     float *b1s = reinterpret_cast<float *>(w2_tile + (size_t)atoms * 2048);
     float *zbuf = b1s + p.BN;                                // [ns][128 rows][16] partial logits of every CTA of the cluster (ns > 1)
+    // fp32 inputs: staging ring behind everything else, 1024-byte aligned for the TMA swizzle
+    uint8_t *xstage = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(zbuf + (p.ns > 1 ? p.ns * BM * CP : 0)) + 1023) & ~(uintptr_t)1023);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int ns = p.ns;
@@ -108,7 +123,10 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     if (threadIdx.x == 0) TRACE(0);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
+        // a stage is full when the W1 tile has landed and the X tile has landed (bf16 inputs: TMA) or been converted
+        // (fp32 inputs: one arrival per converter warp -- 256 per-thread arrivals would serialise on the barrier word)
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], p.x_f32 ? 1 + kEpiThreads / 32 : 2); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < p.xstages; ++s) { mbar_init(&xf_full_bar[s], 1); mbar_init(&xf_empty_bar[s], kEpiThreads / 32); }
         mbar_init(&h_full_bar, 1);
         mbar_init(&w2_full_bar, 1);
         mbar_init(&a_ready_bar, kEpiThreads);
@@ -139,9 +157,18 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         uint32_t phase = 0;
         for (int kb = 0; kb < p.num_kblocks; ++kb) {
             if (elect_one()) {
-                mbar_wait(&empty_bar[s], phase ^ 1);
-                mbar_expect_tx(&full_bar[s], a_bytes);
-                tma_load_2d(&tma_x, &full_bar[s], tiles + (size_t)s * stage_bytes, kb * KATOM, m0);
+                if (!p.x_f32) {
+                    mbar_wait(&empty_bar[s], phase ^ 1);
+                    mbar_expect_tx(&full_bar[s], a_bytes);
+                    tma_load_2d(&tma_x, &full_bar[s], tiles + (size_t)s * stage_bytes, kb * KATOM, m0);
+                } else {
+                    // fp32 tile = two boxes of 32 columns (128 B rows) into the staging ring; the epilogue warps convert
+                    const int xs = kb % p.xstages;
+                    mbar_wait(&xf_empty_bar[xs], ((kb / p.xstages) & 1) ^ 1);
+                    mbar_expect_tx(&xf_full_bar[xs], kXBytes);
+                    tma_load_2d(&tma_x, &xf_full_bar[xs], xstage + (size_t)xs * kXBytes, kb * KATOM, m0);
+                    tma_load_2d(&tma_x, &xf_full_bar[xs], xstage + (size_t)xs * kXBytes + kXBytes / 2, kb * KATOM + 32, m0);
+                }
             }
             __syncwarp();
             if (++s == p.stages) { s = 0; phase ^= 1; }
@@ -241,6 +268,55 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         const int cbeg = half * (p.BN >> 1), cend = cbeg + (p.BN >> 1);     // local columns
         for (int i = et; i < p.BN; i += kEpiThreads) b1s[i] = p.b1[n0 + i];
         named_bar_sync(1, kEpiThreads);
+
+        if (p.x_f32) {
+            // ---- during the main loop these warps are the fp32 -> bf16 converters: thread = (row, 32-column half)
+            const int cr = et >> 1, ch = et & 1;             // tile row 0..127, which fp32 box
+            const uint32_t xsrc0 = smem_u32(xstage) + (uint32_t)ch * (kXBytes / 2) + (uint32_t)cr * 128;
+            const uint32_t dst0 = smem_u32(tiles) + (uint32_t)cr * 128;
+            const uint32_t sw = (uint32_t)(cr & 7);
+            int s = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < p.num_kblocks; ++kb) {
+                const int xs = kb % p.xstages;
+                // every lane observes the TMA barrier itself: bytes written through the async proxy are only guaranteed
+                // visible to threads that waited on the mbarrier
+                mbar_wait(&xf_full_bar[xs], (kb / p.xstages) & 1);          // fp32 tile landed
+                const uint32_t src = xsrc0 + (uint32_t)xs * kXBytes;
+                float4 f[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = lds128(src + (((uint32_t)j ^ sw) << 4));
+                uint4 pk[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    pk[t].x = pack_bf16(f[2 * t].x, f[2 * t].y);
+                    pk[t].y = pack_bf16(f[2 * t].z, f[2 * t].w);
+                    pk[t].z = pack_bf16(f[2 * t + 1].x, f[2 * t + 1].y);
+                    pk[t].w = pack_bf16(f[2 * t + 1].z, f[2 * t + 1].w);
+                }
+                mbar_wait(&empty_bar[s], phase ^ 1);                        // bf16 stage free (its MMAs retired)
+                const uint32_t dst = dst0 + (uint32_t)s * (uint32_t)stage_bytes;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) sts128(dst + ((((uint32_t)ch * 4 + t) ^ sw) << 4), pk[t]);
+                // the staging slot is released only after its values were consumed by the stores above: an arrive does
+                // not wait for loads that are still in flight, so releasing right behind the loads lets the next TMA
+                // fill overtake them
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&xf_empty_bar[xs]);
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full_bar[s]);
+                if (p.x_bf16_out != nullptr && rank == 0 && (int64_t)m0 + cr < p.B) {
+                    // the dW1 = dH^T X GEMM of this step reads the bf16 copy: 64 contiguous bytes per thread
+                    const int col = kb * KATOM + ch * 32;
+                    __nv_bfloat16 *g = p.x_bf16_out + ((int64_t)m0 + cr) * p.D + col;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t)
+                        if (col + t * 8 < p.D) *reinterpret_cast<uint4 *>(g + t * 8) = pk[t];
+                }
+                if (++s == p.stages) { s = 0; phase ^= 1; }
+            }
+        }
 
         // ---- A = relu(dropout(H + b1)) -> bf16 -> swizzled K-major tile
         uint32_t sign[4] = {0, 0, 0, 0};
@@ -539,9 +615,19 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     const uint32_t stage = BM * 128 + p.b_bytes;
     const int atoms = p.BN / KATOM;
     const uint32_t alias_need = 2u * (uint32_t)atoms * BM * 128 + BM * 128;   // A tile + dH tile + dZ tile reuse the stage memory
-    p.stages = (int)((160u * 1024u) / stage);
+    p.x_f32 = a.X_f32 != nullptr ? 1 : 0;
+    TS_REQUIRE((a.X != nullptr) != (a.X_f32 != nullptr), TS_E_INVALID, "fused MLP kernel: exactly one of X (bf16) and X_f32");
+    p.x_bf16_out = p.x_f32 ? a.x_bf16_out : nullptr;
+    // shared memory: pipeline stages + W2 tile + b1 + (cluster) partial logits + (fp32 inputs) staging ring
+    p.xstages = 2;
+    if (const char *f = getenv("TSB_XSTAGES")) p.xstages = atoi(f);
+    TS_REQUIRE(p.xstages >= 1 && p.xstages <= kXStages, TS_E_UNSUPPORTED, "fused MLP kernel: bad staging depth %d", p.xstages);
+    const size_t fixed = (size_t)atoms * 2048 + (size_t)p.BN * 4 + (p.ns > 1 ? (size_t)p.ns * BM * CP * 4 : 0) +
+                         (p.x_f32 ? (size_t)p.xstages * kXBytes + 1024 : 0) + 1024 + 64;
+    p.stages = (int)((226u * 1024u - fixed) / stage);
     if (p.stages > kMaxStages) p.stages = kMaxStages;
-    while ((uint32_t)p.stages * stage < alias_need) ++p.stages;
+    TS_REQUIRE((uint32_t)p.stages * stage >= alias_need && p.stages >= 2, TS_E_UNSUPPORTED,
+               "fused MLP kernel: shared memory budget does not fit H=%d ns=%d (stages %d)", a.H, p.ns, p.stages);
     p.idesc_main = make_idesc(BM, p.BN, TC_MAJOR_K, TC_MAJOR_K);
     p.idesc_z = make_idesc(BM, CP, TC_MAJOR_K, TC_MAJOR_K);
     p.idesc_da = make_idesc(BM, p.BN, TC_MAJOR_K, TC_MAJOR_MN);
@@ -556,15 +642,15 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     p.partials = a.partials; p.ticket = a.ticket; p.record = a.record;
 
     CUtensorMap mx, mw1, mw2;
-    int rc = get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, BM, &mx);
+    int rc = p.x_f32 ? get_map(a.X_f32, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, 32, BM, &mx, 4)
+                     : get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, BM, &mx);
     if (rc) return rc;
     rc = get_map(a.W1, (uint64_t)a.D, (uint64_t)a.H, (uint64_t)a.D, KATOM, (uint32_t)p.BN, &mw1);
     if (rc) return rc;
     rc = get_map(a.W2p, (uint64_t)a.H, (uint64_t)CP, (uint64_t)a.H, KATOM, CP, &mw2);
     if (rc) return rc;
 
-    const size_t smem = (size_t)p.stages * stage + (size_t)atoms * 2048 + (size_t)p.BN * 4 +
-                        (p.ns > 1 ? (size_t)p.ns * BM * CP * 4 : 0) + 1024 + 64;
+    const size_t smem = (size_t)p.stages * stage + fixed;
     const bool train = a.dH_out != nullptr;
     static bool attr_set[2][64] = {{false}};
     int dev = 0;

@@ -148,7 +148,9 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st);
 
 // ---------------------------------------------------------------- fused one-hidden-layer forward + head (fused_mlp.cu)
 struct FusedMlpArgs {
-    const __nv_bfloat16 *X;     // [B, D] bf16
+    const __nv_bfloat16 *X;     // [B, D] bf16 inputs, or nullptr when X_f32 is given
+    const float *X_f32;         // [B, D] fp32 inputs: converted to bf16 on chip (no separate cast kernel)
+    __nv_bfloat16 *x_bf16_out;  // with X_f32 in training: where the bf16 copy for the dW1 GEMM goes
     const __nv_bfloat16 *W1;    // [H, D] bf16 shadow of layer-0 weight
     const __nv_bfloat16 *W2p;   // [16, H] bf16 shadow of the last weight, rows >= C zero
     const float *b1, *b2;

@@ -117,8 +117,8 @@ __host__ __device__ inline uint32_t make_idesc(int M, int N, int a_major, int b_
 
 }  // namespace tc
 
-// cached cuTensorMapEncodeTiled for a row-major bf16 matrix [outer][inner] (pitch in elements), 128-byte swizzle
+// cached cuTensorMapEncodeTiled for a row-major bf16 (or fp32) matrix [outer][inner] (pitch in elements), 128-byte swizzle
 int get_map(const void *ptr, uint64_t inner, uint64_t outer, uint64_t pitch_elems, uint32_t box_inner, uint32_t box_outer,
-            CUtensorMap *out);
+            CUtensorMap *out, uint32_t elem_bytes = 2);
 
 }  // namespace tsb

@@ -13,6 +13,7 @@
 //   dW          = dY^T X : A = dY [K][M] MN-major,  B = X  [K][N] MN-major   (K = batch, split across CTAs)
 #include <cstdlib>
 #include <mutex>
+#include <unordered_map>
 #include <vector>
 
 #include "tc_common.cuh"
@@ -282,40 +283,48 @@ EncodeTiledFn encode_fn() {
 struct MapKey {
     const void *ptr;
     uint64_t inner, outer, pitch;
-    uint32_t box_inner, box_outer;
+    uint32_t box_inner, box_outer, elem_bytes;
     bool operator==(const MapKey &o) const {
         return ptr == o.ptr && inner == o.inner && outer == o.outer && pitch == o.pitch && box_inner == o.box_inner &&
-               box_outer == o.box_outer;
+               box_outer == o.box_outer && elem_bytes == o.elem_bytes;
     }
 };
-std::vector<std::pair<MapKey, CUtensorMap>> g_maps;   // small per-process cache (buffers live in fixed workspaces)
+struct MapKeyHash {
+    size_t operator()(const MapKey &k) const {
+        uint64_t h = (uint64_t)(uintptr_t)k.ptr * 0x9E3779B97F4A7C15ull;
+        h ^= (k.inner * 0xC2B2AE3D27D4EB4Full) ^ (k.outer << 17) ^ (k.pitch << 29) ^ ((uint64_t)k.box_outer << 41) ^ k.elem_bytes;
+        return (size_t)(h ^ (h >> 31));
+    }
+};
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;   // per-process cache: loaders hand out a bounded set of batch views
 std::mutex g_maps_mu;
 
 }  // namespace
 
 int get_map(const void *ptr, uint64_t inner, uint64_t outer, uint64_t pitch_elems, uint32_t box_inner, uint32_t box_outer,
-            CUtensorMap *out) {
-    const MapKey key{ptr, inner, outer, pitch_elems, box_inner, box_outer};
+            CUtensorMap *out, uint32_t elem_bytes) {
+    const MapKey key{ptr, inner, outer, pitch_elems, box_inner, box_outer, elem_bytes};
     std::lock_guard<std::mutex> lock(g_maps_mu);
-    for (auto &e : g_maps)
-        if (e.first == key) { *out = e.second; return TS_OK; }
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return TS_OK; }
     EncodeTiledFn fn = encode_fn();
     TS_REQUIRE(fn != nullptr, TS_E_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
-    TS_REQUIRE(((uintptr_t)ptr & 15) == 0 && (pitch_elems * 2) % 16 == 0, TS_E_INVALID,
+    TS_REQUIRE(elem_bytes == 2 || elem_bytes == 4, TS_E_INVALID, "TMA element size %u", elem_bytes);
+    TS_REQUIRE(((uintptr_t)ptr & 15) == 0 && (pitch_elems * elem_bytes) % 16 == 0, TS_E_INVALID,
                "TMA operand needs a 16-byte aligned base and row pitch (ptr %p, pitch %llu elements)", ptr,
                (unsigned long long)pitch_elems);
     const cuuint64_t dims[2] = {inner, outer};
-    const cuuint64_t strides[1] = {pitch_elems * 2};
+    const cuuint64_t strides[1] = {pitch_elems * elem_bytes};
     const cuuint32_t box[2] = {box_inner, box_outer};
     const cuuint32_t estr[2] = {1, 1};
     CUtensorMap m;
-    const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(ptr), dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    const CUresult r = fn(&m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                          const_cast<void *>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     TS_REQUIRE(r == CUDA_SUCCESS, TS_E_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (dims %llu x %llu, box %u x %u)",
                (int)r, (unsigned long long)inner, (unsigned long long)outer, box_inner, box_outer);
-    if (g_maps.size() > 256) g_maps.clear();
-    g_maps.emplace_back(key, m);
+    if (g_maps.size() > 8192) g_maps.clear();
+    g_maps.emplace(key, m);
     *out = m;
     return TS_OK;
 }
