@@ -3,7 +3,7 @@ sys.path.insert(0, '/root/repo')
 from torch import nn
 from torch.profiler import profile, ProfilerActivity
 from torchsystem_b200 import B200Classifier, MLP
-B = 4096
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
 torch.manual_seed(0)
 opt_kind = sys.argv[1] if len(sys.argv) > 1 else 'sgd'
 net = MLP(784, 256, 10, dropout=0.1, activation=nn.ReLU())

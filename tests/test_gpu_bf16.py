@@ -112,10 +112,11 @@ def test_bf16_wide_hidden_layers_config4_shape_class():
     assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=0.05, steps=2, adam=False)
 
 
-def test_bf16_inkernel_cast_matches_cast_kernel(monkeypatch):
+@pytest.mark.parametrize('B', [4096, 12000])      # a slab is a 4-CTA cluster / a single CTA (12000 rows = 94 slabs, ragged)
+def test_bf16_inkernel_cast_matches_cast_kernel(monkeypatch, B):
     """fp32 batches converted inside the fused kernel (TSB200_INKERNEL_CAST=1 when the handle is created) must give the
     same bits as the cast kernel in front of it: predictions, loss records and the weights after three steps."""
-    dims, p, B, steps = [784, 256, 10], 0.1, 4096, 3
+    dims, p, steps = [784, 256, 10], 0.1, 3
     x, y = synthetic(B * steps + 1000, seed=5)
     init = seeded_init(dims, bf16=True)
     outs = []
@@ -133,3 +134,26 @@ def test_bf16_inkernel_cast_matches_cast_kernel(monkeypatch):
         outs.append(got)
     for a, b in zip(*outs):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize('precision,tol', [('bf16', 1e-2), ('f32', 1e-5)])
+def test_many_row_blocks_two_level_partial_sum(precision, tol):
+    """20,000 rows = 157 row blocks: more than the optimizer sums directly, so the last-layer / bias gradient partials
+    go through the grouped pre-reduction first (and, in bf16 mode, a slab is one CTA with on-chip input conversion)."""
+    dims, p, B, steps = [784, 256, 10], 0.1, 20000, 2
+    x, y = synthetic(B * steps)
+    bf16 = precision == 'bf16'
+    if bf16:
+        x = x.bfloat16().float()
+    init = seeded_init(dims, bf16=bf16)
+    model, net = build_model(dims, p, 'relu', 'sgd', 1e-2, init, precision, max_batch=B)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=OPT['sgd'], lr=1e-2, emulate_bf16=bf16)
+    g = torch.Generator().manual_seed(42)
+    for s in range(steps):
+        xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
+        mask = (torch.rand(B, dims[1], generator=g) >= p).to(torch.uint8)
+        pr, l = model.fit(xb.cuda(), yb.cuda(), masks=[mask.cuda()])
+        opr, ol = oracle.fit(xb.numpy(), yb.numpy(), [mask.numpy()])
+        assert (pr.cpu().numpy() != opr).mean() <= (1e-3 if bf16 else 0.0)
+        assert l.item() == pytest.approx(float(ol), rel=tol)
+    assert_params_close(net_params(net), oracle.parameters(), tol, lr=1e-2, steps=steps, adam=False)

@@ -58,7 +58,7 @@ struct ts_mlp {
     int prec = TS_PREC_F32;
     int device = 0;
     int sm_count = 148;
-    bool inkernel_cast = false;   // fp32 batches converted inside the fused kernel instead of by a cast kernel in front
+    int inkernel_cast = -1;       // fp32 batches converted inside the fused kernel: 1 always, 0 never (cast kernel in front), -1 by batch size
 
     // flat parameter layout (torch order: W0, b0, W1, b1, ...)
     int n_tensors = 0;
@@ -135,7 +135,8 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
     for (int t = 0; t < m->n_tensors; ++t) {
         m->partial_stride[t] = round_up(m->cnt[t], 4) + 32;   // +128 B: successive partials of an element fall into different L2 slices
         m->partial_off[t] = pfloats;
-        if (m->max_split[t] > 1) pfloats += (int64_t)m->max_split[t] * m->partial_stride[t];
+        // tensors that can have more than kReduceAbove partials get kReduceSlots more slots for the pre-reduced groups
+        if (m->max_split[t] > 1) pfloats += (int64_t)(m->max_split[t] + (m->max_split[t] > kReduceAbove ? kReduceSlots : 0)) * m->partial_stride[t];
     }
     m->partials = (float *)c.take(pfloats * 4);
     if (m->prec == TS_PREC_BF16) {
@@ -250,6 +251,23 @@ int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, c
         any_partial |= o.t[t].nsplit > 0;
     }
     if (!update && !any_partial) return TS_OK;
+    // many row-block partials (batches beyond 16,384 rows): one extra launch sums them in groups of kReduceFan first
+    ReduceArgs r{};
+    for (int t = 0; t < m->n_tensors; ++t) {
+        if (o.t[t].nsplit <= kReduceAbove) continue;
+        TS_REQUIRE(r.n < 4 && o.t[t].nsplit <= m->max_split[t] && m->max_split[t] == kMaxRowBlocks, TS_E_INVALID,
+                   "tensor %d: %d partials cannot be pre-reduced", t, o.t[t].nsplit);
+        const int i = r.n++;
+        r.off[i] = m->partial_off[t]; r.stride[i] = m->partial_stride[t]; r.count[i] = m->cnt[t]; r.nsplit[i] = o.t[t].nsplit;
+        r.dst_off[i] = m->partial_off[t] + (int64_t)kMaxRowBlocks * m->partial_stride[t];
+        o.t[t].partial_off = r.dst_off[i];
+        o.t[t].nsplit = (r.nsplit[i] + kReduceFan - 1) / kReduceFan;
+    }
+    if (r.n > 0) {
+        ProfScope ps(K_COLSUM, st);
+        int rc = launch_reduce_partials(m->partials, r, st);
+        if (rc) return rc;
+    }
     o.params = m->params; o.grads = m->grads; o.exp_avg = m->exp_avg; o.exp_avg_sq = m->exp_avg_sq;
     o.partials = m->partials; o.shadow = m->shadow; o.chunk_tensor = m->d_chunk_tensor;
     o.kind = m->opt_kind; o.update = update ? 1 : 0; o.grad_scale = grad_scale;
@@ -277,10 +295,13 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
                   bool train, int64_t *pred, ts_batch_record *rec, const void **a0_out, cudaStream_t st) {
     const void *a0 = x;
     TS_REQUIRE(x_dtype == TS_DT_F32 || x_dtype == TS_DT_BF16, TS_E_INVALID, "unknown inputs dtype %d", x_dtype);
-    // fp32 batches: either a cast kernel in front, or (TSB200_INKERNEL_CAST=1 at ts_mlp_create) converted inside the fused kernel, which then
-    // also leaves the bf16 copy the dW1 GEMM reads
+    // fp32 batches: a cast kernel in front, or converted inside the fused kernel (which then also leaves the bf16 copy
+    // the dW1 GEMM reads). Measured on B200: on-chip conversion wins when a slab is one CTA (large batches, HBM-bound:
+    // 4 B/element read once instead of 4 + 2 + 2), and loses when the slab is a cluster, where every CTA of the cluster
+    // would ingest and convert the whole fp32 tile. TSB200_INKERNEL_CAST=0/1 at ts_mlp_create overrides.
+    const bool inkernel = m->inkernel_cast >= 0 ? m->inkernel_cast != 0 : fused_cluster_size(B, m->dims[1], m->sm_count) == 1;
     FusedMlpArgs f{};
-    if (x_dtype == TS_DT_F32 && m->inkernel_cast) {
+    if (x_dtype == TS_DT_F32 && inkernel) {
         f.X_f32 = (const float *)x;
         f.x_bf16_out = train ? m->x_bf16 : nullptr;
         a0 = m->x_bf16;
@@ -511,7 +532,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     for (int i = 0; i < n_dims; ++i) m->dims[i] = dims[i];
     m->act = activation; m->p = dropout_p; m->scale = 1.0f / (float)(1.0 - (double)dropout_p);
     m->prec = precision; m->device = device; m->sm_count = sms;
-    if (const char *e = getenv("TSB200_INKERNEL_CAST")) m->inkernel_cast = atoi(e) != 0;
+    if (const char *e = getenv("TSB200_INKERNEL_CAST")) m->inkernel_cast = atoi(e) != 0 ? 1 : 0;
     m->n_tensors = 2 * m->n_layers;
     int64_t o = 0, so = 0;
     for (int l = 0; l < m->n_layers; ++l) {

@@ -73,6 +73,9 @@ __device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, f
     asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
@@ -125,8 +128,10 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     if (threadIdx.x == 0) {
         // a stage is full when the W1 tile has landed and the X tile has landed (bf16 inputs: TMA) or been converted
         // (fp32 inputs: one arrival per converter warp -- 256 per-thread arrivals would serialise on the barrier word)
-        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], p.x_f32 ? 1 + kEpiThreads / 32 : 2); mbar_init(&empty_bar[s], 1); }
-        for (int s = 0; s < p.xstages; ++s) { mbar_init(&xf_full_bar[s], 1); mbar_init(&xf_empty_bar[s], kEpiThreads / 32); }
+        // The X tile (bf16) or its fp32 staging slot is shared by the cluster: every CTA loads 1/ns of the rows and
+        // multicasts them, so a slot is free only when all ns CTAs have released it.
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], p.x_f32 ? 1 + kEpiThreads / 32 : 2); mbar_init(&empty_bar[s], p.x_f32 ? 1 : ns); }
+        for (int s = 0; s < p.xstages; ++s) { mbar_init(&xf_full_bar[s], 1); mbar_init(&xf_empty_bar[s], (kEpiThreads / 32) * ns); }
         mbar_init(&h_full_bar, 1);
         mbar_init(&w2_full_bar, 1);
         mbar_init(&a_ready_bar, kEpiThreads);
@@ -153,6 +158,11 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     if (ns > 1 && warp < 3) cluster_arrive();                  // phase 1 (logit exchange): these warps only have to have arrived
     if (warp == 0) {
         // ===================== TMA producer: X tiles (A operand) =====================
+        // In a cluster every CTA needs the same X tile: each loads BM / ns of its rows and multicasts them to all ns CTAs
+        // (a quarter of the TMA requests and of the L2 reads per CTA at ns = 4).
+        const int rows = BM / ns;                                  // rows of the tile this CTA loads
+        const uint32_t slice = (uint32_t)rank * (uint32_t)rows * 128u;
+        const uint16_t mask = (uint16_t)((1u << ns) - 1u);
         int s = 0;
         uint32_t phase = 0;
         for (int kb = 0; kb < p.num_kblocks; ++kb) {
@@ -160,14 +170,22 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 if (!p.x_f32) {
                     mbar_wait(&empty_bar[s], phase ^ 1);
                     mbar_expect_tx(&full_bar[s], a_bytes);
-                    tma_load_2d(&tma_x, &full_bar[s], tiles + (size_t)s * stage_bytes, kb * KATOM, m0);
+                    uint8_t *dst = tiles + (size_t)s * stage_bytes + slice;
+                    if (ns == 1) tma_load_2d(&tma_x, &full_bar[s], dst, kb * KATOM, m0);
+                    else tma_load_2d_multicast(&tma_x, &full_bar[s], dst, kb * KATOM, m0 + (int)rank * rows, mask);
                 } else {
                     // fp32 tile = two boxes of 32 columns (128 B rows) into the staging ring; the epilogue warps convert
                     const int xs = kb % p.xstages;
                     mbar_wait(&xf_empty_bar[xs], ((kb / p.xstages) & 1) ^ 1);
                     mbar_expect_tx(&xf_full_bar[xs], kXBytes);
-                    tma_load_2d(&tma_x, &xf_full_bar[xs], xstage + (size_t)xs * kXBytes, kb * KATOM, m0);
-                    tma_load_2d(&tma_x, &xf_full_bar[xs], xstage + (size_t)xs * kXBytes + kXBytes / 2, kb * KATOM + 32, m0);
+                    uint8_t *dst = xstage + (size_t)xs * kXBytes + slice;
+                    if (ns == 1) {
+                        tma_load_2d(&tma_x, &xf_full_bar[xs], dst, kb * KATOM, m0);
+                        tma_load_2d(&tma_x, &xf_full_bar[xs], dst + kXBytes / 2, kb * KATOM + 32, m0);
+                    } else {
+                        tma_load_2d_multicast(&tma_x, &xf_full_bar[xs], dst, kb * KATOM, m0 + (int)rank * rows, mask);
+                        tma_load_2d_multicast(&tma_x, &xf_full_bar[xs], dst + kXBytes / 2, kb * KATOM + 32, m0 + (int)rank * rows, mask);
+                    }
                 }
             }
             __syncwarp();
@@ -204,7 +222,9 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 #pragma unroll
                 for (int k = 0; k < KATOM / UMMA_K; ++k)
                     umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc_main, (kb > 0 || k > 0) ? 1u : 0u);
-                umma_commit(&empty_bar[s]);
+                // bf16 inputs in a cluster: the stage's X tile was multicast by all ns CTAs, so all of them are told it is free
+                if (ns == 1 || p.x_f32) umma_commit(&empty_bar[s]);
+                else umma_commit_multicast(&empty_bar[s], (uint16_t)((1u << ns) - 1u));
                 if (kb == p.num_kblocks - 1) umma_commit(&h_full_bar);
                 if (kb == 0) TRACE(2);
                 if (kb == p.num_kblocks - 1) TRACE(3);
@@ -302,7 +322,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 // not wait for loads that are still in flight, so releasing right behind the loads lets the next TMA
                 // fill overtake them
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&xf_empty_bar[xs]);
+                if (ns == 1) { if (lane == 0) mbar_arrive(&xf_empty_bar[xs]); }
+                else if (lane < ns) mbar_arrive_cluster(map_to_rank(smem_u32(&xf_empty_bar[xs]), (uint32_t)lane));
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&full_bar[s]);
@@ -592,6 +613,15 @@ int read_fused_trace(unsigned long long *out_host) {
 
 bool fused_mlp_supported(int D, int H, int C) { return (H == 64 || H == 128 || H == 256) && C >= 1 && C <= CP && D % 8 == 0; }
 
+// Split the hidden width of each 128-row slab over a cluster of ns CTAs while the whole grid still fits in one wave:
+// small batches would otherwise leave most SMs idle (batch 4096 = 32 slabs -> 4 x 32 = 128 CTAs).
+int fused_cluster_size(int64_t B, int H, int sm_count) {
+    const int64_t slabs = (B + BM - 1) / BM;
+    for (int ns = 4; ns >= 2; ns >>= 1)
+        if (H / ns >= KATOM && slabs * ns <= sm_count) return ns;
+    return 1;
+}
+
 int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     TS_REQUIRE(fused_mlp_supported(a.D, a.H, a.C), TS_E_UNSUPPORTED, "fused MLP kernel: unsupported shape D=%d H=%d C=%d", a.D, a.H, a.C);
     TS_REQUIRE(a.B >= 1, TS_E_INVALID, "fused MLP kernel: batch %lld", (long long)a.B);
@@ -600,13 +630,7 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     const int slabs = (int)((a.B + BM - 1) / BM);
     TS_REQUIRE(slabs <= kMaxHeadBlocks, TS_E_TOO_LARGE, "fused MLP kernel: batch %lld needs %d row slabs, more than the %d partial slots",
                (long long)a.B, slabs, kMaxHeadBlocks);
-    // Split the hidden width of each 128-row slab over a cluster of ns CTAs while the whole grid still fits in one
-    // wave: small batches would otherwise leave most SMs idle (batch 4096 = 32 slabs -> 4 x 32 = 128 CTAs).
-    p.ns = 1;
-    if (const char *f = getenv("TSB_FUSED_NS")) p.ns = atoi(f);
-    else
-        for (int ns = 4; ns >= 2; ns >>= 1)
-            if (a.H / ns >= KATOM && slabs * ns <= sm_count) { p.ns = ns; break; }
+    p.ns = fused_cluster_size(a.B, a.H, sm_count);
     TS_REQUIRE(p.ns == 1 || p.ns == 2 || p.ns == 4, TS_E_INVALID, "cluster size %d", p.ns);
     TS_REQUIRE(a.H / p.ns >= KATOM, TS_E_INVALID, "cluster size %d leaves fewer than 64 hidden columns per CTA", p.ns);
     p.BN = a.H / p.ns;
@@ -642,8 +666,9 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     p.partials = a.partials; p.ticket = a.ticket; p.record = a.record;
 
     CUtensorMap mx, mw1, mw2;
-    int rc = p.x_f32 ? get_map(a.X_f32, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, 32, BM, &mx, 4)
-                     : get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, BM, &mx);
+    // X box: BM / ns rows -- every CTA of a cluster loads its share of the tile's rows and multicasts it
+    int rc = p.x_f32 ? get_map(a.X_f32, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, 32, (uint32_t)(BM / p.ns), &mx, 4)
+                     : get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, (uint32_t)(BM / p.ns), &mx);
     if (rc) return rc;
     rc = get_map(a.W1, (uint64_t)a.D, (uint64_t)a.H, (uint64_t)a.D, KATOM, (uint32_t)p.BN, &mw1);
     if (rc) return rc;

@@ -9,7 +9,10 @@ constexpr int kMaxLayers = 8;          // dense layers per aggregate
 constexpr int kMaxClasses = 32;        // width of the last layer handled by the fused head kernel
 constexpr int kChunk = 1024;           // flat-buffer alignment of every parameter tensor (elements)
 constexpr int kMaxSplits = 32;         // split-K partials per weight tensor
-constexpr int kMaxRowBlocks = 128;     // 128-row blocks whose small-gradient partials are kept apart (larger batches: more rows per block is not supported -> fallback kernels)
+constexpr int kMaxRowBlocks = 1024;    // 128-row blocks whose small-gradient partials are kept apart (= kMaxHeadBlocks: batches up to 131,072 rows)
+constexpr int kReduceAbove = 128;      // a tensor with more partials than this is pre-reduced in groups of kReduceFan before the optimizer
+constexpr int kReduceFan = 32;
+constexpr int kReduceSlots = kMaxRowBlocks / kReduceFan;   // extra partial slots behind the kMaxRowBlocks regular ones
 constexpr int kMaxHeadBlocks = 1024;   // head-kernel grid cap (partials buffer size)
 
 // ---------------------------------------------------------------- fp32 SIMT GEMM (precision mode F32)
@@ -98,6 +101,15 @@ struct OptArgs {
 };
 int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st);
 
+// Two-level sum for tensors with many row-block partials: group g = partials [32 g, 32 g + 32) summed in index order into
+// slot dst_off + g * stride; the optimizer then sums the groups. Fixed order, no atomics.
+struct ReduceArgs {
+    int n;
+    int64_t off[4], stride[4], count[4], dst_off[4];
+    int nsplit[4];
+};
+int launch_reduce_partials(float *partials, const ReduceArgs &r, cudaStream_t st);
+
 // data parallel: peer-mapped gradient buffers and flag arrays of every rank (this step's parity)
 constexpr int kMaxRanks = 8;
 struct DpArgs {
@@ -171,6 +183,7 @@ struct FusedMlpArgs {
 };
 bool fused_mlp_supported(int D, int H, int C);
 inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }
+int fused_cluster_size(int64_t B, int H, int sm_count);   // CTAs per 128-row slab the launcher will use
 int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st);
 int read_fused_trace(unsigned long long *out_host);   // 32 clock64 samples of CTA 0 of the last launch
 

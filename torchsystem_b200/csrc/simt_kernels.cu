@@ -672,6 +672,43 @@ int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cu
     return TS_OK;
 }
 
+__global__ void __launch_bounds__(256) reduce_partials_kernel(float *partials, ReduceArgs r) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int t = blockIdx.z, grp = blockIdx.y;
+    const int s0 = grp * kReduceFan;
+    if (s0 >= r.nsplit[t]) return;
+    const int64_t j0 = ((int64_t)blockIdx.x * 256 + threadIdx.x) * 4;
+    if (j0 >= r.count[t]) return;
+    const int s1 = min(s0 + kReduceFan, r.nsplit[t]);
+    const float *q = partials + r.off[t] + j0;          // partial rows are padded past `count`: whole float4 loads
+    float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    for (int s = s0; s < s1; s += 8) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            v[u] = (s + u < s1) ? *reinterpret_cast<const float4 *>(q + (int64_t)(s + u) * r.stride[t]) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (s + u < s1) { g[0] += v[u].x; g[1] += v[u].y; g[2] += v[u].z; g[3] += v[u].w; }
+    }
+    *reinterpret_cast<float4 *>(partials + r.dst_off[t] + (int64_t)grp * r.stride[t] + j0) = make_float4(g[0], g[1], g[2], g[3]);
+}
+
+int launch_reduce_partials(float *partials, const ReduceArgs &r, cudaStream_t st) {
+    int64_t max_count = 0;
+    int max_groups = 0;
+    for (int t = 0; t < r.n; ++t) {
+        max_count = r.count[t] > max_count ? r.count[t] : max_count;
+        const int g = (r.nsplit[t] + kReduceFan - 1) / kReduceFan;
+        max_groups = g > max_groups ? g : max_groups;
+    }
+    const dim3 grid((unsigned)((max_count + 1023) / 1024), (unsigned)max_groups, (unsigned)r.n);
+    TS_CUDA_CHECK(launch_pdl(reduce_partials_kernel, grid, dim3(256), 0, st, 1, partials, r));
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
 int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st) {
     TS_CUDA_CHECK(launch_pdl(optimizer_kernel, dim3((unsigned)n_chunks), dim3(256), 0, st, 1, a));
     TS_LAUNCH_CHECK();
