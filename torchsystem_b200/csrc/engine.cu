@@ -87,6 +87,8 @@ struct ts_mlp {
     float *partials = nullptr;
     int64_t partial_off[2 * kMaxLayers] = {0}, partial_stride[2 * kMaxLayers] = {0};
     __nv_bfloat16 *x_bf16 = nullptr, *shadow = nullptr;
+    __nv_bfloat16 *x_bf16_alt = nullptr;   // second input buffer of the fused path: lets the next batch's cast overlap this step's optimizer
+    int x_parity = 0;
     int64_t shadow_off[kMaxLayers] = {0};   // hidden-layer weights, dense [out][in]; last layer: [16][in], rows >= classes zero
     int64_t shadow_total = 0;
     bool fused = false;                     // one hidden layer of a width the fused kernel takes
@@ -141,6 +143,7 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
     m->partials = (float *)c.take(pfloats * 4);
     if (m->prec == TS_PREC_BF16) {
         m->x_bf16 = (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2);
+        m->x_bf16_alt = m->fused ? (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2) : nullptr;
         m->shadow = (__nv_bfloat16 *)c.take(m->shadow_total * 2);
     }
     return c.used;
@@ -301,16 +304,23 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     // would ingest and convert the whole fp32 tile. TSB200_INKERNEL_CAST=0/1 at ts_mlp_create overrides.
     const bool inkernel = m->inkernel_cast >= 0 ? m->inkernel_cast != 0 : fused_cluster_size(B, m->dims[1], m->sm_count) == 1;
     FusedMlpArgs f{};
+    if (x_dtype == TS_DT_F32) m->x_parity ^= 1;      // both fp32 routes alternate between the two bf16 input buffers
+    __nv_bfloat16 *xb = m->x_parity ? m->x_bf16_alt : m->x_bf16;
     if (x_dtype == TS_DT_F32 && inkernel) {
         f.X_f32 = (const float *)x;
-        f.x_bf16_out = train ? m->x_bf16 : nullptr;
-        a0 = m->x_bf16;
+        f.x_bf16_out = train ? xb : nullptr;
+        a0 = xb;
     } else if (x_dtype == TS_DT_F32) {
+        // The cast does not wait for the kernel in front (the previous step's optimizer) before converting, only before
+        // exiting, so it overlaps it. Why its destination is free: the two buffers alternate per cast, so this one was
+        // last read by the fused kernel / dW GEMM that followed the cast before the previous one; this cast can only
+        // start once the most recent fused kernel has released its dependents, which that kernel does after its own
+        // wait, i.e. after everything older -- those readers included -- has completed.
         ProfScope ps(K_CAST, st);
-        int rc = launch_cast_bf16((const float *)x, m->x_bf16, B * m->dims[0], st);
+        int rc = launch_cast_bf16((const float *)x, xb, B * m->dims[0], st, true);
         if (rc) return rc;
-        a0 = m->x_bf16;
-        f.X = m->x_bf16;
+        a0 = xb;
+        f.X = xb;
     } else {
         f.X = (const __nv_bfloat16 *)x;
     }

@@ -151,8 +151,10 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
     if (ns > 1) { cluster_arrive(); cluster_wait(); }          // every CTA of the cluster is running: its shared memory may be written
-    pdl_launch_dependents();
+    // Dependents are released only AFTER the wait: the early-running cast of the next batch (engine.cu) relies on
+    // "a kernel behind this one has started" implying "everything in front of this one has completed".
     pdl_wait();          // the prologue above overlapped the predecessor's tail; global memory is touched from here on
+    pdl_launch_dependents();
     if (threadIdx.x == 0) TRACE(1);
 
     if (ns > 1 && warp < 3) cluster_arrive();                  // phase 1 (logit exchange): these warps only have to have arrived

@@ -120,7 +120,7 @@ struct DpArgs {
 };
 int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cudaStream_t st);
 
-int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st);
+int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end = false);
 
 // ---------------------------------------------------------------- metrics
 int launch_metrics_accumulate(ts_metrics_state *state, const ts_batch_record *ring, int64_t ring_len, int64_t first,

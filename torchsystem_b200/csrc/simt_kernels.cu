@@ -716,9 +716,13 @@ int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st) {
 }
 
 // =====================================================================================
-__global__ void __launch_bounds__(256) cast_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int64_t n) {
+// wait_at_end = 0: ordinary stream order (dst may still be read by the kernel in front).
+// wait_at_end = 1: the conversion runs concurrently with the kernel in front (the previous step's optimizer) and only
+//   waits for it before exiting, so "this kernel is complete" still implies "everything before it is complete" for the
+//   kernel behind. The caller guarantees nothing in flight touches dst (alternating buffers, see engine.cu).
+__global__ void __launch_bounds__(256) cast_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int64_t n, int wait_at_end) {
     pdl_launch_dependents();
-    pdl_wait();      // dst may still be read by a kernel of the previous step
+    if (!wait_at_end) pdl_wait();
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * 8;
     for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
         if (i + 8 <= n) {
@@ -731,14 +735,15 @@ __global__ void __launch_bounds__(256) cast_bf16_kernel(const float *__restrict_
             for (int64_t e = i; e < n; ++e) dst[e] = __float2bfloat16_rn(src[e]);
         }
     }
+    if (wait_at_end) pdl_wait();
 }
 
-int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st) {
+int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end) {
     if (n <= 0) return TS_OK;
     int64_t blocks = (n / 8 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     if (blocks < 1) blocks = 1;
-    TS_CUDA_CHECK(launch_pdl(cast_bf16_kernel, dim3((unsigned)blocks), dim3(256), 0, st, 1, src, dst, n));
+    TS_CUDA_CHECK(launch_pdl(cast_bf16_kernel, dim3((unsigned)blocks), dim3(256), 0, st, 1, src, dst, n, wait_at_end ? 1 : 0));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
