@@ -135,13 +135,15 @@ int32_t ts_fit_backward(ts_mlp *m, const void *inputs, int32_t inputs_dtype, con
                         ts_batch_record *record, void *stream);
 int32_t ts_opt_apply(ts_mlp *m, float grad_scale, void *stream);
 
+#define TS_DP_FLAG_WORDS 64
 /* Data parallel without a separate collective (no counterpart in the reference, which is single-process): after
- * ts_dp_bind, ts_fit_step keeps this rank's reduced gradient in `grad_bufs[parity][rank]` and its optimizer kernel
- * reads the same chunk of every rank's buffer over the peer mappings (NVLink / NVSwitch), sums in rank order,
+ * ts_dp_bind, ts_fit_step's optimizer kernel sums this rank's gradient partials into `grad_bufs[parity][rank]`, signals
+ * its peers, reads the same chunk of every rank's buffer over the peer mappings (NVLink / NVSwitch), sums in rank order,
  * scales by 1/world and updates -- all ranks end a step with bit-identical weights.
  *   grad_bufs  HOST array of 2*world device pointers, buffer b of rank r at [b*world + r]; each as long as the flat
  *              parameter buffer (ts_mlp_param_layout), mapped on THIS device (e.g. torch symmetric memory, CUDA IPC)
- *   flag_bufs  HOST array of world device pointers to each rank's flag array (>= 8 x uint32, zero-initialised)
+ *   flag_bufs  HOST array of world device pointers to each rank's flag array: TS_DP_FLAG_WORDS uint32, zero-initialised
+ *              (word q < world: last step rank q has published; word 8: arrival ticket; words 16..20: time trace)
  * Every rank must call ts_fit_step the same number of times; a rank that never arrives makes the others trap. */
 int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bufs /*HOST*/, uint32_t *const *flag_bufs /*HOST*/);
 

@@ -21,8 +21,8 @@ for i in range(256): step(i)
 e1.record(); torch.cuda.synchronize()
 if rank == 0: print(f'{mode}: {e0.elapsed_time(e1) / 256 * 1e3:.1f} us per fit (world {world})', flush=True)
 if model._p2p is not None:
-    tr = model._p2p[1][16:21].cpu().tolist(); tr = [(v - tr[0]) & 0xffffffff for v in tr]
-    print(f'rank {rank} dp kernel trace ns: pdl_wait_done {tr[1]}, flags_seen {tr[2]}, peers_read {tr[3]}, updated {tr[4]}', flush=True)
+    tr = model._p2p[1][16:24].cpu().tolist(); tr = [(v - tr[0]) & 0xffffffff for v in tr]
+    print(f'rank {rank} dp kernel trace ns: pdl_wait_done {tr[1]}, flags_seen {tr[2]}, peers_read {tr[3]}, updated {tr[4]} | part1_done {tr[5]} last_cta_ticket {tr[6]} flags_sent {tr[7]}', flush=True)
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for i in range(64): step(i)
     torch.cuda.synchronize()

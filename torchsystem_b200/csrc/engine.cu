@@ -241,20 +241,19 @@ void fill_head(const ts_mlp *m, HeadArgs &h, const void *a_last, const int64_t *
     h.partials = m->head_partials; h.ticket = m->ticket; h.record = rec;
 }
 
-int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, cudaStream_t st) {
-    OptArgs o{};
+// Tensor table of the optimizer kernels. Tensors with many row-block partials (batches beyond 16,384 rows) are summed in
+// groups of kReduceFan by one extra launch first; the optimizer then sums the groups.
+int fill_tensor_table(ts_mlp *m, const int *nsplit, OptArgs &o, bool *any_partial, cudaStream_t st) {
     o.n_tensors = m->n_tensors;
-    bool any_partial = false;
+    *any_partial = false;
     for (int t = 0; t < m->n_tensors; ++t) {
         o.t[t].offset = m->off[t]; o.t[t].count = m->cnt[t];
         o.t[t].partial_off = m->partial_off[t]; o.t[t].partial_stride = m->partial_stride[t];
         const int l = t / 2;
         o.t[t].shadow_off = (m->prec == TS_PREC_BF16 && t % 2 == 0) ? m->shadow_off[l] : -1;
         o.t[t].nsplit = nsplit ? nsplit[t] : 0;
-        any_partial |= o.t[t].nsplit > 0;
+        *any_partial |= o.t[t].nsplit > 0;
     }
-    if (!update && !any_partial) return TS_OK;
-    // many row-block partials (batches beyond 16,384 rows): one extra launch sums them in groups of kReduceFan first
     ReduceArgs r{};
     for (int t = 0; t < m->n_tensors; ++t) {
         if (o.t[t].nsplit <= kReduceAbove) continue;
@@ -273,21 +272,38 @@ int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, c
     }
     o.params = m->params; o.grads = m->grads; o.exp_avg = m->exp_avg; o.exp_avg_sq = m->exp_avg_sq;
     o.partials = m->partials; o.shadow = m->shadow; o.chunk_tensor = m->d_chunk_tensor;
-    o.kind = m->opt_kind; o.update = update ? 1 : 0; o.grad_scale = grad_scale;
-    if (update) {
-        m->step += 1;
-        const double b1 = m->hyper.beta1, b2 = m->hyper.beta2;
-        o.lr = (float)m->hyper.lr;
-        o.beta1 = (float)b1; o.beta2 = (float)b2; o.eps = (float)m->hyper.eps;
-        o.one_minus_beta1 = (float)(1.0 - b1); o.one_minus_beta2 = (float)(1.0 - b2);
-        if (m->opt_kind == TS_OPT_ADAM) {
-            // host doubles exactly as torch computes them (adam.py: bias_correction*, step_size)
-            const double bc1 = 1.0 - pow(b1, (double)m->step);
-            const double bc2 = 1.0 - pow(b2, (double)m->step);
-            o.step_size = (float)(m->hyper.lr / bc1);
-            o.bc2_sqrt = (float)sqrt(bc2);
-        }
+    o.kind = m->opt_kind;
+    o.partial_depth = m->n_chunks <= 3 * (int64_t)m->sm_count ? 16 : 4;
+    return TS_OK;
+}
+
+// Advances the step counter and fills the hyper-parameters of one update.
+void fill_update(ts_mlp *m, OptArgs &o) {
+    m->step += 1;
+    const double b1 = m->hyper.beta1, b2 = m->hyper.beta2;
+    o.lr = (float)m->hyper.lr;
+    o.beta1 = (float)b1; o.beta2 = (float)b2; o.eps = (float)m->hyper.eps;
+    o.one_minus_beta1 = (float)(1.0 - b1); o.one_minus_beta2 = (float)(1.0 - b2);
+    if (m->opt_kind == TS_OPT_ADAM) {
+        // host doubles exactly as torch computes them (adam.py: bias_correction*, step_size)
+        const double bc1 = 1.0 - pow(b1, (double)m->step);
+        const double bc2 = 1.0 - pow(b2, (double)m->step);
+        o.step_size = (float)(m->hyper.lr / bc1);
+        o.bc2_sqrt = (float)sqrt(bc2);
     }
+}
+
+int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, cudaStream_t st) {
+    OptArgs o{};
+    bool any_partial = false;
+    if (!update) {      // nothing to launch when no tensor has partials to fold
+        for (int t = 0; t < m->n_tensors; ++t) any_partial |= nsplit && nsplit[t] > 0;
+        if (!any_partial) return TS_OK;
+    }
+    int rc = fill_tensor_table(m, nsplit, o, &any_partial, st);
+    if (rc) return rc;
+    o.update = update ? 1 : 0; o.grad_scale = grad_scale;
+    if (update) fill_update(m, o);
     ProfScope ps(K_OPT, st);
     return launch_optimizer(o, m->n_chunks, st);
 }
@@ -347,33 +363,21 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     return launch_fused_mlp(f, m->sm_count, st);
 }
 
-// Data-parallel update: the cross-rank gradient sum happens inside the optimizer kernel, over peer mappings.
-int run_dp_optimizer(ts_mlp *m, cudaStream_t st) {
+// Data-parallel update: the split-partial sum AND the cross-rank gradient sum happen inside the optimizer kernel, over
+// peer mappings (dp_optimizer_kernel).
+int run_dp_optimizer(ts_mlp *m, const int *nsplit, cudaStream_t st) {
     OptArgs o{};
-    o.n_tensors = m->n_tensors;
-    for (int t = 0; t < m->n_tensors; ++t) {
-        o.t[t].offset = m->off[t]; o.t[t].count = m->cnt[t];
-        o.t[t].shadow_off = (m->prec == TS_PREC_BF16 && t % 2 == 0) ? m->shadow_off[t / 2] : -1;
-        o.t[t].nsplit = 0;
-    }
-    o.params = m->params; o.grads = m->grads; o.exp_avg = m->exp_avg; o.exp_avg_sq = m->exp_avg_sq;
-    o.partials = m->partials; o.shadow = m->shadow; o.chunk_tensor = m->d_chunk_tensor;
-    o.kind = m->opt_kind; o.update = 1; o.grad_scale = 1.0f / (float)m->dp_world;
+    bool any_partial = false;
+    int rc = fill_tensor_table(m, nsplit, o, &any_partial, st);
+    if (rc) return rc;
+    o.update = 1; o.grad_scale = 1.0f / (float)m->dp_world;
     const int parity = (int)(m->step & 1);
-    m->step += 1;
-    const double b1 = m->hyper.beta1, b2 = m->hyper.beta2;
-    o.lr = (float)m->hyper.lr;
-    o.beta1 = (float)b1; o.beta2 = (float)b2; o.eps = (float)m->hyper.eps;
-    o.one_minus_beta1 = (float)(1.0 - b1); o.one_minus_beta2 = (float)(1.0 - b2);
-    if (m->opt_kind == TS_OPT_ADAM) {
-        o.step_size = (float)(m->hyper.lr / (1.0 - pow(b1, (double)m->step)));
-        o.bc2_sqrt = (float)sqrt(1.0 - pow(b2, (double)m->step));
-    }
+    fill_update(m, o);
     DpArgs dp{};
     dp.world = m->dp_world; dp.rank = m->dp_rank; dp.step = (uint32_t)m->step;
     for (int r = 0; r < m->dp_world; ++r) { dp.grads[r] = m->dp_grads[parity][r]; dp.flags[r] = m->dp_flags[r]; }
     ProfScope ps(K_OPT, st);
-    return launch_dp_optimizer(o, dp, m->n_chunks, st);
+    return launch_dp_optimizer(o, dp, m->n_chunks, m->sm_count, st);
 }
 
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
@@ -497,9 +501,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         }
     }
     if (!dp) return run_optimizer(m, nsplit, update, 1.0f, st);
-    rc = run_optimizer(m, nsplit, false, 1.0f, st);          // fold the split partials into this rank's gradient
-    if (rc) return rc;
-    return run_dp_optimizer(m, st);
+    return run_dp_optimizer(m, nsplit, st);
 }
 
 }  // namespace

@@ -96,6 +96,7 @@ struct OptArgs {
     const int32_t *chunk_tensor;
     int kind;
     int update;          // 0: only reduce partials into grads (data-parallel backward)
+    int partial_depth;   // partial rows in flight per thread (4 KiB of shared memory each): 16 for small models, 4 for large ones
     float grad_scale;
     float lr, beta1, beta2, eps, one_minus_beta1, one_minus_beta2, step_size, bc2_sqrt;
 };
@@ -114,11 +115,11 @@ int launch_reduce_partials(float *partials, const ReduceArgs &r, cudaStream_t st
 constexpr int kMaxRanks = 8;
 struct DpArgs {
     const float *grads[kMaxRanks];   // rank r's reduced gradient (flat layout), readable from this GPU
-    uint32_t *flags[kMaxRanks];      // rank r's flag array: entry q = last step whose gradient rank q has published
+    uint32_t *flags[kMaxRanks];      // rank r's flag array: entry q = last step whose gradient rank q has published; [8] arrival ticket
     int world, rank;
     uint32_t step;
 };
-int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cudaStream_t st);
+int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, int sm_count, cudaStream_t st);
 
 int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end = false);
 

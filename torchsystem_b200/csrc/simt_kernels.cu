@@ -559,7 +559,33 @@ __device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc 
     }
 }
 
+// Sum of `nsplit` partial rows at q (row stride `stride`), s ascending: a fixed order. Always whole float4 loads (partial
+// rows are padded past `count`, so a tail thread may read and ignore up to three floats of padding). The loads go
+// through cp.async into this thread's own shared-memory slots, kPartialDepth of them in flight per round, and are
+// added in order afterwards: with plain loads ptxas interleaves the adds with the loads and the in-order issue then
+// pays close to one memory round trip per partial -- and the tensors with one partial per 128-row block (32 at batch
+// 4096) are the critical path of the whole launch.
+constexpr int kPartialDepth = 16;                          // small models; large ones run 4 deep to keep 8 CTAs per SM
+constexpr int kPartialSmem = kPartialDepth * 256 * 16;     // most dynamic shared memory of the optimizer kernels
+__device__ __forceinline__ void sum_partials(const float *q, int64_t stride, int nsplit, float (&g)[4], float4 *slots, int depth) {
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(slots + threadIdx.x);
+    for (int s = 0; s < nsplit; s += depth) {
+#pragma unroll
+        for (int u = 0; u < kPartialDepth; ++u)
+            if (u < depth && s + u < nsplit)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(base + (uint32_t)u * 256u * 16u), "l"(q + (int64_t)(s + u) * stride) : "memory");
+        asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+        for (int u = 0; u < kPartialDepth; ++u)
+            if (u < depth && s + u < nsplit) {
+                const float4 v = slots[u * 256 + threadIdx.x];
+                g[0] += v.x; g[1] += v.y; g[2] += v.z; g[3] += v.w;
+            }
+    }
+}
+
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
+    extern __shared__ float4 slots[];
     pdl_launch_dependents();
     const int tix = p.chunk_tensor[blockIdx.x];     // static map: may be read before the predecessor has finished
     pdl_wait();
@@ -573,27 +599,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
     float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     if (d.nsplit > 0) {
         const float *q = p.partials + d.partial_off + j0;
-        // Always whole float4 loads: partial rows are padded past `count`, so the tail thread may read (and ignore)
-        // up to three floats of padding. Eight loads are in flight per round; a scalar, one-load-per-iteration
-        // tail would serialise a memory round trip per partial. The sum order (s ascending) is fixed.
-        int s = 0;
-        for (; s + 8 <= d.nsplit; s += 8) {
-            float4 v[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const float4 *>(q + (int64_t)(s + u) * d.partial_stride);
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { g[0] += v[u].x; g[1] += v[u].y; g[2] += v[u].z; g[3] += v[u].w; }
-        }
-        if (s < d.nsplit) {
-            float4 v[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-                v[u] = (s + u < d.nsplit) ? *reinterpret_cast<const float4 *>(q + (int64_t)(s + u) * d.partial_stride)
-                                          : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-                if (s + u < d.nsplit) { g[0] += v[u].x; g[1] += v[u].y; g[2] += v[u].z; g[3] += v[u].w; }
-        }
+        sum_partials(q, d.partial_stride, d.nsplit, g, slots, p.partial_depth);
         if (n == 4) *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], g[1], g[2], g[3]);
         else for (int e = 0; e < n; ++e) p.grads[i0 + e] = g[e];
     } else {
@@ -605,15 +611,17 @@ __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
 }
 
 // =====================================================================================
-// Data-parallel optimizer with the gradient all-reduce folded in (no separate collective). Every rank keeps its
-// reduced local gradient in a peer-mapped buffer (NVLink / NVSwitch); this kernel
-//   1. publishes "my gradient of step s is complete" by storing s into every rank's flag array (release, system scope),
-//   2. waits until the local flag array shows step s for every rank,
+// Data-parallel optimizer with the gradient all-reduce folded in (no separate collective, no separate partial-sum
+// launch). Every rank keeps its local gradient in a peer-mapped buffer (NVLink / NVSwitch). This kernel
+//   1. sums the split partials (fixed order) into this rank's peer-visible buffer,
+//   2. publishes "my gradient of step s is complete" into every rank's flag array and waits until the local flag array
+//      shows step s for every rank,
 //   3. reads the same chunk of all `world` gradient buffers straight over the peer mappings, sums them in rank
 //      order (identical order on every rank -> bit-identical replicas), scales by 1/world and applies SGD / Adam.
 // One-shot (every rank reads everything) is the right shape here: the whole gradient is well under 1 MB, so latency,
 // not bandwidth, is what the step pays. Buffers alternate with the step parity, so nobody overwrites a gradient a
-// peer may still be reading (a rank passes step s+1's wait only after every peer finished reading step s).
+// peer may still be reading (a rank passes step s+1's wait only after every peer finished the kernel of step s).
+// Every CTA spins in part 2, so the grid must be co-resident: the launcher caps it and the CTAs loop over chunks.
 // =====================================================================================
 __device__ __forceinline__ uint32_t global_ns32() {
     unsigned long long t;
@@ -621,53 +629,108 @@ __device__ __forceinline__ uint32_t global_ns32() {
     return (uint32_t)t;
 }
 
-__global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp) {
+__global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp, int n_chunks) {
+    extern __shared__ float4 slots[];
     pdl_launch_dependents();
-    uint32_t *trace = dp.flags[dp.rank] + 16;          // spare words of this rank's flag array: a 4-point time trace (ns)
-    if (blockIdx.x == 1 && threadIdx.x == 0) trace[0] = global_ns32();
+    uint32_t *own = dp.flags[dp.rank];
+    uint32_t *trace = own + 16;                        // spare words of this rank's flag array: a 5-point time trace (ns)
+    const bool tracer = blockIdx.x == 1 && threadIdx.x == 0;
+    if (tracer) trace[0] = global_ns32();
     pdl_wait();
-    if (blockIdx.x == 1 && threadIdx.x == 0) trace[1] = global_ns32();
-    if (blockIdx.x == 0 && threadIdx.x < dp.world) {
-        // This rank's gradient was written by the previous kernel in the stream, so it is already visible to peers;
-        // a release store orders the flag behind it. (A full system fence here cost ~10 us per step.)
-        uint32_t *peer_flag = dp.flags[threadIdx.x] + dp.rank;
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(peer_flag), "r"(dp.step) : "memory");
+    if (tracer) trace[1] = global_ns32();
+
+    // 1. local gradient: sum the split partials of this CTA's chunks into the peer-visible buffer (p.grads is this
+    //    rank's buffer of this step's parity)
+    for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const int tix = p.chunk_tensor[chunk];
+        if (tix < 0) continue;
+        const TensorDesc d = p.t[tix];
+        const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+        const int64_t j0 = i0 - d.offset;
+        if (j0 >= d.count || d.nsplit <= 0) continue;
+        const int n = (int)min((int64_t)4, d.count - j0);
+        const float *q = p.partials + d.partial_off + j0;
+        float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        sum_partials(q, d.partial_stride, d.nsplit, g, slots, p.partial_depth);
+        // padding lanes (e >= n) carry zeros: the flat buffers are padded to whole chunks
+        *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], n > 1 ? g[1] : 0.0f, n > 2 ? g[2] : 0.0f, n > 3 ? g[3] : 0.0f);
+    }
+
+    // 2. one handshake per step: the last CTA of this rank to finish part 1 publishes "my gradient of step s is
+    //    complete" into every rank's flag array (release, system scope). Per-CTA system-scope releases, or a full system
+    //    fence in every CTA, cost several microseconds each while the next batch's cast streams through the same SMs.
+    __shared__ bool s_last;
+    __syncthreads();
+    if (tracer) trace[5] = global_ns32();
+    if (threadIdx.x == 0) {
+        __threadfence();                                           // this CTA's gradient stores before its ticket
+        const uint32_t arrived = atomicAdd(own + 8, 1u);
+        s_last = arrived == gridDim.x - 1;
+        if (s_last) { own[8] = 0u; trace[6] = global_ns32(); }     // next step's kernel starts from zero
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < dp.world) {
+        // one thread per destination rank: the system-scope releases (a few microseconds each) run side by side
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dp.flags[threadIdx.x] + dp.rank), "r"(dp.step) : "memory");
+        if (threadIdx.x == 0) trace[7] = global_ns32();
     }
     if (threadIdx.x < dp.world) {
-        const uint32_t *mine = dp.flags[dp.rank] + threadIdx.x;
+        const uint32_t *mine = own + threadIdx.x;
         uint32_t spins = 0, seen;
         for (;;) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
             if ((int32_t)(seen - dp.step) >= 0) break;
             __nanosleep(32);
-            if (++spins > (1u << 25)) __trap();                  // a peer never arrived: fail loudly instead of hanging
+            if (++spins > (1u << 25)) __trap();                    // a peer never arrived: fail loudly instead of hanging
         }
     }
     __syncthreads();
-    if (blockIdx.x == 1 && threadIdx.x == 0) trace[2] = global_ns32();
+    if (tracer) trace[2] = global_ns32();
 
-    const int tix = p.chunk_tensor[blockIdx.x];
-    if (tix < 0) return;
-    const TensorDesc d = p.t[tix];
-    const int64_t i0 = (int64_t)blockIdx.x * kChunk + threadIdx.x * 4;
-    const int64_t j0 = i0 - d.offset;
-    if (j0 >= d.count) return;
-    const int n = (int)min((int64_t)4, d.count - j0);
-    float4 v[8];
+    // 3. all ranks' gradient chunk in rank order (identical order on every rank), scaled update
+    for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const int tix = p.chunk_tensor[chunk];
+        if (tix < 0) continue;
+        const TensorDesc d = p.t[tix];
+        const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+        const int64_t j0 = i0 - d.offset;
+        if (j0 >= d.count) continue;
+        const int n = (int)min((int64_t)4, d.count - j0);
+        float4 v[8];
 #pragma unroll
-    for (int r = 0; r < 8; ++r)       // flat buffers are padded to whole chunks: the float4 is always in bounds
-        v[r] = (r < dp.world) ? __ldcv(reinterpret_cast<const float4 *>(dp.grads[r] + i0)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        for (int r = 0; r < 8; ++r)   // flat buffers are padded to whole chunks: the float4 is always in bounds
+            v[r] = (r < dp.world) ? __ldcv(reinterpret_cast<const float4 *>(dp.grads[r] + i0)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
-    for (int r = 0; r < 8; ++r)
-        if (r < dp.world) { g[0] += v[r].x; g[1] += v[r].y; g[2] += v[r].z; g[3] += v[r].w; }
-    if (blockIdx.x == 1 && threadIdx.x == 0) trace[3] = global_ns32();
-    apply_update(p, d, i0, j0, n, g);
-    if (blockIdx.x == 1 && threadIdx.x == 0) trace[4] = global_ns32();
+        for (int r = 0; r < 8; ++r)
+            if (r < dp.world) { g[0] += v[r].x; g[1] += v[r].y; g[2] += v[r].z; g[3] += v[r].w; }
+        if (tracer && chunk == 1) trace[3] = global_ns32();
+        apply_update(p, d, i0, j0, n, g);
+        if (tracer && chunk == 1) trace[4] = global_ns32();
+    }
 }
 
-int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, cudaStream_t st) {
-    TS_CUDA_CHECK(launch_pdl(dp_optimizer_kernel, dim3((unsigned)n_chunks), dim3(256), 0, st, 1, a, dp));
+// 64 KiB of dynamic shared memory needs the opt-in attribute, once per device.
+static int ensure_optimizer_smem() {
+    static bool done[64] = {false};
+    int dev = 0;
+    TS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!done[dev & 63]) {
+        TS_CUDA_CHECK(cudaFuncSetAttribute(dp_optimizer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPartialSmem));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(optimizer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPartialSmem));
+        done[dev & 63] = true;
+    }
+    return TS_OK;
+}
+
+int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, int sm_count, cudaStream_t st) {
+    // every CTA must be resident at once (they wait for each other and for the peer GPUs): with up to 64 KiB of shared
+    // memory each 3 per SM fit; 2 leaves room for the early-running cast of the next batch
+    int64_t grid = (int64_t)sm_count * 2;
+    if (grid > n_chunks) grid = n_chunks;
+    int rc = ensure_optimizer_smem();
+    if (rc) return rc;
+    TS_CUDA_CHECK(launch_pdl(dp_optimizer_kernel, dim3((unsigned)grid), dim3(256), (size_t)a.partial_depth * 4096, st, 1, a, dp, (int)n_chunks));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
@@ -710,7 +773,9 @@ int launch_reduce_partials(float *partials, const ReduceArgs &r, cudaStream_t st
 }
 
 int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st) {
-    TS_CUDA_CHECK(launch_pdl(optimizer_kernel, dim3((unsigned)n_chunks), dim3(256), 0, st, 1, a));
+    int rc = ensure_optimizer_smem();
+    if (rc) return rc;
+    TS_CUDA_CHECK(launch_pdl(optimizer_kernel, dim3((unsigned)n_chunks), dim3(256), (size_t)a.partial_depth * 4096, st, 1, a));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }

@@ -56,7 +56,7 @@ def bind_peer_gradients(engine, params, dp: DataParallel):
     dev, total = engine.device, engine.total
     with torch.cuda.device(engine.index):
         gbuf = symm.empty(2 * total, dtype=torch.float32, device=dev)
-        flags = symm.empty(64, dtype=torch.int32, device=dev)
+        flags = symm.empty(64, dtype=torch.int32, device=dev)      # TS_DP_FLAG_WORDS, see include/tsb200.h ts_dp_bind
         gbuf.zero_()
         flags.zero_()
         hg = symm.rendezvous(gbuf, group)
