@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define TS_ABI_VERSION 1
+#define TS_ABI_VERSION 2
 
 /* status codes */
 #define TS_OK 0
@@ -57,11 +57,19 @@ extern "C" {
 
 typedef struct ts_mlp ts_mlp; /* opaque aggregate handle */
 
-/* Hyper-parameters, torch.optim semantics (momentum/weight decay/amsgrad not supported: 0). */
+/* Hyper-parameters, torch.optim semantics (torch/optim/adam.py _single_tensor_adam, sgd.py _single_tensor_sgd);
+ * `maximize` is not supported. Zero-initialise the struct: every field after `eps` defaults to "off". */
 typedef struct ts_opt_hyper {
     double lr;
-    double beta1, beta2; /* Adam only */
-    double eps;          /* Adam only */
+    double beta1, beta2;     /* Adam only */
+    double eps;              /* Adam only */
+    double weight_decay;     /* SGD and Adam: grad += weight_decay * param (or decoupled, see below) */
+    double momentum;         /* SGD: momentum buffer lives in the `exp_avg` array given to ts_opt_bind */
+    double dampening;        /* SGD */
+    int32_t nesterov;        /* SGD */
+    int32_t amsgrad;         /* Adam: needs the `max_exp_avg_sq` array */
+    int32_t decoupled_weight_decay; /* Adam: param *= 1 - lr * weight_decay instead (AdamW) */
+    int32_t reserved;
 } ts_opt_hyper;
 
 /* One record per fit/evaluate call, written by the fused head kernel (16 bytes, device memory).
@@ -101,10 +109,13 @@ int32_t ts_mlp_param_layout(const ts_mlp *m, int64_t *offsets /*HOST*/, int64_t 
 /* Alias the caller's parameter and gradient storage (fp32 master weights stay where torch sees them). */
 int32_t ts_mlp_bind_params(ts_mlp *m, float *params, float *grads);
 
-/* replaces torch.optim.Adam/SGD construction (examples/tinysys/main.py:62); moments may be NULL for SGD.
- * `step` is the number of optimizer steps already taken (resume). */
+/* replaces torch.optim.Adam/AdamW/SGD construction (examples/tinysys/main.py:62). State arrays are flat like the
+ * parameters: `exp_avg` (Adam's first moment, or SGD's momentum buffer when momentum != 0), `exp_avg_sq` (Adam),
+ * `max_exp_avg_sq` (Adam with amsgrad); the ones a configuration does not use may be NULL.
+ * `step` is the number of optimizer steps already taken (resume; SGD with momentum copies the first gradient into
+ * the momentum buffer when step == 0, as torch does for a missing buffer). */
 int32_t ts_opt_bind(ts_mlp *m, int32_t kind, const ts_opt_hyper *hyper /*HOST*/, float *exp_avg, float *exp_avg_sq,
-                    int64_t step);
+                    float *max_exp_avg_sq, int64_t step);
 int64_t ts_opt_step_count(const ts_mlp *m);
 
 int64_t ts_mlp_workspace_bytes(const ts_mlp *m, int64_t max_batch);

@@ -25,7 +25,8 @@ algorithms are restated below:
 * CrossEntropyLoss: mean_i(logsumexp(z_i) - z_i[y_i])
 * argmax(dim=1):    first maximum wins on ties
 * Adam:             torch/optim/adam.py `_single_tensor_adam` (non-capturable branch)
-* SGD:              torch/optim/sgd.py `_single_tensor_sgd` (momentum 0)
+* SGD:              torch/optim/sgd.py `_single_tensor_sgd` (weight decay, momentum, dampening, Nesterov)
+*                   Adam also with weight decay (L2 or decoupled = AdamW) and amsgrad
 * Mean:             fp64 weighted_sum += loss, weights += 1 ; compute = sum / weights
 * MulticlassAccuracy(micro): num_correct += (pred == tgt).sum(), num_total += B
 
@@ -99,10 +100,18 @@ class OracleMLP:
     lr: float = 1e-3
     betas: tuple[float, float] = (0.9, 0.999)
     eps: float = 1e-8
+    weight_decay: float = 0.0
+    decoupled_weight_decay: bool = False   # AdamW (adam.py:417-419)
+    amsgrad: bool = False
+    momentum: float = 0.0                  # SGD (sgd.py:358-372)
+    dampening: float = 0.0
+    nesterov: bool = False
     emulate_bf16: bool = False
     step: int = 0
     exp_avg: list[np.ndarray] = field(default_factory=list)
     exp_avg_sq: list[np.ndarray] = field(default_factory=list)
+    max_exp_avg_sq: list[np.ndarray] = field(default_factory=list)
+    momentum_buffer: list = field(default_factory=list)      # None until the first step, like torch
 
     def __post_init__(self):
         self.weights = [np.array(w, dtype=np.float32) for w in self.weights]
@@ -110,6 +119,10 @@ class OracleMLP:
         if not self.exp_avg:
             self.exp_avg = [np.zeros_like(p) for p in self.parameters()]
             self.exp_avg_sq = [np.zeros_like(p) for p in self.parameters()]
+        if not self.max_exp_avg_sq:
+            self.max_exp_avg_sq = [np.zeros_like(p) for p in self.parameters()]
+        if not self.momentum_buffer:
+            self.momentum_buffer = [None for _ in self.parameters()]
 
     def parameters(self) -> list[np.ndarray]:
         """torch order: layer0.weight, layer0.bias, layer1.weight, ... (mlp.py:8-11)."""
@@ -196,21 +209,43 @@ class OracleMLP:
     def _optimizer_step(self, grads: list[np.ndarray]):
         self.step += 1
         params = self.parameters()
-        if self.opt_kind == OPT_SGD:
-            for p, g in zip(params, grads):
-                p -= np.float32(self.lr) * g  # param.add_(grad, alpha=-lr)
+        f = np.float32
+        wd = self.weight_decay
+        if self.opt_kind == OPT_SGD:                                   # sgd.py _single_tensor_sgd
+            for i, (p, g) in enumerate(zip(params, grads)):
+                if wd != 0:
+                    g = g + f(wd) * p                                  # grad.add(param, alpha=weight_decay)
+                if self.momentum != 0:
+                    buf = self.momentum_buffer[i]
+                    if buf is None:
+                        buf = g.copy()                                 # first step: clone(grad)
+                    else:
+                        buf *= f(self.momentum)
+                        buf += f(1.0 - self.dampening) * g             # buf.mul_(momentum).add_(grad, alpha=1-dampening)
+                    self.momentum_buffer[i] = buf
+                    g = g + f(self.momentum) * buf if self.nesterov else buf
+                p -= f(self.lr) * g                                    # param.add_(grad, alpha=-lr)
             return
         b1, b2 = self.betas
         bc1 = 1.0 - b1 ** self.step
         bc2 = 1.0 - b2 ** self.step
         step_size = self.lr / bc1
         bc2_sqrt = bc2 ** 0.5
-        for p, g, m, v in zip(params, grads, self.exp_avg, self.exp_avg_sq):
-            m += (g - m) * np.float32(1.0 - b1)                       # exp_avg.lerp_(grad, 1-beta1)
-            v *= np.float32(b2)
-            v += np.float32(1.0 - b2) * g * g                         # mul_(beta2).addcmul_(g, g, 1-beta2)
-            denom = np.sqrt(v) / np.float32(bc2_sqrt) + np.float32(self.eps)
-            p -= np.float32(step_size) * (m / denom)                  # addcdiv_(m, denom, -step_size)
+        for p, g, m, v, mx in zip(params, grads, self.exp_avg, self.exp_avg_sq, self.max_exp_avg_sq):
+            if wd != 0:
+                if self.decoupled_weight_decay:
+                    p *= f(1.0 - self.lr * wd)                         # param.mul_(1 - lr * weight_decay)
+                else:
+                    g = g + f(wd) * p
+            m += (g - m) * f(1.0 - b1)                                 # exp_avg.lerp_(grad, 1-beta1)
+            v *= f(b2)
+            v += f(1.0 - b2) * g * g                                   # mul_(beta2).addcmul_(g, g, 1-beta2)
+            if self.amsgrad:
+                np.maximum(mx, v, out=mx)                              # torch.maximum(max_exp_avg_sq, exp_avg_sq)
+                denom = np.sqrt(mx) / f(bc2_sqrt) + f(self.eps)
+            else:
+                denom = np.sqrt(v) / f(bc2_sqrt) + f(self.eps)
+            p -= f(step_size) * (m / denom)                            # addcdiv_(m, denom, -step_size)
 
 
 class OracleMetrics:

@@ -265,7 +265,9 @@ def test_errors_are_loud():
     with pytest.raises(TypeError):
         B200Classifier(net, nn.MSELoss(), torch.optim.SGD(net.parameters(), lr=0.1), device='cuda:0')
     with pytest.raises(NotImplementedError):
-        B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.1, momentum=0.9), device='cuda:0')
+        B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.1, maximize=True), device='cuda:0')
+    with pytest.raises(TypeError):
+        B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.RMSprop(net.parameters(), lr=0.1), device='cuda:0')
     with pytest.raises(TypeError):
         B200Classifier(nn.Sequential(nn.Linear(4, 4), nn.Tanh(), nn.Linear(4, 2)), nn.CrossEntropyLoss(),
                        torch.optim.SGD(net.parameters(), lr=0.1), device='cuda:0')

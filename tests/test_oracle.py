@@ -104,3 +104,48 @@ def test_metrics_semantics_mean_of_batch_means():
     assert r['loss'] == 2.0 and r['accuracy'] == 0.75
     m.reset()
     assert m.compute()['loss'] == 0.0
+
+
+OPT_VARIANTS = {
+    'sgd_wd': ('sgd', dict(lr=0.05, weight_decay=1e-2)),
+    'sgd_momentum': ('sgd', dict(lr=0.05, momentum=0.9)),
+    'sgd_momentum_dampening_wd': ('sgd', dict(lr=0.05, momentum=0.8, dampening=0.3, weight_decay=1e-3)),
+    'sgd_nesterov': ('sgd', dict(lr=0.05, momentum=0.9, nesterov=True)),
+    'adam_wd': ('adam', dict(lr=1e-3, weight_decay=1e-2)),
+    'adam_amsgrad': ('adam', dict(lr=1e-3, amsgrad=True)),
+    'adamw': ('adamw', dict(lr=1e-3, weight_decay=1e-1)),
+    'adamw_amsgrad': ('adamw', dict(lr=1e-3, weight_decay=1e-1, amsgrad=True, betas=(0.8, 0.99))),
+}
+
+
+def torch_optimizer(kind, params, hyper):
+    return {'sgd': torch.optim.SGD, 'adam': torch.optim.Adam, 'adamw': torch.optim.AdamW}[kind](params, **hyper)
+
+
+def oracle_hyper(kind, hyper):
+    h = dict(hyper)
+    h['opt_kind'] = onp.OPT_SGD if kind == 'sgd' else onp.OPT_ADAM
+    if kind == 'adamw':
+        h['decoupled_weight_decay'] = True
+    return h
+
+
+@pytest.mark.parametrize('name', sorted(OPT_VARIANTS))
+def test_oracle_optimizer_variants_match_torch_optim(name):
+    """Pins the restated SGD (weight decay, momentum, dampening, Nesterov) and Adam / AdamW (weight decay, amsgrad)
+    updates to torch.optim's single-tensor CPU path on the same gradient sequence (5 steps)."""
+    kind, hyper = OPT_VARIANTS[name]
+    g = torch.Generator().manual_seed(7)
+    shapes = [(16, 24), (16,), (10, 16), (10,)]
+    params = [torch.nn.Parameter(torch.randn(s, generator=g)) for s in shapes]
+    opt = torch_optimizer(kind, params, dict(hyper, foreach=False))
+    oracle = onp.OracleMLP(weights=[params[0].detach().numpy(), params[2].detach().numpy()],
+                           biases=[params[1].detach().numpy(), params[3].detach().numpy()], **oracle_hyper(kind, hyper))
+    for _ in range(5):
+        grads = [torch.randn(s, generator=g) * 0.1 for s in shapes]
+        for p, gr in zip(params, grads):
+            p.grad = gr.clone()
+        opt.step()
+        oracle._optimizer_step([gr.numpy().copy() for gr in grads])
+        for p, q in zip(params, oracle.parameters()):
+            np.testing.assert_allclose(q, p.detach().numpy(), rtol=2e-6, atol=1e-7)

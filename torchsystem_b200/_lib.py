@@ -19,7 +19,9 @@ STATE_BYTES = 32
 
 
 class OptHyper(C.Structure):
-    _fields_ = [('lr', C.c_double), ('beta1', C.c_double), ('beta2', C.c_double), ('eps', C.c_double)]
+    _fields_ = [('lr', C.c_double), ('beta1', C.c_double), ('beta2', C.c_double), ('eps', C.c_double),
+                ('weight_decay', C.c_double), ('momentum', C.c_double), ('dampening', C.c_double),
+                ('nesterov', C.c_int32), ('amsgrad', C.c_int32), ('decoupled_weight_decay', C.c_int32), ('reserved', C.c_int32)]
 
 
 class MetricsState(C.Structure):
@@ -39,7 +41,7 @@ PROTOTYPES = {
     'ts_mlp_destroy': (C.c_int32, [C.c_void_p]),
     'ts_mlp_param_layout': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     'ts_mlp_bind_params': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p]),
-    'ts_opt_bind': (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(OptHyper), C.c_void_p, C.c_void_p, C.c_int64]),
+    'ts_opt_bind': (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(OptHyper), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     'ts_opt_step_count': (C.c_int64, [C.c_void_p]),
     'ts_dp_bind': (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     'ts_mlp_workspace_bytes': (C.c_int64, [C.c_void_p, C.c_int64]),

@@ -29,18 +29,23 @@ def _check_criterion(criterion: nn.Module) -> None:
 
 
 def _optimizer_config(optimizer: torch.optim.Optimizer):
+    """(kind, hyper-parameters) of a torch.optim.SGD / Adam / AdamW with one param group, as the fused optimizer takes
+    them (torch/optim/sgd.py _single_tensor_sgd, adam.py _single_tensor_adam)."""
     if len(optimizer.param_groups) != 1:
         raise TypeError('exactly one optimizer param group is supported')
     g = optimizer.param_groups[0]
-    if isinstance(optimizer, torch.optim.Adam) and type(optimizer) is torch.optim.Adam:
-        if g.get('weight_decay', 0) != 0 or g.get('amsgrad', False) or g.get('maximize', False):
-            raise NotImplementedError('Adam weight_decay / amsgrad / maximize are not supported by the fused optimizer')
-        return 'adam', dict(lr=float(g['lr']), betas=tuple(float(b) for b in g['betas']), eps=float(g['eps']))
+    if g.get('maximize', False):
+        raise NotImplementedError('maximize=True is not supported by the fused optimizer')
+    if type(optimizer) in (torch.optim.Adam, torch.optim.AdamW):
+        decoupled = bool(g.get('decoupled_weight_decay', type(optimizer) is torch.optim.AdamW))
+        return 'adam', dict(lr=float(g['lr']), betas=tuple(float(b) for b in g['betas']), eps=float(g['eps']),
+                            weight_decay=float(g.get('weight_decay', 0.0)), amsgrad=bool(g.get('amsgrad', False)),
+                            decoupled_weight_decay=decoupled)
     if type(optimizer) is torch.optim.SGD:
-        if g.get('momentum', 0) != 0 or g.get('weight_decay', 0) != 0 or g.get('nesterov', False) or g.get('maximize', False):
-            raise NotImplementedError('SGD momentum / weight_decay / nesterov / maximize are not supported by the fused optimizer')
-        return 'sgd', dict(lr=float(g['lr']))
-    raise TypeError(f'unsupported optimizer {type(optimizer).__name__}: the fused step implements Adam and SGD')
+        return 'sgd', dict(lr=float(g['lr']), weight_decay=float(g.get('weight_decay', 0.0)),
+                           momentum=float(g.get('momentum', 0.0)), dampening=float(g.get('dampening', 0.0)),
+                           nesterov=bool(g.get('nesterov', False)))
+    raise TypeError(f'unsupported optimizer {type(optimizer).__name__}: the fused step implements SGD, Adam and AdamW')
 
 
 class B200Classifier(Aggregate):
@@ -77,7 +82,7 @@ class B200Classifier(Aggregate):
         nn.to(dev)
         self.engine = Engine(spec, precision, dev, max_batch=max_batch)
         self.engine.adopt(self._params)
-        step = self._adopt_optimizer_state(kind)
+        step = self._adopt_optimizer_state(kind, hyper)
         self.engine.bind_optimizer(kind, step=step, **hyper)
         self._dp = parallel.DataParallel(process_group)
         self._p2p = None
@@ -100,25 +105,36 @@ class B200Classifier(Aggregate):
         """Call after editing `nn`'s weights by hand; re-derives the bf16 operand copies."""
         self.engine.sync_weights()
 
-    def _adopt_optimizer_state(self, kind: str) -> int:
-        """Resume: take over exp_avg / exp_avg_sq / step if the torch optimizer already holds state, and make
-        the optimizer's state dict alias the engine's buffers from now on."""
-        step = 0
-        if kind != 'adam':
-            return step
+    def _adopt_optimizer_state(self, kind: str, hyper: dict) -> int:
+        """Resume: take over the state the torch optimizer already holds (Adam: exp_avg / exp_avg_sq / max_exp_avg_sq /
+        step; SGD: momentum_buffer) and make the optimizer's state dict alias the engine's flat buffers from now on."""
         eng = self.engine
-        eng.exp_avg = torch.zeros_like(eng.params)
-        eng.exp_avg_sq = torch.zeros_like(eng.params)
+        step = 0
+        if kind == 'adam':
+            names = ['exp_avg', 'exp_avg_sq'] + (['max_exp_avg_sq'] if hyper['amsgrad'] else [])
+        elif hyper['momentum'] != 0:
+            names = ['momentum_buffer']
+        else:
+            return step
+        flat = {n: torch.zeros_like(eng.params) for n in names}
         for i, p in enumerate(self._params):
             o, n = eng.offsets[i], p.numel()
             st = self.optimizer.state.get(p, {})
-            if 'exp_avg' in st:
-                eng.exp_avg[o:o + n].copy_(st['exp_avg'].reshape(-1))
-                eng.exp_avg_sq[o:o + n].copy_(st['exp_avg_sq'].reshape(-1))
-                step = int(st['step']) if not isinstance(st['step'], Tensor) else int(st['step'].item())
-            self.optimizer.state[p] = {'step': torch.tensor(float(step)),
-                                       'exp_avg': eng.exp_avg[o:o + n].view(p.shape),
-                                       'exp_avg_sq': eng.exp_avg_sq[o:o + n].view(p.shape)}
+            have = all(st.get(k) is not None for k in names)
+            if have:
+                for k in names:
+                    flat[k][o:o + n].copy_(st[k].reshape(-1))
+                if kind == 'adam':
+                    step = int(st['step']) if not isinstance(st['step'], Tensor) else int(st['step'].item())
+                else:
+                    step = max(step, 1)          # a momentum buffer exists: not the first step any more
+            new = {k: flat[k][o:o + n].view(p.shape) for k in names}
+            if kind == 'adam':
+                new['step'] = torch.tensor(float(step))
+            self.optimizer.state[p] = new
+        eng.exp_avg = flat.get('exp_avg', flat.get('momentum_buffer'))
+        eng.exp_avg_sq = flat.get('exp_avg_sq')
+        eng.max_exp_avg_sq = flat.get('max_exp_avg_sq')
         return step
 
     def sync_optimizer_state(self) -> None:
@@ -131,9 +147,7 @@ class B200Classifier(Aggregate):
 
     def _refresh_hyper(self) -> None:
         kind, hyper = _optimizer_config(self.optimizer)      # follows lr schedulers / manual edits
-        want = (kind, hyper['lr'], tuple(hyper.get('betas', (0.9, 0.999))), hyper.get('eps', 1e-8))
-        if want != self.engine._hyper:
-            self.engine.bind_optimizer(kind, step=self.engine.step_count, **hyper)
+        self.engine.bind_optimizer(kind, step=self.engine.step_count, **hyper)
 
     # ------------------------------------------------------------------ the hot path
     def forward(self, input: Tensor) -> Tensor:

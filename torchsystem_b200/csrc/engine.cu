@@ -71,7 +71,7 @@ struct ts_mlp {
     bool opt_bound = false;
     int opt_kind = TS_OPT_SGD;
     ts_opt_hyper hyper = {0, 0, 0, 0};
-    float *exp_avg = nullptr, *exp_avg_sq = nullptr;
+    float *exp_avg = nullptr, *exp_avg_sq = nullptr, *max_exp_avg_sq = nullptr;
     int64_t step = 0;
 
     // workspace (caller-owned memory)
@@ -271,6 +271,7 @@ int fill_tensor_table(ts_mlp *m, const int *nsplit, OptArgs &o, bool *any_partia
         if (rc) return rc;
     }
     o.params = m->params; o.grads = m->grads; o.exp_avg = m->exp_avg; o.exp_avg_sq = m->exp_avg_sq;
+    o.max_exp_avg_sq = m->max_exp_avg_sq;
     o.partials = m->partials; o.shadow = m->shadow; o.chunk_tensor = m->d_chunk_tensor;
     o.kind = m->opt_kind;
     o.partial_depth = m->n_chunks <= 3 * (int64_t)m->sm_count ? 16 : 4;
@@ -279,7 +280,13 @@ int fill_tensor_table(ts_mlp *m, const int *nsplit, OptArgs &o, bool *any_partia
 
 // Advances the step counter and fills the hyper-parameters of one update.
 void fill_update(ts_mlp *m, OptArgs &o) {
+    o.first_step = m->step == 0 ? 1 : 0;
     m->step += 1;
+    o.weight_decay = (float)m->hyper.weight_decay;
+    o.wd_mul = (float)(1.0 - m->hyper.lr * m->hyper.weight_decay);
+    o.momentum = (float)m->hyper.momentum;
+    o.one_minus_dampening = (float)(1.0 - m->hyper.dampening);
+    o.nesterov = m->hyper.nesterov; o.amsgrad = m->hyper.amsgrad; o.decoupled = m->hyper.decoupled_weight_decay;
     const double b1 = m->hyper.beta1, b2 = m->hyper.beta2;
     o.lr = (float)m->hyper.lr;
     o.beta1 = (float)b1; o.beta2 = (float)b2; o.eps = (float)m->hyper.eps;
@@ -593,12 +600,20 @@ int32_t ts_mlp_bind_params(ts_mlp *m, float *params, float *grads) {
     return TS_OK;
 }
 
-int32_t ts_opt_bind(ts_mlp *m, int32_t kind, const ts_opt_hyper *hyper, float *exp_avg, float *exp_avg_sq, int64_t step) {
+int32_t ts_opt_bind(ts_mlp *m, int32_t kind, const ts_opt_hyper *hyper, float *exp_avg, float *exp_avg_sq,
+                    float *max_exp_avg_sq, int64_t step) {
     TS_REQUIRE(m && hyper, TS_E_INVALID, "null argument");
     TS_REQUIRE(kind == TS_OPT_SGD || kind == TS_OPT_ADAM, TS_E_INVALID, "unknown optimizer kind %d", kind);
     TS_REQUIRE(kind == TS_OPT_SGD || (exp_avg && exp_avg_sq), TS_E_INVALID, "Adam needs exp_avg and exp_avg_sq buffers");
+    TS_REQUIRE(kind != TS_OPT_ADAM || !hyper->amsgrad || max_exp_avg_sq, TS_E_INVALID, "amsgrad needs the max_exp_avg_sq buffer");
+    TS_REQUIRE(kind != TS_OPT_SGD || hyper->momentum == 0.0 || exp_avg, TS_E_INVALID,
+               "SGD with momentum needs the momentum buffer (exp_avg argument)");
+    TS_REQUIRE(hyper->weight_decay >= 0.0 && hyper->momentum >= 0.0, TS_E_INVALID, "negative weight_decay or momentum");
+    TS_REQUIRE(!hyper->nesterov || (hyper->momentum > 0.0 && hyper->dampening == 0.0), TS_E_INVALID,
+               "Nesterov momentum requires a momentum and zero dampening");     // torch/optim/sgd.py __init__
     TS_REQUIRE(step >= 0, TS_E_INVALID, "negative step");
-    m->opt_kind = kind; m->hyper = *hyper; m->exp_avg = exp_avg; m->exp_avg_sq = exp_avg_sq; m->step = step;
+    m->opt_kind = kind; m->hyper = *hyper; m->exp_avg = exp_avg; m->exp_avg_sq = exp_avg_sq; m->max_exp_avg_sq = max_exp_avg_sq;
+    m->step = step;
     m->opt_bound = true;
     return TS_OK;
 }

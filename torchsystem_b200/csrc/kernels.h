@@ -90,7 +90,7 @@ struct TensorDesc {
 struct OptArgs {
     TensorDesc t[2 * kMaxLayers];
     int n_tensors;
-    float *params, *grads, *exp_avg, *exp_avg_sq;
+    float *params, *grads, *exp_avg, *exp_avg_sq, *max_exp_avg_sq;
     const float *partials;
     __nv_bfloat16 *shadow;
     const int32_t *chunk_tensor;
@@ -99,6 +99,8 @@ struct OptArgs {
     int partial_depth;   // partial rows in flight per thread (4 KiB of shared memory each): 16 for small models, 4 for large ones
     float grad_scale;
     float lr, beta1, beta2, eps, one_minus_beta1, one_minus_beta2, step_size, bc2_sqrt;
+    float weight_decay, wd_mul /* 1 - lr * weight_decay (decoupled) */, momentum, one_minus_dampening;
+    int nesterov, amsgrad, decoupled, first_step /* SGD momentum: buffer := grad */;
 };
 int launch_optimizer(const OptArgs &a, int64_t n_chunks, cudaStream_t st);
 

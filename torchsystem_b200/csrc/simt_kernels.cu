@@ -519,32 +519,45 @@ __device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc 
     // Whole float4 accesses (the flat buffers are padded to 1024-element chunks and i0 is a multiple of 4); all
     // loads are issued before the first use, the padding lanes (e >= n) are written back unchanged.
     const float4 w4 = *reinterpret_cast<const float4 *>(p.params + i0);
-    float4 m4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), v4 = m4;
+    float4 m4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), v4 = m4, x4 = m4;
     const bool adam = p.kind != TS_OPT_SGD;
-    if (adam) {
-        m4 = *reinterpret_cast<const float4 *>(p.exp_avg + i0);
-        v4 = *reinterpret_cast<const float4 *>(p.exp_avg_sq + i0);
-    }
+    const bool use_m = adam || p.momentum != 0.0f;       // exp_avg doubles as SGD's momentum buffer
+    const bool use_x = adam && p.amsgrad;
+    if (use_m) m4 = *reinterpret_cast<const float4 *>(p.exp_avg + i0);
+    if (adam) v4 = *reinterpret_cast<const float4 *>(p.exp_avg_sq + i0);
+    if (use_x) x4 = *reinterpret_cast<const float4 *>(p.max_exp_avg_sq + i0);
     float w[4] = {w4.x, w4.y, w4.z, w4.w}, m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
+    float x[4] = {x4.x, x4.y, x4.z, x4.w};
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
         if (e >= n) continue;
-        const float grad = g[e] * p.grad_scale;
-        if (!adam) {
+        float grad = g[e] * p.grad_scale;
+        if (!adam) {                                                       // sgd.py _single_tensor_sgd
+            if (p.weight_decay != 0.0f) grad = grad + p.weight_decay * w[e];   // grad.add(param, alpha=weight_decay)
+            if (p.momentum != 0.0f) {
+                // buf = clone(grad) on the first step, else buf.mul_(momentum).add_(grad, alpha=1 - dampening)
+                m[e] = p.first_step ? grad : m[e] * p.momentum + p.one_minus_dampening * grad;
+                grad = p.nesterov ? grad + p.momentum * m[e] : m[e];
+            }
             w[e] = w[e] - p.lr * grad;                                     // param.add_(grad, alpha=-lr)
-        } else {
+        } else {                                                           // adam.py _single_tensor_adam
+            if (p.weight_decay != 0.0f) {
+                if (p.decoupled) w[e] = w[e] * p.wd_mul;                   // param.mul_(1 - lr * weight_decay)   (AdamW)
+                else grad = grad + p.weight_decay * w[e];
+            }
             m[e] = m[e] + p.one_minus_beta1 * (grad - m[e]);               // exp_avg.lerp_(grad, 1 - beta1)
             v[e] = v[e] * p.beta2;                                         // exp_avg_sq.mul_(beta2)
             v[e] = v[e] + p.one_minus_beta2 * (grad * grad);               //   .addcmul_(grad, grad, value=1 - beta2)
-            const float denom = sqrtf(v[e]) / p.bc2_sqrt + p.eps;          // (sqrt(v) / sqrt(bias_correction2)).add_(eps)
+            float second = v[e];
+            if (p.amsgrad) { x[e] = fmaxf(x[e], v[e]); second = x[e]; }    // torch.maximum(max_exp_avg_sq, exp_avg_sq)
+            const float denom = sqrtf(second) / p.bc2_sqrt + p.eps;        // (sqrt(.) / sqrt(bias_correction2)).add_(eps)
             w[e] = w[e] - p.step_size * (m[e] / denom);                    // param.addcdiv_(exp_avg, denom, value=-step_size)
         }
     }
     *reinterpret_cast<float4 *>(p.params + i0) = make_float4(w[0], w[1], w[2], w[3]);
-    if (adam) {
-        *reinterpret_cast<float4 *>(p.exp_avg + i0) = make_float4(m[0], m[1], m[2], m[3]);
-        *reinterpret_cast<float4 *>(p.exp_avg_sq + i0) = make_float4(v[0], v[1], v[2], v[3]);
-    }
+    if (use_m) *reinterpret_cast<float4 *>(p.exp_avg + i0) = make_float4(m[0], m[1], m[2], m[3]);
+    if (adam) *reinterpret_cast<float4 *>(p.exp_avg_sq + i0) = make_float4(v[0], v[1], v[2], v[3]);
+    if (use_x) *reinterpret_cast<float4 *>(p.max_exp_avg_sq + i0) = make_float4(x[0], x[1], x[2], x[3]);
     if (d.shadow_off >= 0 && p.shadow != nullptr) {
         __nv_bfloat16 *sh = p.shadow + d.shadow_off + j0;
         if (n == 4 && (((uintptr_t)sh) & 7) == 0) {

@@ -36,7 +36,7 @@ class Engine:
         with torch.cuda.device(self.index):
             self.params = torch.zeros(self.total, dtype=torch.float32, device=device)
             self.grads = torch.zeros(self.total, dtype=torch.float32, device=device)
-            self.exp_avg = self.exp_avg_sq = None
+            self.exp_avg = self.exp_avg_sq = self.max_exp_avg_sq = None
             self.ring = torch.zeros(RING * 4, dtype=torch.float32, device=device)
         check(lib.ts_mlp_bind_params(self.handle, self.params.data_ptr(), self.grads.data_ptr()), 'ts_mlp_bind_params')
         # pre-built 0-d views of every record's loss, tagged so B200Metrics can find the record
@@ -90,17 +90,27 @@ class Engine:
                 p.grad = self.grads[o:o + n].view(p.shape)
         self.sync_weights()
 
-    def bind_optimizer(self, kind: str, lr: float, betas=(0.9, 0.999), eps: float = 1e-8, step: int = 0) -> None:
+    def bind_optimizer(self, kind: str, lr: float, betas=(0.9, 0.999), eps: float = 1e-8, step: int = 0, *,
+                       weight_decay: float = 0.0, momentum: float = 0.0, dampening: float = 0.0, nesterov: bool = False,
+                       amsgrad: bool = False, decoupled_weight_decay: bool = False) -> None:
+        """torch.optim.SGD / Adam / AdamW hyper-parameters (one param group). State lives in flat buffers laid out
+        like the parameters: exp_avg (Adam's first moment or SGD's momentum buffer), exp_avg_sq, max_exp_avg_sq."""
         self.opt_kind = kind
-        if kind == 'adam' and self.exp_avg is None:
+        adam = kind == 'adam'
+        if (adam or momentum != 0) and self.exp_avg is None:
             self.exp_avg = torch.zeros_like(self.params)
+        if adam and self.exp_avg_sq is None:
             self.exp_avg_sq = torch.zeros_like(self.params)
-        h = _lib.OptHyper(float(lr), float(betas[0]), float(betas[1]), float(eps))
-        m = self.exp_avg.data_ptr() if kind == 'adam' else None
-        v = self.exp_avg_sq.data_ptr() if kind == 'adam' else None
-        check(lib.ts_opt_bind(self.handle, _lib.TS_OPT_ADAM if kind == 'adam' else _lib.TS_OPT_SGD, C.byref(h), m, v,
+        if adam and amsgrad and self.max_exp_avg_sq is None:
+            self.max_exp_avg_sq = torch.zeros_like(self.params)
+        h = _lib.OptHyper(float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), float(momentum),
+                          float(dampening), int(bool(nesterov)), int(bool(amsgrad)), int(bool(decoupled_weight_decay)), 0)
+        ptr = lambda t: t.data_ptr() if t is not None else None
+        check(lib.ts_opt_bind(self.handle, _lib.TS_OPT_ADAM if adam else _lib.TS_OPT_SGD, C.byref(h), ptr(self.exp_avg),
+                              ptr(self.exp_avg_sq) if adam else None, ptr(self.max_exp_avg_sq) if adam and amsgrad else None,
                               int(step)), 'ts_opt_bind')
-        self._hyper = (kind, float(lr), tuple(betas), float(eps))
+        self._hyper = (kind, float(lr), tuple(betas), float(eps), float(weight_decay), float(momentum), float(dampening),
+                       bool(nesterov), bool(amsgrad), bool(decoupled_weight_decay))
 
     @property
     def step_count(self) -> int:
