@@ -36,7 +36,7 @@ def test_header_symbols_are_exported_and_bound(built):
 
 
 def test_abi_version_and_error_string(built):
-    assert built.lib.ts_abi_version() == 1
+    assert built.lib.ts_abi_version() == built.ABI_VERSION == 2
     h = ctypes.c_void_p()
     dims = (ctypes.c_int32 * 2)(784, 10)
     rc = built.lib.ts_mlp_create(ctypes.byref(h), dims, 2, 0, 0.0, 0, 0)      # no hidden layer: rejected before any CUDA call

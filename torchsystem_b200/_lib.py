@@ -71,6 +71,9 @@ PROTOTYPES = {
 }
 
 
+ABI_VERSION = 2      # TS_ABI_VERSION in include/tsb200.h
+
+
 def _load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
@@ -80,6 +83,9 @@ def _load():
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)
         fn.restype, fn.argtypes = res, args
+    if lib.ts_abi_version() != ABI_VERSION:
+        raise ImportError(f'{LIB_PATH} has ABI version {lib.ts_abi_version()}, this package binds version {ABI_VERSION}: '
+                          'rebuild it (python -c "import __graft_entry__ as g; g.build()")')
     return lib
 
 
