@@ -301,6 +301,57 @@ def main():
                                          'frac_of_hbm_peak': v_rate * 3152 / 1e9 / peak,
                                          'note': 'validate handler (inference_mode, evaluate + fused metrics), fp32 inputs resident in HBM'}
 
+    # ---- extras for BASELINE.json configs[2] and configs[3] (one GPU only; not the headline)
+    if not args.skip_extras and world == 1:
+        import time
+        # configs[2]: the tinysys aggregate as shipped (Adam, batch 32) through a full `iterate` (train + validation
+        # phases, events dispatched to a consumer that reads the results like the logging consumer does); wall clock
+        torch.manual_seed(0)
+        net3 = MLP(DIMS[0], DIMS[1], DIMS[2], dropout=DROPOUT, activation=nn.ReLU())
+        model3 = B200Classifier(net3, nn.CrossEntropyLoss(), torch.optim.Adam(net3.parameters(), lr=1e-3), precision=args.precision,
+                                device=dev, max_batch=32)
+        n_tr, n_va = 32 * 1024, 32 * 256
+        loaders = [('train', DeviceLoader(x[:n_tr], y[:n_tr], 32, device=dev)),
+                   ('validation', DeviceLoader(x[n_tr:n_tr + n_va], y[n_tr:n_tr + n_va], 32, device=dev))]
+        training.service.handle('iterate', model3, loaders, metrics)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            training.service.handle('iterate', model3, loaders, metrics)
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) / 3
+        extras['config3_iterate_batch32'] = {
+            'value': (n_tr + n_va) / wall, 'unit': 'samples/s', 'wall_ms_per_epoch': wall * 1e3,
+            'us_per_batch': wall / ((n_tr + n_va) / 32) * 1e6,
+            'note': 'shipped aggregate (Adam lr 1e-3, dropout 0.1), iterate = 1024 train + 256 validation batches of 32, '
+                    'events dispatched and read by a consumer; host wall clock (launch-bound at this batch size)'}
+        del model3, loaders
+        # configs[3]'s model on one GPU: 784 -> 4096 x 4 -> 10, the 8-GPU share (8,192) of the global batch 65,536;
+        # 315,080,704 FLOP per sample against the measured cuBLAS bf16 peaks
+        BL = 8192
+        torch.manual_seed(0)
+        netL = MLP(DIMS[0], [4096] * 4, DIMS[2], dropout=DROPOUT, activation=nn.ReLU())
+        modelL = B200Classifier(netL, nn.CrossEntropyLoss(), torch.optim.Adam(netL.parameters(), lr=1e-3), precision=args.precision,
+                                device=dev, max_batch=BL)
+        xl, yl = x[:BL * 4], y[:BL * 4]
+        for i in range(3):
+            modelL.fit(xl[(i % 4) * BL:(i % 4 + 1) * BL], yl[(i % 4) * BL:(i % 4 + 1) * BL])
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for i in range(12):
+            modelL.fit(xl[(i % 4) * BL:(i % 4 + 1) * BL], yl[(i % 4) * BL:(i % 4 + 1) * BL])
+        e1.record()
+        torch.cuda.synchronize()
+        l_ms = e0.elapsed_time(e1) / 12
+        tfl = BL * 315080704 / (l_ms * 1e-3) / 1e12
+        extras['config4_L_model_one_gpu'] = {
+            'value': BL / (l_ms * 1e-3), 'unit': 'samples/s', 'ms_per_step': l_ms, 'tflops': tfl,
+            'frac_of_bf16_sustained_peak': tfl / (peaks or {}).get('bf16_tflops_sustained', 1363.5),
+            'frac_of_bf16_burst_peak': tfl / (peaks or {}).get('bf16_tflops', 1650.7),
+            'note': 'MLP 784-4096x4-10, Adam, batch 8192 per step, fp32 inputs resident; dense-layer FLOPs only'}
+        del modelL, netL
+
     # ---- e2e: host buffers, H2D every step, result read back
     if args.skip_e2e:
         e2e = None

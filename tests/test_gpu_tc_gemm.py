@@ -32,6 +32,9 @@ CASES = [
     (1, 1, 64, 48, 200, 1),            # small hidden sizes (golden 'deep' case class)
     (1, 0, 128, 128, 128, 1),          # remaining combination
     (0, 0, 130, 24, 40, 1),            # tiny N (multiple of 8), K < 64
+    (0, 0, 1000, 16, 512, 1),          # tensor-core head: logits against the [16, K] padded last-layer weights
+    (0, 1, 1000, 384, 16, 1),          # tensor-core head: dA = dZ W_last, contraction over the 16 padded classes
+    (1, 1, 384, 16, 1000, 3),          # tensor-core head: dW_last^T = A^T dZ, batch split
 ]
 
 

@@ -89,6 +89,10 @@ struct ts_mlp {
     __nv_bfloat16 *x_bf16 = nullptr, *shadow = nullptr;
     __nv_bfloat16 *x_bf16_alt = nullptr;   // second input buffer of the fused path: lets the next batch's cast overlap this step's optimizer
     int x_parity = 0;
+    // tensor-core head (bf16 mode, models the fused kernel does not take, <= 16 classes): logits / dZ operand / dW_last^T partials
+    bool tc_head = false;
+    float *zbuf = nullptr, *wt_partial = nullptr;
+    __nv_bfloat16 *dzb = nullptr;
     int64_t shadow_off[kMaxLayers] = {0};   // hidden-layer weights, dense [out][in]; last layer: [16][in], rows >= classes zero
     int64_t shadow_total = 0;
     bool fused = false;                     // one hidden layer of a width the fused kernel takes
@@ -145,6 +149,11 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
         m->x_bf16 = (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2);
         m->x_bf16_alt = m->fused ? (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2) : nullptr;
         m->shadow = (__nv_bfloat16 *)c.take(m->shadow_total * 2);
+    }
+    if (m->tc_head) {
+        m->zbuf = (float *)c.take(Bm * 16 * 4);
+        m->dzb = (__nv_bfloat16 *)c.take(Bm * 16 * 2);
+        m->wt_partial = (float *)c.take((int64_t)kMaxSplits * m->dims[L - 1] * 16 * 4);
     }
     return c.used;
 }
@@ -387,6 +396,62 @@ int run_dp_optimizer(ts_mlp *m, const int *nsplit, cudaStream_t st) {
     return launch_dp_optimizer(o, dp, m->n_chunks, m->sm_count, st);
 }
 
+// Last layer + loss on the tensor cores (bf16 mode, hidden layers wider than the fused kernel takes):
+//   Z[B,16] = A_last W_last^T as a tcgen05 GEMM against the zero-padded [16, K] shadow, then one thread per row for
+//   softmax / NLL / argmax / dZ (logits_head_kernel). The SIMT head_kernel spent 404 us on this at 8192 x 4096.
+int tc_head_forward(ts_mlp *m, const void *a_last, const int64_t *y, int64_t B, bool train, int64_t *pred, ts_batch_record *rec,
+                    cudaStream_t st) {
+    const int L = m->n_layers, K = m->dims[L - 1];
+    TcGemmArgs g{};
+    g.A = (const __nv_bfloat16 *)a_last; g.a_major = TC_MAJOR_K; g.lda = K;
+    g.B = m->shadow + m->shadow_off[L - 1]; g.b_major = TC_MAJOR_K; g.ldb = K;
+    g.M = (int)B; g.N = 16; g.K = K;
+    g.epi = TC_EPI_STORE_F32; g.out = m->zbuf; g.ldo = 16; g.splits = 1;
+    ProfScope ps(K_HEAD, st);
+    int rc = launch_tc_gemm(g, m->sm_count, st);
+    if (rc) return rc;
+    return launch_logits_head(m->zbuf, m->params + m->off[2 * (L - 1) + 1], y, B, m->dims[L], pred, train ? m->dz : nullptr, m->dzb,
+                              m->head_partials, m->ticket, rec, st);
+}
+
+// Backward of the last layer on the tensor cores: dH = (dZ W_last) * act'(A_last) / (1 - p) with the activation gradient
+// in the GEMM epilogue (K = 16), dW_last^T = A_last^T dZ split over the batch, then the fold into `grads`.
+int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *const *masks, uint64_t seed, cudaStream_t st) {
+    const int L = m->n_layers, K = m->dims[L - 1], C = m->dims[L];
+    int rc;
+    {
+        TcGemmArgs g{};
+        g.A = m->dzb; g.a_major = TC_MAJOR_K; g.lda = 16;
+        g.B = m->shadow + m->shadow_off[L - 1]; g.b_major = TC_MAJOR_MN; g.ldb = K;
+        g.M = (int)B; g.N = K; g.K = 16;
+        g.epi = TC_EPI_ACTGRAD; g.out = m->dh[0]; g.ldo = K; g.splits = 1;
+        g.A_prev = (const __nv_bfloat16 *)a_last;
+        g.drop = drop_spec(m, masks, seed, L - 2, true); g.training = m->p > 0.0f;
+        ProfScope ps(K_HEAD, st);
+        rc = launch_tc_gemm(g, m->sm_count, st);
+        if (rc) return rc;
+    }
+    const int m_tiles = (K + 127) / 128;
+    int S = m->sm_count / m_tiles;
+    S = S < 1 ? 1 : (S > kMaxSplits ? kMaxSplits : S);
+    int64_t kc = round_up((B + S - 1) / S, 128);
+    S = (int)((B + kc - 1) / kc);
+    {
+        TcGemmArgs g{};
+        g.A = (const __nv_bfloat16 *)a_last; g.a_major = TC_MAJOR_MN; g.lda = K;
+        g.B = m->dzb; g.b_major = TC_MAJOR_MN; g.ldb = 16;
+        g.M = K; g.N = 16; g.K = (int)B;
+        g.epi = TC_EPI_STORE_F32; g.out = m->wt_partial; g.ldo = 16; g.splits = S; g.k_chunk = (int)kc;
+        g.split_stride = (int64_t)K * 16;
+        ProfScope ps(K_HEAD_WGRAD, st);
+        rc = launch_tc_gemm(g, m->sm_count, st);
+        if (rc) return rc;
+        rc = launch_wlast_finish(m->wt_partial, (int64_t)K * 16, S, K, C, m->dz, B, m->grads + m->off[2 * (L - 1)],
+                                 m->grads + m->off[2 * (L - 1) + 1], st);
+    }
+    return rc;
+}
+
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
              uint64_t seed, int64_t *pred, ts_batch_record *rec, cudaStream_t st, bool update) {
     int rc = check_ready(m, B, update);
@@ -405,21 +470,31 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     } else {
         rc = forward_hidden(m, x, x_dtype, B, masks, seed, true, &a0, &a_last, st);
         if (rc) return rc;
-        HeadArgs h{};
-        fill_head(m, h, a_last, y, B, pred, rec);
-        h.dz = m->dz; h.dH = m->dh[0];
-        h.U_prev = m->upre[L - 2];
-        h.drop = drop_spec(m, masks, seed, L - 2, true);
-        { ProfScope ps(K_HEAD, st); rc = launch_head(h, m->sm_count, st); }
+        if (m->tc_head) {
+            rc = tc_head_forward(m, a_last, y, B, true, pred, rec, st);
+            if (rc) return rc;
+            rc = tc_head_backward(m, a_last, B, masks, seed, st);
+        } else {
+            HeadArgs h{};
+            fill_head(m, h, a_last, y, B, pred, rec);
+            h.dz = m->dz; h.dH = m->dh[0];
+            h.U_prev = m->upre[L - 2];
+            h.drop = drop_spec(m, masks, seed, L - 2, true);
+            ProfScope ps(K_HEAD, st);
+            rc = launch_head(h, m->sm_count, st);
+        }
         if (rc) return rc;
     }
 
     int nsplit[2 * kMaxLayers] = {0};
     const int64_t row_blocks = (B + 127) / 128;
-    const bool small = m->classes() <= 16 && row_blocks <= kMaxRowBlocks;   // one launch for dW_last, db_last, db of the last hidden layer
+    const bool tc_head = m->tc_head && !m->fused;      // last-layer gradients already in `grads` (tc_head_backward)
+    const bool small = !tc_head && m->classes() <= 16 && row_blocks <= kMaxRowBlocks;   // one launch for dW_last, db_last, db of the last hidden layer
     const bool in_kernel = m->fused && fused_grads_supported(m->dims[1], m->dims[2], B);   // the fused kernel already left them
     if (in_kernel) {
         nsplit[2] = nsplit[3] = nsplit[1] = (int)row_blocks;
+    } else if (tc_head) {
+        // nothing to launch here
     } else if (small) {
         const int tw = 2 * (L - 1), tb = tw + 1, th = 2 * (L - 2) + 1;
         const bool direct = row_blocks == 1;
@@ -565,10 +640,12 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
         m->max_split[2 * l] = (l == m->n_layers - 1) ? kMaxRowBlocks : (int)s;
         m->max_split[2 * l + 1] = (l >= m->n_layers - 2) ? kMaxRowBlocks : kMaxSplits;
         m->shadow_off[l] = so;
-        so += round_up(in * (l < m->n_layers - 1 ? outw : 16), 128);
+        so += round_up(in * (l < m->n_layers - 1 ? outw : (outw > 16 ? outw : 16)), 128);   // last layer: at least 16 class rows
     }
     m->shadow_total = so;
     m->fused = precision == TS_PREC_BF16 && m->n_layers == 2 && fused_mlp_supported(dims[0], dims[1], dims[2]);
+    m->tc_head = precision == TS_PREC_BF16 && !m->fused && dims[n_dims - 1] <= 16;
+    if (const char *e = getenv("TSB200_SIMT_HEAD")) m->tc_head = m->tc_head && atoi(e) == 0;   // A/B switch for measurements
     m->total = o;
     m->n_chunks = o / kChunk;
     m->chunk_tensor_host.assign((size_t)m->n_chunks, -1);
@@ -703,6 +780,7 @@ int32_t ts_eval_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const 
         return fused_forward(m, inputs, inputs_dtype, targets, batch, nullptr, 0, false, predictions, record, &a0, (cudaStream_t)stream);
     rc = forward_hidden(m, inputs, inputs_dtype, batch, nullptr, 0, false, &a0, &a_last, (cudaStream_t)stream);
     if (rc) return rc;
+    if (m->tc_head) return tc_head_forward(m, a_last, targets, batch, false, predictions, record, (cudaStream_t)stream);
     HeadArgs h{};
     fill_head(m, h, a_last, targets, batch, predictions, record);
     h.drop = drop_spec(m, nullptr, 0, m->n_layers - 2, false);

@@ -64,6 +64,13 @@ struct HeadArgs {
 };
 int launch_head(const HeadArgs &a, int sm_count, cudaStream_t st);
 
+// Tensor-core head (bf16 mode, wide hidden layers): softmax / NLL / argmax / dZ from the logits GEMM's output, and the
+// fold of the transposed dW_last partials + db_last into `grads` (the contractions themselves are tc_gemm launches).
+int launch_logits_head(const float *Z, const float *bias, const int64_t *y, int64_t B, int C, int64_t *pred, float *dz,
+                       __nv_bfloat16 *dzb, HeadPartial *partials, unsigned int *ticket, ts_batch_record *record, cudaStream_t st);
+int launch_wlast_finish(const float *wt, int64_t split_stride, int splits, int K, int C, const float *dz, int64_t B, float *gw,
+                        float *gb, cudaStream_t st);
+
 // dW_last[c,k] = sum_r dz[r,c] * A[r,k], db_last[c] = sum_r dz[r,c]; `splits` row ranges -> partials
 int launch_head_wgrad(const void *A, int a_is_bf16, const float *dz, int64_t B, int K, int C, float *w_partial,
                       int64_t w_stride, float *b_partial, int64_t b_stride, int splits, cudaStream_t st);

@@ -311,6 +311,177 @@ int launch_head(const HeadArgs &a, int sm_count, cudaStream_t st) {
 // =====================================================================================
 // dW_last / db_last partials: thread per hidden column k, dz rows broadcast from shared memory.
 // =====================================================================================
+__device__ __forceinline__ uint32_t pack2_bf16(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// =====================================================================================
+// Tensor-core head (bf16 mode, hidden layers too wide for the fused kernel): the two big contractions of the last
+// layer run as tcgen05 GEMMs (engine.cu), and these two small kernels do what is left.
+//
+// logits_head_kernel: thread = batch row. Z[r, 0..15] (fp32, from the Z = A W^T GEMM, classes padded to 16) + bias
+//   -> log-softmax / NLL / first-max argmax -> dZ (fp32 [B, C] for db_last, and bf16 [B, 16] zero-padded as the operand
+//   of the dA and dW GEMMs); loss sum and correct count warp -> block -> grid like head_kernel.
+// =====================================================================================
+__global__ void __launch_bounds__(256) logits_head_kernel(const float *__restrict__ Z, const float *__restrict__ bias,
+                                                          const int64_t *__restrict__ y, int64_t B, int C, int64_t *__restrict__ pred,
+                                                          float *__restrict__ dz, __nv_bfloat16 *__restrict__ dzb,
+                                                          HeadPartial *partials, unsigned int *ticket, ts_batch_record *record) {
+    __shared__ float s_loss[8];
+    __shared__ int s_corr[8];
+    __shared__ bool s_last;
+    pdl_launch_dependents();
+    pdl_wait();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    float row_loss = 0.0f;
+    int corr = 0;
+    if (r < B) {
+        float z[16];
+        const float4 *zr = reinterpret_cast<const float4 *>(Z + r * 16);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float4 v = zr[q];
+            z[4 * q] = v.x; z[4 * q + 1] = v.y; z[4 * q + 2] = v.z; z[4 * q + 3] = v.w;
+        }
+#pragma unroll
+        for (int c = 0; c < 16; ++c) z[c] = (c < C) ? z[c] + bias[c] : 0.0f;
+        float mx = z[0];
+        int arg = 0;
+#pragma unroll
+        for (int c = 1; c < 16; ++c)
+            if (c < C && z[c] > mx) { mx = z[c]; arg = c; }      // strict '>': first maximum wins, like torch.argmax
+        float sum = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+            if (c < C) sum += expf(z[c] - mx);
+        const float lse = mx + logf(sum);
+        const int yy = (int)y[r];
+        float zy = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+            if (c == yy) zy = z[c];
+        row_loss = lse - zy;
+        if (yy < 0 || yy >= C) row_loss = __int_as_float(0x7fc00000);   // target outside [0,C): poison the loss
+        corr = (arg == yy);
+        pred[r] = arg;
+        if (dz != nullptr) {
+            const float inv_B = 1.0f / (float)B;
+            float d[16];
+#pragma unroll
+            for (int c = 0; c < 16; ++c) d[c] = (c < C) ? (expf(z[c] - lse) - (c == yy ? 1.0f : 0.0f)) * inv_B : 0.0f;
+            for (int c = 0; c < C; ++c) dz[r * C + c] = d[c];
+            uint4 lo, hi;
+            lo.x = pack2_bf16(d[0], d[1]); lo.y = pack2_bf16(d[2], d[3]); lo.z = pack2_bf16(d[4], d[5]); lo.w = pack2_bf16(d[6], d[7]);
+            hi.x = pack2_bf16(d[8], d[9]); hi.y = pack2_bf16(d[10], d[11]); hi.z = pack2_bf16(d[12], d[13]); hi.w = pack2_bf16(d[14], d[15]);
+            uint4 *o = reinterpret_cast<uint4 *>(dzb + r * 16);
+            o[0] = lo; o[1] = hi;
+        }
+    }
+    row_loss = warp_sum(row_loss);
+    corr = warp_sum(corr);
+    if (lane == 0) { s_loss[warp] = row_loss; s_corr[warp] = corr; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float l = 0.0f;
+        int c = 0;
+        for (int w = 0; w < 8; ++w) { l += s_loss[w]; c += s_corr[w]; }
+        partials[blockIdx.x].loss_sum = l;
+        partials[blockIdx.x].correct = c;
+        __threadfence();
+        s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && warp == 0) {
+        __threadfence();
+        float l = 0.0f;
+        int c = 0;
+        for (int b = lane; b < (int)gridDim.x; b += 32) {
+            const volatile HeadPartial *q = partials + b;
+            l += q->loss_sum;
+            c += q->correct;
+        }
+        l = warp_sum(l);
+        c = warp_sum(c);
+        if (lane == 0) {
+            record->loss = l / (float)B;   // reduction='mean'
+            record->n_correct = c;
+            record->n_rows = (int32_t)B;
+            record->reserved = 0;
+            *ticket = 0u;
+        }
+    }
+}
+
+int launch_logits_head(const float *Z, const float *bias, const int64_t *y, int64_t B, int C, int64_t *pred, float *dz,
+                       __nv_bfloat16 *dzb, HeadPartial *partials, unsigned int *ticket, ts_batch_record *record, cudaStream_t st) {
+    const int64_t blocks = (B + 255) / 256;
+    TS_REQUIRE(blocks <= kMaxHeadBlocks, TS_E_TOO_LARGE, "batch %lld needs %lld head blocks, more than %d", (long long)B,
+               (long long)blocks, kMaxHeadBlocks);
+    TS_CUDA_CHECK(launch_pdl(logits_head_kernel, dim3((unsigned)blocks), dim3(256), 0, st, 1, Z, bias, y, B, C, pred, dz, dzb, partials,
+                             ticket, record));
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+// wlast_finish_kernel: dW_last[c, k] = sum over split-K partials of the transposed product dWt[s][k][16] (what the
+// dW^T = A^T dZ GEMM writes), and db_last[c] = sum_r dz[r, c] (fp32 dZ, fixed-order tree). Writes straight into `grads`.
+__global__ void __launch_bounds__(256) wlast_finish_kernel(const float *__restrict__ wt, int64_t split_stride, int splits, int K, int C,
+                                                           const float *__restrict__ dz, int64_t B, float *__restrict__ gw,
+                                                           float *__restrict__ gb) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int wblocks = (K + 255) / 256;
+    if ((int)blockIdx.x < wblocks) {
+        const int k = blockIdx.x * 256 + threadIdx.x;
+        if (k >= K) return;
+        float acc[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) acc[c] = 0.0f;
+        for (int s = 0; s < splits; ++s) {
+            const float4 *q = reinterpret_cast<const float4 *>(wt + (int64_t)s * split_stride + (int64_t)k * 16);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 v = q[j];
+                acc[4 * j] += v.x; acc[4 * j + 1] += v.y; acc[4 * j + 2] += v.z; acc[4 * j + 3] += v.w;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+            if (c < C) gw[(int64_t)c * K + k] = acc[c];         // coalesced over k for every class row
+        return;
+    }
+    // one block per class: the bias gradient. Thread t sums rows t, t+256, ... (8 loads in flight), then a fixed-order tree.
+    __shared__ float red[256];
+    const int c = (int)blockIdx.x - wblocks;
+    float a = 0.0f;
+    int64_t r = threadIdx.x;
+    for (; r + 7 * 256 < B; r += 8 * 256) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = dz[(r + u * 256) * C + c];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) a += v[u];
+    }
+    for (; r < B; r += 256) a += dz[r * C + c];
+    red[threadIdx.x] = a;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if ((int)threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) gb[c] = red[0];
+}
+
+int launch_wlast_finish(const float *wt, int64_t split_stride, int splits, int K, int C, const float *dz, int64_t B, float *gw,
+                        float *gb, cudaStream_t st) {
+    const unsigned blocks = (unsigned)((K + 255) / 256) + (unsigned)C;
+    TS_CUDA_CHECK(launch_pdl(wlast_finish_kernel, dim3(blocks), dim3(256), 0, st, 1, wt, split_stride, splits, K, C, dz, B, gw, gb));
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
 template <typename T, int MAXC>
 __global__ void __launch_bounds__(128) head_wgrad_kernel(const T *__restrict__ A, const float *__restrict__ dz, int64_t B,
                                                          int K, int C, float *__restrict__ w_partial, int64_t w_stride,
