@@ -16,6 +16,13 @@ for _ in range(10): p, l = model.fit(x, y)
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 10
 print(f'L model fit (SIMT_HEAD={os.environ.get("TSB200_SIMT_HEAD")}): {ms:.3f} ms/step, {B*315080704/ms/1e9:.1f} TFLOP/s, loss {l.item():.4f}')
+from torchsystem_b200 import _lib
+_lib.profile_begin()
+for _ in range(4): model.fit(x, y)
+torch.cuda.synchronize()
+pk = _lib.profile_end()
+print('event-bracketed kinds (us per launch, launches per step):', {k: (round(v[0] / v[1] * 1e3, 1), v[1] // 4) for k, v in pk.items()})
+print('sum per step: %.1f us' % (sum(v[0] for v in pk.values()) / 4 * 1e3))
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(3): model.fit(x, y)
     torch.cuda.synchronize()

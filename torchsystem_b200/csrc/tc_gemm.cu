@@ -24,7 +24,8 @@ using namespace tc;
 
 namespace {
 
-constexpr int kThreads = 224;  // warp 0: A producer, 1: MMA issuer + TMEM owner, 2: B producer, 3..6: epilogue
+constexpr int kThreads = 352;  // warp 0: A producer, 1: MMA issuer + TMEM owner, 2: B producer, 3..10: epilogue
+constexpr int kEpiWarps = 8;   // two per TMEM lane quarter, taking alternate 32-column chunks
 constexpr int kMaxStages = 8;
 
 struct TcParams {
@@ -76,7 +77,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }   // A + B producers arrive
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full_bar[b], 1); mbar_init(&tmem_empty_bar[b], 4); }  // 4 epilogue warps
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full_bar[b], 1); mbar_init(&tmem_empty_bar[b], kEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_a)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_b)) : "memory");
@@ -191,6 +192,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     } else if (warp >= 3) {
         // ===================== epilogue: TMEM -> registers -> smem (transpose) -> coalesced global =====================
         const int q = warp & 3;                  // TMEM lane quarter this warp may read
+        const int half = (warp - 3) >> 2;        // which of the two warps of that quarter: chunks half, half + 2, ...
         float4 *stage = reinterpret_cast<float4 *>(staging + (size_t)(warp - 3) * 4096);
         const int sub_row = lane >> 3, piece = lane & 7;     // phase-2 mapping: 4 rows x 8 float4 per instruction
         for (int t = blockIdx.x, it = 0; t < total_tiles; t += gridDim.x, ++it) {
@@ -214,13 +216,18 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                         prev_next[i] = *reinterpret_cast<const uint2 *>(p.A_prev + (int64_t)row * p.ldo + n);
                 }
             };
-            if (EPI == TC_EPI_ACTGRAD) fetch_prev(0);
-            for (int c = 0; c < p.BN; c += 32) {
+            if (half * 32 >= p.BN) {             // narrow tile: nothing for the second warp of the quarter
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+            }
+            if (EPI == TC_EPI_ACTGRAD) fetch_prev(half * 32);
+            for (int c = half * 32; c < p.BN; c += 64) {
                 uint2 prev[8];
                 if (EPI == TC_EPI_ACTGRAD) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) prev[i] = prev_next[i];
-                    fetch_prev(c + 32);
+                    fetch_prev(c + 64);
                 }
                 float v[32];
                 if (has_k) {
@@ -230,8 +237,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = 0.0f;
                 }
-                if (c + 32 >= p.BN) {
-                    // last TMEM read of this tile is in registers: hand the accumulator back to the MMA issuer
+                if (c + 64 >= p.BN) {
+                    // this warp's last TMEM read of the tile is in registers: hand the accumulator back to the MMA issuer
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
@@ -434,8 +441,8 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     const long total_tiles = (long)p.tiles_m * p.tiles_n * splits;
     const int grid_x = (int)(total_tiles < sm_count ? total_tiles : sm_count);
     const long tiles_per_cta = (total_tiles + grid_x - 1) / grid_x;
-    // pipeline stages + 16 KiB of epilogue staging (the pipeline stays live while a tile's epilogue runs) + alignment
-    p.stages = (int)((226u * 1024u - 1024u - 4u * 4096u - 512u) / stage);
+    // pipeline stages + 32 KiB of epilogue staging (the pipeline stays live while a tile's epilogue runs) + alignment
+    p.stages = (int)((226u * 1024u - 1024u - (uint32_t)kEpiWarps * 4096u) / stage);
     if (p.stages > kMaxStages) p.stages = kMaxStages;
     const long kblocks_per_cta = (long)p.kblocks_per_split * tiles_per_cta;
     if (p.stages > kblocks_per_cta) p.stages = kblocks_per_cta < 2 ? 2 : (int)kblocks_per_cta;
@@ -455,7 +462,7 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     else rc = get_map(a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb, 64, (uint32_t)p.BK, &mb);
     if (rc) return rc;
 
-    const size_t smem = (size_t)p.stages * stage + 4 * 4096 + 1024;
+    const size_t smem = (size_t)p.stages * stage + kEpiWarps * 4096 + 1024;
     dim3 grid((unsigned)grid_x);
 #define TS_TC_LAUNCH(E)                                                                                             \
     do {                                                                                                            \
