@@ -416,7 +416,7 @@ int tc_head_forward(ts_mlp *m, const void *a_last, const int64_t *y, int64_t B, 
 
 // Backward of the last layer on the tensor cores: dH = (dZ W_last) * act'(A_last) / (1 - p) with the activation gradient
 // in the GEMM epilogue (K = 16), dW_last^T = A_last^T dZ split over the batch, then the fold into `grads`.
-int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *const *masks, uint64_t seed, cudaStream_t st) {
+int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *const *masks, uint64_t seed, int *nsplit, cudaStream_t st) {
     const int L = m->n_layers, K = m->dims[L - 1], C = m->dims[L];
     int rc;
     {
@@ -427,6 +427,11 @@ int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *co
         g.epi = TC_EPI_ACTGRAD; g.out = m->dh[0]; g.ldo = K; g.splits = 1;
         g.A_prev = (const __nv_bfloat16 *)a_last;
         g.drop = drop_spec(m, masks, seed, L - 2, true); g.training = m->p > 0.0f;
+        const int tb = 2 * (L - 2) + 1, rows4 = 4 * (int)((B + 127) / 128);
+        if (rows4 <= kMaxRowBlocks) {    // db of the last hidden layer = column sums of this dH, taken in the epilogue
+            g.colsum_out = m->partials + m->partial_off[tb]; g.colsum_stride = m->partial_stride[tb];
+            nsplit[tb] = rows4;
+        }
         ProfScope ps(K_HEAD, st);
         rc = launch_tc_gemm(g, m->sm_count, st);
         if (rc) return rc;
@@ -463,6 +468,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     const bool dp = m->dp_world > 1 && update;
     if (dp) m->grads = m->dp_grads[m->step & 1][m->dp_rank];     // this step's peer-visible gradient buffer
     const void *a0 = nullptr, *a_last = nullptr;
+    int nsplit[2 * kMaxLayers] = {0};
     if (m->fused) {
         rc = fused_forward(m, x, x_dtype, y, B, masks, seed, true, pred, rec, &a0, st);
         if (rc) return rc;
@@ -473,7 +479,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         if (m->tc_head) {
             rc = tc_head_forward(m, a_last, y, B, true, pred, rec, st);
             if (rc) return rc;
-            rc = tc_head_backward(m, a_last, B, masks, seed, st);
+            rc = tc_head_backward(m, a_last, B, masks, seed, nsplit, st);
         } else {
             HeadArgs h{};
             fill_head(m, h, a_last, y, B, pred, rec);
@@ -486,7 +492,6 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         if (rc) return rc;
     }
 
-    int nsplit[2 * kMaxLayers] = {0};
     const int64_t row_blocks = (B + 127) / 128;
     const bool tc_head = m->tc_head && !m->fused;      // last-layer gradients already in `grads` (tc_head_backward)
     const bool small = !tc_head && m->classes() <= 16 && row_blocks <= kMaxRowBlocks;   // one launch for dW_last, db_last, db of the last hidden layer
@@ -524,7 +529,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         const void *dHl = m->dh[cur];
         const void *a_prev = (l == 0) ? a0 : m->acts[l - 1];
         const int tw = 2 * l, tb = tw + 1;
-        if (!((small || in_kernel) && l == L - 2)) {   // db_l = colsum(dH_l) (the last hidden layer's came with the small-gradient launch)
+        if (!((small || in_kernel) && l == L - 2) && nsplit[tb] == 0) {   // db_l = colsum(dH_l), unless it came with the kernel that produced dH_l
             int kc;
             const int S = splits_for(B, kMaxSplits, 1, &kc);
             float *bp = S > 1 ? m->partials + m->partial_off[tb] : m->grads + m->off[tb];
@@ -575,6 +580,11 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
                 g.M = (int)B; g.N = in; g.K = out;
                 g.epi = TC_EPI_ACTGRAD; g.out = m->dh[cur ^ 1]; g.ldo = in; g.splits = 1;
                 g.A_prev = (const __nv_bfloat16 *)m->acts[l - 1];
+                const int tbp = 2 * (l - 1) + 1, rows4 = 4 * (int)((B + 127) / 128);
+                if (rows4 <= kMaxRowBlocks) {    // db of layer l-1 = column sums of the dH this GEMM stores
+                    g.colsum_out = m->partials + m->partial_off[tbp]; g.colsum_stride = m->partial_stride[tbp];
+                    nsplit[tbp] = rows4;
+                }
                 g.drop = ds; g.training = m->p > 0.0f;
                 rc = launch_tc_gemm(g, m->sm_count, st);
             }
@@ -638,7 +648,8 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
         int64_t s = sms / tiles;   // one wave of CTAs
         s = s < 1 ? 1 : (s > kMaxSplits ? kMaxSplits : s);
         m->max_split[2 * l] = (l == m->n_layers - 1) ? kMaxRowBlocks : (int)s;
-        m->max_split[2 * l + 1] = (l >= m->n_layers - 2) ? kMaxRowBlocks : kMaxSplits;
+        // bf16 mode: hidden bias gradients come out of the dH-producing GEMM epilogues, 4 partial rows per 128-row tile
+        m->max_split[2 * l + 1] = (l >= m->n_layers - 2 || precision == TS_PREC_BF16) ? kMaxRowBlocks : kMaxSplits;
         m->shadow_off[l] = so;
         so += round_up(in * (l < m->n_layers - 1 ? outw : (outw > 16 ? outw : 16)), 128);   // last layer: at least 16 class rows
     }

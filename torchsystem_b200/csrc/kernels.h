@@ -162,6 +162,8 @@ struct TcGemmArgs {
     int64_t split_stride;  // elements between split outputs
     const float *bias;             // FWD: [N]
     const __nv_bfloat16 *A_prev;   // ACTGRAD: the layer's own bf16 output [M][ldo]
+    float *colsum_out;             // ACTGRAD (optional): column sums of the stored output per 32-row group -> row (4 * row_tile + quarter)
+    int64_t colsum_stride;         //   of this array (the hidden-layer bias gradient partials; fixed order, no atomics)
     DropoutSpec drop;
     int training;
     unsigned long long *dbg;       // optional device buffer of 32 clock64 samples from CTA (0,0,0)

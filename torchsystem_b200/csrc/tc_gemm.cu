@@ -42,6 +42,8 @@ struct TcParams {
     int64_t ldo, split_stride;
     const float *bias;
     const __nv_bfloat16 *A_prev;
+    float *colsum_out;
+    int64_t colsum_stride;
     DropoutSpec drop;
     int training;
     unsigned long long *dbg;   // optional trace buffer (test hook), or nullptr
@@ -249,6 +251,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     stage[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                 __syncwarp();
                 // phase 2: 8 consecutive lanes cover 128 contiguous bytes of one output row.
+                float cs[4] = {0.0f, 0.0f, 0.0f, 0.0f};      // ACTGRAD: column sums of what this lane stores (bias gradient)
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int rr = i * 4 + sub_row;
@@ -286,8 +289,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                                 for (int j = 0; j < nv; ++j) w[j] = (__bfloat162float(ap[j]) > 0.0f) ? w[j] * sc : 0.0f;
                             }
                         }
+                        __nv_bfloat162 lo = __floats2bfloat162_rn(w[0], w[1]), hi = __floats2bfloat162_rn(w[2], w[3]);
+                        if (EPI == TC_EPI_ACTGRAD) {      // sums of the ROUNDED values: what a column sum of the stored dH gives
+                            cs[0] += __low2float(lo); cs[1] += __high2float(lo); cs[2] += __low2float(hi); cs[3] += __high2float(hi);
+                        }
                         if (nv == 4 && (p.ldo & 3) == 0) {
-                            __nv_bfloat162 lo = __floats2bfloat162_rn(w[0], w[1]), hi = __floats2bfloat162_rn(w[2], w[3]);
                             uint2 pk;
                             pk.x = *reinterpret_cast<uint32_t *>(&lo);
                             pk.y = *reinterpret_cast<uint32_t *>(&hi);
@@ -295,6 +301,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                         } else {
                             for (int j = 0; j < nv; ++j) o[j] = __float2bfloat16_rn(w[j]);
                         }
+                    }
+                }
+                if (EPI == TC_EPI_ACTGRAD && p.colsum_out != nullptr) {
+                    // the 4 lanes that share a column quad (sub_row 0..3) fold their 8 rows each: 32 rows per warp
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
+                        cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
+                    }
+                    const int n = n0 + c + piece * 4;
+                    if (sub_row == 0 && c + piece * 4 < p.BN) {
+                        float *o = p.colsum_out + (int64_t)(tm_ * 4 + q) * p.colsum_stride + n;
+                        for (int j = 0; j < 4; ++j)
+                            if (n + j < p.N) o[j] = cs[j];
                     }
                 }
                 __syncwarp();
@@ -450,7 +470,8 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     while ((int)p.acc_stride < p.BN) p.acc_stride <<= 1;
     p.tmem_cols = 2 * p.acc_stride;
     p.out = a.out; p.ldo = a.ldo; p.split_stride = a.split_stride;
-    p.bias = a.bias; p.A_prev = a.A_prev; p.drop = a.drop; p.training = a.training;
+    p.bias = a.bias; p.A_prev = a.A_prev; p.colsum_out = a.colsum_out; p.colsum_stride = a.colsum_stride;
+    p.drop = a.drop; p.training = a.training;
     p.dbg = a.dbg;
 
     CUtensorMap ma, mb;
