@@ -145,6 +145,23 @@ int32_t ts_fit_backward(ts_mlp *m, const void *inputs, int32_t inputs_dtype, con
                         const uint8_t *const *masks /*HOST*/, uint64_t seed, int64_t *predictions,
                         ts_batch_record *record, void *stream);
 int32_t ts_opt_apply(ts_mlp *m, float grad_scale, void *stream);
+/* ts_opt_apply for the parameter tensors [first_tensor, first_tensor + n_tensors) only (torch order W0, b0, W1, ...), so
+ * the update of a bucket whose all-reduce has finished can run while the next bucket is still being reduced. The first
+ * range of a step passes advance_step = 1 (optimizer step counter, Adam bias correction), the others 0. */
+int32_t ts_opt_apply_range(ts_mlp *m, float grad_scale, int32_t first_tensor, int32_t n_tensors, int32_t advance_step, void *stream);
+
+/* ts_fit_backward for callers that overlap the gradient all-reduce with the rest of the backward pass (no counterpart
+ * in the reference, which is single-process; BASELINE north star: "NCCL allreduces gradients ... overlapped with
+ * backward"). `layer_events[l]` (HOST array of n_layers cudaEvent_t) is recorded on `stream` as soon as the kernels
+ * producing layer l's gradients are enqueued -- last layer first. `tensor_final[t]` (HOST out, 2*n_layers: W0, b0, W1,
+ * ...) says whether gradient tensor t is already complete in `grads` at that event (the caller may all-reduce it on
+ * another stream that waits for the event) or only when the whole call has run (small tensors kept as partials).
+ * ts_dp_reserve_sms makes the backward GEMMs of later calls leave `n_sms` SMs free for that collective's kernels. */
+int32_t ts_fit_backward_overlap(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                                const uint8_t *const *masks /*HOST*/, uint64_t seed, int64_t *predictions,
+                                ts_batch_record *record, void *stream, void *const *layer_events /*HOST*/,
+                                int32_t *tensor_final /*HOST*/);
+int32_t ts_dp_reserve_sms(ts_mlp *m, int32_t n_sms);
 
 #define TS_DP_FLAG_WORDS 64
 /* Data parallel without a separate collective (no counterpart in the reference, which is single-process): after

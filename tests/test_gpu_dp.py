@@ -18,7 +18,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, precision, dp_mode, out):
+def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1024):
     import torch.distributed as dist
     from torch import nn
     os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
@@ -26,18 +26,19 @@ def _worker(rank, world, port, precision, dp_mode, out):
     dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
     from torchsystem_b200 import B200Classifier, B200Metrics, MLP
     from tests.test_gpu_parity import synthetic, seeded_init
-    dims, B = [784, 256, 10], 1024
+    dims = list(dims)
     x, y = synthetic(B * 3)
     if precision == 'bf16':
         x = x.bfloat16().float()
     init = seeded_init(dims, seed=rank, bf16=precision == 'bf16')      # different per rank: the broadcast must fix it
-    net = MLP(784, 256, 10, dropout=0.0, activation=nn.ReLU())
+    net = MLP(dims[0], dims[1] if len(dims) == 3 else dims[1:-1], dims[-1], dropout=0.0, activation=nn.ReLU())
     with torch.no_grad():
         for p, w in zip([q for lin in net.linears() for q in (lin.weight, lin.bias)], init):
             p.copy_(torch.from_numpy(w))
     model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
                            device=f'cuda:{rank}', max_batch=B, dp_mode=dp_mode)
     assert (model._p2p is not None) == (dp_mode == 'p2p')
+    assert model._overlap == (dp_mode == 'nccl' and os.environ.get('TSB200_DP_OVERLAP', '0') != '0')
     metrics = B200Metrics(device=f'cuda:{rank}', log_every=0)
     half = B // world
     for s in range(3):
@@ -80,3 +81,27 @@ def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, to
     loss_sum, n_batches, n_correct, n_total = got['counters']
     assert (n_batches, n_total) == (6, total)
     assert abs(n_correct - correct) <= (0 if precision == 'f32' else 3)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
+@pytest.mark.parametrize('overlap', ['0', '1'])
+def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
+    """'nccl' mode on a net with 2048- and 4096-wide layers: several all-reduce buckets with the optimizer applied bucket by
+    bucket (overlap '0', the default), or (overlap '1') each layer's gradient all-reduced on the side stream while the
+    backward pass is still running, biases in a packed all-reduce at the end. Must match the full-batch oracle."""
+    monkeypatch.setenv('TSB200_DP_OVERLAP', overlap)
+    import torch.multiprocessing as mp
+    from oracle import mlp_numpy as onp
+    from tests.test_gpu_parity import synthetic, seeded_init
+    from tests.golden_util import assert_params_close
+    dims, B = (784, 4096, 4096, 2048, 10), 1024
+    out = str(tmp_path / 'rank0.npz')
+    mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nccl', out, dims, B), nprocs=2, join=True)
+    x, y = synthetic(B * 3)
+    x = x.bfloat16().float()
+    init = seeded_init(list(dims), seed=0, bf16=True)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=True)
+    for s in range(3):
+        oracle.fit(x[s * B:(s + 1) * B].numpy(), y[s * B:(s + 1) * B].numpy(), None)
+    got = np.load(out)
+    assert_params_close([got[f'arr_{i}'] for i in range(8)], oracle.parameters(), 1e-2, adam=False)

@@ -51,7 +51,12 @@ PROTOTYPES = {
                                 C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     'ts_fit_backward': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.POINTER(C.c_void_p),
                                     C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'ts_fit_backward_overlap': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.POINTER(C.c_void_p),
+                                            C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p),
+                                            C.POINTER(C.c_int32)]),
+    'ts_dp_reserve_sms': (C.c_int32, [C.c_void_p, C.c_int32]),
     'ts_opt_apply': (C.c_int32, [C.c_void_p, C.c_float, C.c_void_p]),
+    'ts_opt_apply_range': (C.c_int32, [C.c_void_p, C.c_float, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     'ts_eval_step': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                  C.c_void_p]),
     'ts_eval_step_static': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,

@@ -12,6 +12,8 @@ mirrors the reference aggregate (/root/reference/examples/tinysys/tinysys/classi
 `torch.save(model.nn)`, `load_state_dict` and `gethash(model.nn)` behave as before."""
 from __future__ import annotations
 
+import os
+
 import torch
 from torch import Tensor, nn
 
@@ -55,7 +57,10 @@ class B200Classifier(Aggregate):
     dropout_seed  key of the in-kernel counter-based dropout masks (pass `masks=` to `fit` to supply them instead)
     process_group  torch.distributed group for data-parallel training (default: the world, if initialised)
     dp_mode     'p2p': every rank's optimizer kernel reads all ranks' gradients over NVLink peer mappings (no separate
-                collective); 'nccl': ts_fit_backward -> NCCL all-reduce -> ts_opt_apply
+                collective; right for gradients of about a megabyte); 'nccl': NCCL all-reduce of the flat gradient
+                in buckets of whole layers on a side stream, the optimizer updating each bucket as it arrives
+                (ts_opt_apply_range) -- right for large models. TSB200_DP_OVERLAP=1 instead starts each layer's all-reduce
+                during the backward pass (ts_fit_backward_overlap)
     """
 
     def __init__(self, nn: nn.Module, criterion: nn.Module, optimizer: torch.optim.Optimizer, *, precision: str = 'bf16',
@@ -86,11 +91,36 @@ class B200Classifier(Aggregate):
         self.engine.bind_optimizer(kind, step=step, **hyper)
         self._dp = parallel.DataParallel(process_group)
         self._p2p = None
+        self._overlap = False
         if self._dp.world > 1:
             self._dp.broadcast_(self.engine.params)          # same initial weights on every rank
             self.engine.sync_weights()
             if dp_mode == 'p2p':
                 self._p2p = parallel.bind_peer_gradients(self.engine, self._params, self._dp)
+            elif dp_mode == 'nccl':
+                # buckets of whole layers, at least 16 M elements each (the last one absorbs what is left)
+                self._comm = torch.cuda.Stream(device=dev)
+                self._buckets, t0, o0 = [], 0, self.engine.offsets[0]
+                n_t = len(self._params)
+                for l in range(len(spec.linears)):
+                    end_t = 2 * l + 2
+                    end_o = self.engine.offsets[end_t] if end_t < n_t else self.engine.total
+                    if end_o - o0 >= (16 << 20) or end_t == n_t:
+                        self._buckets.append((t0, end_t - t0, o0, end_o - o0))
+                        t0, o0 = end_t, end_o
+                if len(self._buckets) > 1 and self._buckets[-1][3] < (4 << 20):       # fold a small tail into its neighbour
+                    a, b = self._buckets[-2], self._buckets.pop()
+                    self._buckets[-1] = (a[0], a[1] + b[1], a[2], a[3] + b[3])
+                self._bucket_events = [torch.cuda.Event() for _ in self._buckets]
+            if dp_mode == 'nccl' and os.environ.get('TSB200_DP_OVERLAP', '0') != '0':
+                # opt-in: all-reduce per layer on a side stream, under the rest of the backward pass; the backward GEMMs
+                # leave `reserve` SMs to the collective's kernels (they cannot share an SM with a 225 KB persistent GEMM
+                # CTA). Measured slower than the bucketed scheme on 8 B200s (NCCL needs more SMs than it pays to give up).
+                self._overlap = True
+                self._layer_events = [torch.cuda.Event() for _ in spec.linears]
+                for e in self._layer_events:
+                    e.record()                               # creates the underlying cudaEvent_t
+                self.engine.reserve_sms(int(os.environ.get('TSB200_DP_RESERVE_SMS', '16')))
 
     # ------------------------------------------------------------------ identity / hooks
     @property
@@ -163,10 +193,57 @@ class B200Classifier(Aggregate):
             return self.engine.fit(inputs, targets, masks, self.dropout_seed)
         if self._p2p is not None:      # gradient all-reduce folded into the optimizer kernel over NVLink peer mappings
             return self.engine.fit(inputs, targets, masks, self.dropout_seed + self._dp.rank)
-        out = self.engine.fit(inputs, targets, masks, self.dropout_seed + self._dp.rank, update=False)
-        self._dp.all_reduce_sum_(self.engine.grads)
-        self.engine.apply(1.0 / self._dp.world)
+        if self._overlap:
+            return self._fit_overlapped(inputs, targets, masks)
+        return self._fit_bucketed(inputs, targets, masks)
+
+    def _fit_bucketed(self, inputs: Tensor, targets: Tensor, masks) -> tuple[Tensor, Tensor]:
+        """'nccl' mode: backward pass, then the flat gradient is all-reduced bucket by bucket (about 64 MB each, whole layers)
+        on a side stream while the optimizer already updates the buckets that have arrived (ts_opt_apply_range). One bucket
+        (small models) degenerates to all-reduce -> apply."""
+        eng, dp = self.engine, self._dp
+        out = eng.fit(inputs, targets, masks, self.dropout_seed + dp.rank, update=False)
+        if len(self._buckets) == 1:
+            dp.all_reduce_sum_(eng.grads)
+            eng.apply(1.0 / dp.world)
+            return out
+        main = torch.cuda.current_stream(eng.index)
+        self._comm.wait_stream(main)
+        for i, (t0, nt, o, n) in enumerate(self._buckets):
+            with torch.cuda.stream(self._comm):
+                dp.all_reduce_sum_(eng.grads[o:o + n])
+                self._bucket_events[i].record(self._comm)
+            main.wait_event(self._bucket_events[i])
+            eng.apply_range(1.0 / dp.world, t0, nt, advance=i == 0)
         return out
+
+    def _fit_overlapped(self, inputs: Tensor, targets: Tensor, masks) -> tuple[Tensor, Tensor]:
+        """'nccl' mode with the all-reduce of each layer's gradient issued on a side stream as soon as that layer's
+        backward kernels are enqueued (last layer first), so it runs under the remaining dX / dW GEMMs; the small
+        tensors that are still partial sums at that point (biases) go in one packed all-reduce at the end."""
+        eng, dp = self.engine, self._dp
+        main = torch.cuda.current_stream(eng.index)
+        pred, loss, final = eng.fit_backward_overlap(inputs, targets, masks, self.dropout_seed + dp.rank, self._layer_events)
+        n_layers = len(self._layer_events)
+        late = []
+        with torch.cuda.stream(self._comm):
+            for l in range(n_layers - 1, -1, -1):
+                self._comm.wait_event(self._layer_events[l])
+                for t in (2 * l, 2 * l + 1):
+                    o, n = eng.offsets[t], self._params[t].numel()
+                    if final[t]:
+                        dp.all_reduce_sum_(eng.grads[o:o + n])
+                    else:
+                        late.append((o, n))
+            self._comm.wait_stream(main)                 # the fold of the remaining partials is the last kernel of the call
+            if late:
+                packed = torch.cat([eng.grads[o:o + n] for o, n in late])
+                dp.all_reduce_sum_(packed)
+                for (o, n), piece in zip(late, packed.split([n for _, n in late])):
+                    eng.grads[o:o + n].copy_(piece)
+        main.wait_stream(self._comm)
+        eng.apply(1.0 / dp.world)
+        return pred, loss
 
     def evaluate(self, inputs: Tensor, targets: Tensor) -> tuple[Tensor, Tensor]:
         return self.engine.evaluate(inputs, targets)

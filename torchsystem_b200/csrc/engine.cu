@@ -58,6 +58,9 @@ struct ts_mlp {
     int prec = TS_PREC_F32;
     int device = 0;
     int sm_count = 148;
+    int bwd_sms = 148;            // SMs the backward GEMMs use: fewer than sm_count leaves room for a concurrently running collective
+    cudaEvent_t *ov_events = nullptr;   // per-call (ts_fit_backward_overlap): event of layer l recorded once its gradients are enqueued
+    int32_t *ov_final = nullptr;        // per-call out: gradient tensor t is final in `grads` when its layer's event fires
     int inkernel_cast = -1;       // fp32 batches converted inside the fused kernel: 1 always, 0 never (cast kernel in front), -1 by batch size
 
     // flat parameter layout (torch order: W0, b0, W1, b1, ...)
@@ -89,6 +92,7 @@ struct ts_mlp {
     __nv_bfloat16 *x_bf16 = nullptr, *shadow = nullptr;
     __nv_bfloat16 *x_bf16_alt = nullptr;   // second input buffer of the fused path: lets the next batch's cast overlap this step's optimizer
     int x_parity = 0;
+    bool first_step = false;      // the step being applied is the first one (SGD momentum buffer := gradient)
     // tensor-core head (bf16 mode, models the fused kernel does not take, <= 16 classes): logits / dZ operand / dW_last^T partials
     bool tc_head = false;
     float *zbuf = nullptr, *wt_partial = nullptr;
@@ -288,9 +292,12 @@ int fill_tensor_table(ts_mlp *m, const int *nsplit, OptArgs &o, bool *any_partia
 }
 
 // Advances the step counter and fills the hyper-parameters of one update.
-void fill_update(ts_mlp *m, OptArgs &o) {
-    o.first_step = m->step == 0 ? 1 : 0;
-    m->step += 1;
+void fill_update(ts_mlp *m, OptArgs &o, bool advance = true) {
+    if (advance) {
+        m->first_step = m->step == 0;
+        m->step += 1;
+    }
+    o.first_step = m->first_step ? 1 : 0;
     o.weight_decay = (float)m->hyper.weight_decay;
     o.wd_mul = (float)(1.0 - m->hyper.lr * m->hyper.weight_decay);
     o.momentum = (float)m->hyper.momentum;
@@ -433,7 +440,7 @@ int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *co
             nsplit[tb] = rows4;
         }
         ProfScope ps(K_HEAD, st);
-        rc = launch_tc_gemm(g, m->sm_count, st);
+        rc = launch_tc_gemm(g, m->bwd_sms, st);
         if (rc) return rc;
     }
     const int m_tiles = (K + 127) / 128;
@@ -449,12 +456,21 @@ int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *co
         g.epi = TC_EPI_STORE_F32; g.out = m->wt_partial; g.ldo = 16; g.splits = S; g.k_chunk = (int)kc;
         g.split_stride = (int64_t)K * 16;
         ProfScope ps(K_HEAD_WGRAD, st);
-        rc = launch_tc_gemm(g, m->sm_count, st);
+        rc = launch_tc_gemm(g, m->bwd_sms, st);
         if (rc) return rc;
         rc = launch_wlast_finish(m->wt_partial, (int64_t)K * 16, S, K, C, m->dz, B, m->grads + m->off[2 * (L - 1)],
                                  m->grads + m->off[2 * (L - 1) + 1], st);
     }
     return rc;
+}
+
+// ts_fit_backward_overlap: layer l's weight / bias gradients have been enqueued; tell the caller which of them are already
+// final in `grads` (no partials left to fold) and mark the point in the stream.
+int mark_layer_ready(ts_mlp *m, int l, const int *nsplit, cudaStream_t st) {
+    if (m->ov_events == nullptr) return TS_OK;
+    if (m->ov_final) { m->ov_final[2 * l] = nsplit[2 * l] == 0; m->ov_final[2 * l + 1] = nsplit[2 * l + 1] == 0; }
+    TS_CUDA_CHECK(cudaEventRecord(m->ov_events[l], st));
+    return TS_OK;
 }
 
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
@@ -523,6 +539,8 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         if (rc) return rc;
         nsplit[tw] = nsplit[tb] = S > 1 ? S : 0;
     }
+    rc = mark_layer_ready(m, L - 1, nsplit, st);
+    if (rc) return rc;
     int cur = 0;
     for (int l = L - 2; l >= 0; --l) {
         const int in = m->dims[l], out = m->dims[l + 1];
@@ -556,11 +574,13 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
                 g.B = (const __nv_bfloat16 *)a_prev; g.b_major = TC_MAJOR_MN; g.ldb = in;
                 g.M = out; g.N = in; g.K = (int)B;
                 g.epi = TC_EPI_STORE_F32; g.out = wp; g.ldo = in; g.splits = S; g.k_chunk = kc; g.split_stride = m->partial_stride[tw];
-                rc = launch_tc_gemm(g, m->sm_count, st);
+                rc = launch_tc_gemm(g, m->bwd_sms, st);
             }
             if (rc) return rc;
             nsplit[tw] = S > 1 ? S : 0;
         }
+        rc = mark_layer_ready(m, l, nsplit, st);
+        if (rc) return rc;
         if (l > 0) {   // dH_{l-1} = (dH_l W_l) * act'(layer l-1) * keep/(1-p)
             const DropoutSpec ds = drop_spec(m, masks, seed, l - 1, true);
             ProfScope ps(K_DX_GEMM, st);
@@ -586,7 +606,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
                     nsplit[tbp] = rows4;
                 }
                 g.drop = ds; g.training = m->p > 0.0f;
-                rc = launch_tc_gemm(g, m->sm_count, st);
+                rc = launch_tc_gemm(g, m->bwd_sms, st);
             }
             if (rc) return rc;
             cur ^= 1;
@@ -635,7 +655,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     m->n_layers = n_dims - 1;
     for (int i = 0; i < n_dims; ++i) m->dims[i] = dims[i];
     m->act = activation; m->p = dropout_p; m->scale = 1.0f / (float)(1.0 - (double)dropout_p);
-    m->prec = precision; m->device = device; m->sm_count = sms;
+    m->prec = precision; m->device = device; m->sm_count = sms; m->bwd_sms = sms;
     if (const char *e = getenv("TSB200_INKERNEL_CAST")) m->inkernel_cast = atoi(e) != 0 ? 1 : 0;
     m->n_tensors = 2 * m->n_layers;
     int64_t o = 0, so = 0;
@@ -773,11 +793,52 @@ int32_t ts_fit_backward(ts_mlp *m, const void *inputs, int32_t inputs_dtype, con
     return fit_impl(m, inputs, inputs_dtype, targets, batch, masks, seed, predictions, record, (cudaStream_t)stream, false);
 }
 
+int32_t ts_fit_backward_overlap(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
+                                const uint8_t *const *masks, uint64_t seed, int64_t *predictions, ts_batch_record *record, void *stream,
+                                void *const *layer_events, int32_t *tensor_final) {
+    TS_REQUIRE(m && layer_events && tensor_final, TS_E_INVALID, "null handle / layer_events / tensor_final");
+    for (int l = 0; l < m->n_layers; ++l) TS_REQUIRE(layer_events[l] != nullptr, TS_E_INVALID, "layer_events[%d] is null", l);
+    for (int t = 0; t < m->n_tensors; ++t) tensor_final[t] = 0;
+    m->ov_events = (cudaEvent_t *)layer_events;
+    m->ov_final = tensor_final;
+    const int rc = fit_impl(m, inputs, inputs_dtype, targets, batch, masks, seed, predictions, record, (cudaStream_t)stream, false);
+    m->ov_events = nullptr;
+    m->ov_final = nullptr;
+    return rc;
+}
+
+int32_t ts_dp_reserve_sms(ts_mlp *m, int32_t n_sms) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    TS_REQUIRE(n_sms >= 0 && n_sms < m->sm_count, TS_E_INVALID, "cannot reserve %d of %d SMs", n_sms, m->sm_count);
+    m->bwd_sms = m->sm_count - n_sms;
+    return TS_OK;
+}
+
 int32_t ts_opt_apply(ts_mlp *m, float grad_scale, void *stream) {
     TS_REQUIRE(m, TS_E_INVALID, "null handle");
     TS_REQUIRE(m->params && m->grads && m->ws_set && m->opt_bound, TS_E_STATE, "bind parameters, optimizer and workspace first");
     TS_CUDA_CHECK(cudaSetDevice(m->device));
     return run_optimizer(m, nullptr, true, grad_scale, (cudaStream_t)stream);
+}
+
+int32_t ts_opt_apply_range(ts_mlp *m, float grad_scale, int32_t first_tensor, int32_t n_tensors, int32_t advance_step, void *stream) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    TS_REQUIRE(m->params && m->grads && m->ws_set && m->opt_bound, TS_E_STATE, "bind parameters, optimizer and workspace first");
+    TS_REQUIRE(first_tensor >= 0 && n_tensors >= 1 && first_tensor + n_tensors <= m->n_tensors, TS_E_INVALID,
+               "tensor range [%d, %d) outside [0, %d)", first_tensor, first_tensor + n_tensors, m->n_tensors);
+    TS_REQUIRE(advance_step || m->step >= 1, TS_E_STATE, "the first range of a step must advance the step counter");
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    OptArgs o{};
+    bool any_partial = false;
+    int rc = fill_tensor_table(m, nullptr, o, &any_partial, (cudaStream_t)stream);
+    if (rc) return rc;
+    o.update = 1; o.grad_scale = grad_scale;
+    fill_update(m, o, advance_step != 0);
+    const int last = first_tensor + n_tensors - 1;
+    o.chunk_begin = (int)(m->off[first_tensor] / kChunk);
+    const int64_t chunk_end = (m->off[last] + round_up(m->cnt[last], kChunk)) / kChunk;
+    ProfScope ps(K_OPT, (cudaStream_t)stream);
+    return launch_optimizer(o, chunk_end - o.chunk_begin, (cudaStream_t)stream);
 }
 
 int32_t ts_eval_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,

@@ -103,6 +103,7 @@ struct OptArgs {
     const int32_t *chunk_tensor;
     int kind;
     int update;          // 0: only reduce partials into grads (data-parallel backward)
+    int chunk_begin;     // first 1024-element chunk this launch covers (ts_opt_apply_range), 0 for the whole buffer
     int partial_depth;   // partial rows in flight per thread (4 KiB of shared memory each): 16 for small models, 4 for large ones
     float grad_scale;
     float lr, beta1, beta2, eps, one_minus_beta1, one_minus_beta2, step_size, bc2_sqrt;

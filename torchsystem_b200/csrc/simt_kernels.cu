@@ -771,11 +771,12 @@ __device__ __forceinline__ void sum_partials(const float *q, int64_t stride, int
 __global__ void __launch_bounds__(256) optimizer_kernel(OptArgs p) {
     extern __shared__ float4 slots[];
     pdl_launch_dependents();
-    const int tix = p.chunk_tensor[blockIdx.x];     // static map: may be read before the predecessor has finished
+    const int chunk = (int)blockIdx.x + p.chunk_begin;
+    const int tix = p.chunk_tensor[chunk];          // static map: may be read before the predecessor has finished
     pdl_wait();
     if (tix < 0) return;
     const TensorDesc d = p.t[tix];
-    const int64_t i0 = (int64_t)blockIdx.x * kChunk + threadIdx.x * 4;
+    const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
     const int64_t j0 = i0 - d.offset;
     if (j0 >= d.count) return;
     const int n = (int)min((int64_t)4, d.count - j0);

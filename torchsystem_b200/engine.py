@@ -177,8 +177,31 @@ class Engine:
             check(rc, 'ts_fit_step')
         return pred, self.loss_views[slot]
 
+    def fit_backward_overlap(self, inputs: Tensor, targets: Tensor, masks, seed: int, events):
+        """ts_fit_backward_overlap: like fit(update=False), plus one CUDA event per layer recorded as soon as that layer's
+        gradients are enqueued. Returns (pred, loss, final) with final[t] = gradient tensor t is complete at its event."""
+        B = self._check_batch(inputs, targets)
+        pred = torch.empty(B, dtype=torch.int64, device=self.device)
+        slot = self._next_slot()
+        mptr, keep = self._masks(masks, B)
+        n = len(events)
+        evs = (C.c_void_p * n)(*[e.cuda_event for e in events])
+        final = (C.c_int32 * (2 * n))()
+        rc = lib.ts_fit_backward_overlap(self.handle, inputs.data_ptr(), self._dtype_code(inputs), targets.data_ptr(), B, mptr, seed,
+                                         pred.data_ptr(), self._ring_ptr + _lib.RECORD_BYTES * slot, self._stream(), evs, final)
+        if rc:
+            check(rc, 'ts_fit_backward_overlap')
+        return pred, self.loss_views[slot], list(final)
+
+    def reserve_sms(self, n: int) -> None:
+        check(lib.ts_dp_reserve_sms(self.handle, int(n)), 'ts_dp_reserve_sms')
+
     def apply(self, grad_scale: float = 1.0) -> None:
         check(lib.ts_opt_apply(self.handle, float(grad_scale), self._stream()), 'ts_opt_apply')
+
+    def apply_range(self, grad_scale: float, first_tensor: int, n_tensors: int, advance: bool) -> None:
+        check(lib.ts_opt_apply_range(self.handle, float(grad_scale), int(first_tensor), int(n_tensors), int(bool(advance)),
+                                     self._stream()), 'ts_opt_apply_range')
 
     def evaluate(self, inputs: Tensor, targets: Tensor):
         B = self._check_batch(inputs, targets)
