@@ -84,12 +84,13 @@ def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, to
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
-@pytest.mark.parametrize('overlap', ['0', '1'])
+@pytest.mark.parametrize('overlap', ['buckets', 'backward'])
 def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
     """'nccl' mode on a net with 2048- and 4096-wide layers: several all-reduce buckets with the optimizer applied bucket by
-    bucket (overlap '0', the default), or (overlap '1') each layer's gradient all-reduced on the side stream while the
+    bucket (TSB200_DP_BUCKETS=1), or (TSB200_DP_OVERLAP=1) each layer's gradient all-reduced on the side stream while the
     backward pass is still running, biases in a packed all-reduce at the end. Must match the full-batch oracle."""
-    monkeypatch.setenv('TSB200_DP_OVERLAP', overlap)
+    monkeypatch.setenv('TSB200_DP_OVERLAP', '1' if overlap == 'backward' else '0')
+    monkeypatch.setenv('TSB200_DP_BUCKETS', '1' if overlap == 'buckets' else '0')
     import torch.multiprocessing as mp
     from oracle import mlp_numpy as onp
     from tests.test_gpu_parity import synthetic, seeded_init

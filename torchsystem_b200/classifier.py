@@ -57,10 +57,11 @@ class B200Classifier(Aggregate):
     dropout_seed  key of the in-kernel counter-based dropout masks (pass `masks=` to `fit` to supply them instead)
     process_group  torch.distributed group for data-parallel training (default: the world, if initialised)
     dp_mode     'p2p': every rank's optimizer kernel reads all ranks' gradients over NVLink peer mappings (no separate
-                collective; right for gradients of about a megabyte); 'nccl': NCCL all-reduce of the flat gradient
-                in buckets of whole layers on a side stream, the optimizer updating each bucket as it arrives
-                (ts_opt_apply_range) -- right for large models. TSB200_DP_OVERLAP=1 instead starts each layer's all-reduce
-                during the backward pass (ts_fit_backward_overlap)
+                collective; right for gradients of about a megabyte); 'nccl': ts_fit_backward -> NCCL all-reduce of the flat gradient
+                -> ts_opt_apply -- right for large models. Opt-in variants (both measured slower on 8 B200s, see
+                _fit_bucketed): TSB200_DP_BUCKETS=1 pipelines bucketed all-reduces with per-bucket optimizer updates
+                (ts_opt_apply_range); TSB200_DP_OVERLAP=1 starts each layer's all-reduce during the backward pass
+                (ts_fit_backward_overlap)
     """
 
     def __init__(self, nn: nn.Module, criterion: nn.Module, optimizer: torch.optim.Optimizer, *, precision: str = 'bf16',
@@ -112,6 +113,7 @@ class B200Classifier(Aggregate):
                     a, b = self._buckets[-2], self._buckets.pop()
                     self._buckets[-1] = (a[0], a[1] + b[1], a[2], a[3] + b[3])
                 self._bucket_events = [torch.cuda.Event() for _ in self._buckets]
+                self._bucketed = os.environ.get('TSB200_DP_BUCKETS', '0') != '0'
             if dp_mode == 'nccl' and os.environ.get('TSB200_DP_OVERLAP', '0') != '0':
                 # opt-in: all-reduce per layer on a side stream, under the rest of the backward pass; the backward GEMMs
                 # leave `reserve` SMs to the collective's kernels (they cannot share an SM with a 225 KB persistent GEMM
@@ -198,12 +200,14 @@ class B200Classifier(Aggregate):
         return self._fit_bucketed(inputs, targets, masks)
 
     def _fit_bucketed(self, inputs: Tensor, targets: Tensor, masks) -> tuple[Tensor, Tensor]:
-        """'nccl' mode: backward pass, then the flat gradient is all-reduced bucket by bucket (about 64 MB each, whole layers)
-        on a side stream while the optimizer already updates the buckets that have arrived (ts_opt_apply_range). One bucket
-        (small models) degenerates to all-reduce -> apply."""
+        """'nccl' mode: backward pass, one all-reduce of the flat gradient, optimizer. With TSB200_DP_BUCKETS=1 the gradient
+        is instead all-reduced bucket by bucket (about 64 MB each, whole layers) on a side stream while the optimizer
+        already updates the buckets that have arrived (ts_opt_apply_range). Measured on 8 B200s, L model, 8,192 rows per
+        GPU: 3.10 ms per step plain, 3.40 ms bucketed, 3.31 ms with the all-reduce started during the backward pass
+        (TSB200_DP_OVERLAP=1): NCCL wants the whole GPU, so the plain sequence is the default."""
         eng, dp = self.engine, self._dp
         out = eng.fit(inputs, targets, masks, self.dropout_seed + dp.rank, update=False)
-        if len(self._buckets) == 1:
+        if len(self._buckets) == 1 or not self._bucketed:
             dp.all_reduce_sum_(eng.grads)
             eng.apply(1.0 / dp.world)
             return out
