@@ -2,7 +2,7 @@ import sys, time, torch
 sys.path.insert(0, '/root/repo')
 from torch import nn
 from torchsystem_b200 import B200Classifier, B200Metrics, MLP, DeviceLoader, training, _lib
-B = 4096
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 torch.manual_seed(0)
 net = MLP(784, 256, 10, dropout=0.1, activation=nn.ReLU())
 model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.01), precision='bf16', device='cuda:0', max_batch=B)
