@@ -9,7 +9,7 @@ def trace(tag):
     print(tag, 'CTA1:', {k: d[16+k]-d[16] for k in (1,2,3,4,5,8,14,15,9,12,13) if d[16+k]}, 'start skew', d[16]-d[0])
     names = {14:'z_sent',15:'cluster_waited',1:'setup',2:'first_mma',3:'last_mma_issued',4:'h_full_seen',5:'A_written',7:'A_copied',8:'z_full_seen',6:'z_mma_issued',9:'dz_written',10:'da_issued',11:'da_seen',12:'dH_done',13:'end'}
     print(tag, {names[i]: d[i]-t0 for i in sorted(names) if d[i] >= t0 and d[i]})
-for p, B in ((0.1, 4096),):
+for p, B in ((0.1, 4096), (0.0, 4096)):
     torch.manual_seed(0)
     net = MLP(784, 256, 10, dropout=p, activation=nn.ReLU())
     model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.01), precision='bf16', device='cuda:0', max_batch=B)

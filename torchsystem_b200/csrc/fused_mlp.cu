@@ -134,11 +134,11 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         for (int s = 0; s < p.xstages; ++s) { mbar_init(&xf_full_bar[s], 1); mbar_init(&xf_empty_bar[s], (kEpiThreads / 32) * ns); }
         mbar_init(&h_full_bar, 1);
         mbar_init(&w2_full_bar, 1);
-        mbar_init(&a_ready_bar, kEpiThreads);
+        mbar_init(&a_ready_bar, kEpiThreads / 32);      // one arrival per warp: 256 per-thread arrivals serialise on the barrier word
         mbar_init(&z_full_bar, 1);
-        mbar_init(&dz_ready_bar, 128);
+        mbar_init(&dz_ready_bar, 4);
         mbar_init(&da_full_bar, 1);
-        mbar_init(&dh_ready_bar, kEpiThreads);
+        mbar_init(&dh_ready_bar, kEpiThreads / 32);
         mbar_init(&g_full_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_x)) : "memory");
@@ -341,6 +341,36 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             }
         }
 
+        // ---- dropout keep decisions of this thread's row x columns, one bit per hidden unit. They depend on indices
+        //      only (counter-based hash) or on the caller's mask, so they are drawn here, while the main loop is still
+        //      running on the tensor cores. Rolled loops on purpose: this code runs once per thread, and straight-line
+        //      code that is executed once costs about a cycle per instruction in instruction fetch alone.
+        uint32_t keepb[4] = {~0u, ~0u, ~0u, ~0u};
+        const bool dropout_on = TRAIN && p.training && p.drop.p > 0.0f;
+        if (dropout_on && row_ok) {
+#pragma unroll 1
+            for (int ci = 0; ci < 4; ++ci) {
+                const int c0 = cbeg + 32 * ci;
+                if (c0 >= cend) break;
+                uint32_t kb = 0;
+                if (p.drop.mask == nullptr) {
+#pragma unroll 2
+                    for (int j = 0; j < 32; j += 2) {
+                        const uint32_t h = dropout_bits(p.drop.key, row, (n0 + c0 + j) >> 1);
+                        kb |= ((h & 0xFFFFu) >= p.drop.thresh ? 1u : 0u) << j;
+                        kb |= ((h >> 16) >= p.drop.thresh ? 1u : 0u) << (j + 1);
+                    }
+                } else {
+                    const uint8_t *mrow = p.drop.mask + row * (int64_t)p.H + n0 + c0;
+#pragma unroll 4
+                    for (int j = 0; j < 32; ++j) kb |= (mrow[j] != 0 ? 1u : 0u) << j;
+                }
+                if (ci == 0) keepb[0] = kb; else if (ci == 1) keepb[1] = kb; else if (ci == 2) keepb[2] = kb; else keepb[3] = kb;
+            }
+        }
+        // keep the draws on this side of the wait below (the compiler would otherwise sink them next to their use)
+        asm volatile("" ::"r"(keepb[0]), "r"(keepb[1]), "r"(keepb[2]), "r"(keepb[3]) : "memory");
+
         // ---- A = relu(dropout(H + b1)) -> bf16 -> swizzled K-major tile
         uint32_t sign[4] = {0, 0, 0, 0};
         if (elect_one()) mbar_wait(&h_full_bar, 0);
@@ -353,10 +383,15 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             tmem_ld16(t_lane + (uint32_t)c0, *reinterpret_cast<float(*)[16]>(&v[0]));
             tmem_ld16(t_lane + (uint32_t)(c0 + 16), *reinterpret_cast<float(*)[16]>(&v[16]));
             uint32_t bits = 0;
+            const int ci_k = (c0 - cbeg) >> 5;
+            const uint32_t kb = ci_k == 0 ? keepb[0] : ci_k == 1 ? keepb[1] : ci_k == 2 ? keepb[2] : keepb[3];
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
                 float keep[4] = {1.0f, 1.0f, 1.0f, 1.0f};
-                if (TRAIN && p.training && row_ok) p.drop.factor4(row, n0 + c0 + j, p.H, keep);
+                if (dropout_on) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) keep[i] = ((kb >> (j + i)) & 1u) ? p.drop.scale : 0.0f;
+                }
                 const float4 bb = *reinterpret_cast<const float4 *>(&b1s[c0 + j]);
                 const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
@@ -382,7 +417,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         }
         fence_proxy_async_smem();          // the tensor core reads this tile through the async proxy
         tc_fence_before();
-        mbar_arrive(&a_ready_bar);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_ready_bar);
         if (et == 0) TRACE(5);
 
         // ---- coalesced copy of this warp's rows x columns of a bf16 tile held in a_stage to a global [B, H] matrix
@@ -420,8 +456,9 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             if (ns > 1) {
                 // every CTA holds the logits of its slice of the hidden units only: all-gather the partial logits
                 // through distributed shared memory, then every CTA adds them up in the same (rank) order
+                // (this warp sends to the lower half of the ranks, its idle twin of the other column half to the upper)
                 const uint32_t mine = smem_u32(zbuf + ((size_t)rank * BM + r_local) * CP);
-                for (int t = 0; t < ns; ++t) {
+                for (int t = 0; t < (ns >> 1); ++t) {
                     const uint32_t dst = map_to_rank(mine, (uint32_t)t);
 #pragma unroll
                     for (int c = 0; c < CP; c += 4) st_cluster_v4(dst + c * 4, z[c], z[c + 1], z[c + 2], z[c + 3]);
@@ -490,7 +527,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 *reinterpret_cast<uint4 *>(drow + ((1 ^ (r_local & 7)) << 4)) = c1v;
                 fence_proxy_async_smem();
                 tc_fence_before();
-                mbar_arrive(&dz_ready_bar);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&dz_ready_bar);
                 if (et == 0) TRACE(9);
                 if (p.w2_partial != nullptr && rank == 0) {
                     // db2[c] = sum_r dz[r, c] (fp32), off the critical path: the dA MMA is already running
@@ -502,7 +540,20 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 }
             }
         } else if (ns > 1) {
-            cluster_arrive();                            // phase 1: nothing to exchange from these warps
+            // the other column half's warps have nothing to compute here: they carry the same rows' partial logits to
+            // the upper half of the cluster (the same TMEM lanes are readable by both warps of a lane quarter)
+            if (elect_one()) mbar_wait(&z_full_bar, 0);
+            __syncwarp();
+            tc_fence_after();
+            float z[CP];
+            tmem_ld16(t_lane + (uint32_t)kZCol, z);
+            const uint32_t mine = smem_u32(zbuf + ((size_t)rank * BM + r_local) * CP);
+            for (int t = ns >> 1; t < ns; ++t) {
+                const uint32_t dst = map_to_rank(mine, (uint32_t)t);
+#pragma unroll
+                for (int c = 0; c < CP; c += 4) st_cluster_v4(dst + c * 4, z[c], z[c + 1], z[c + 2], z[c + 3]);
+            }
+            cluster_arrive();                            // phase 1: these warps only have to have arrived
         }
 
         if (TRAIN) {
@@ -535,8 +586,8 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             }
             fence_proxy_async_smem();
             tc_fence_before();
-            mbar_arrive(&dh_ready_bar);
             __syncwarp();
+            if (lane == 0) mbar_arrive(&dh_ready_bar);
             if (p.dH_out != nullptr) copy_out(p.dH_out, dh_stage);
 
             if (p.w2_partial != nullptr) {
