@@ -188,7 +188,7 @@ class OracleMLP:
         gb[-1] = dz.sum(axis=0)
         da = rnd(dz) @ rnd(self.weights[-1])
         for l in range(n - 2, -1, -1):
-            g = _act_grad(pre[l], acts[l + 1], self.activation)
+            g = _act_grad(rnd(pre[l]), acts[l + 1], self.activation)     # tensor-core mode stores the pre-activation in bf16
             if masks is not None and self.dropout > 0.0:
                 g = g * (masks[l].astype(np.float32) * scale)
             dh = (da * g).astype(np.float32)

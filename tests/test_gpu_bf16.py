@@ -157,3 +157,29 @@ def test_many_row_blocks_two_level_partial_sum(precision, tol):
         assert (pr.cpu().numpy() != opr).mean() <= (1e-3 if bf16 else 0.0)
         assert l.item() == pytest.approx(float(ol), rel=tol)
     assert_params_close(net_params(net), oracle.parameters(), tol, lr=1e-2, steps=steps, adam=False)
+
+
+@pytest.mark.parametrize('dims', [[784, 512, 10], [784, 256, 128, 10]])
+def test_bf16_gelu_against_emulating_oracle(dims):
+    """GELU in the tensor-core mode: layer-by-layer tcgen05 path with the pre-activations kept in bf16 for gelu'
+    (the oracle rounds them at the same point), dropout masks supplied; loss and weights within 1e-2."""
+    p, B, steps = 0.1, 2048, 3
+    x, y = synthetic(B * steps + B)
+    x = x.bfloat16().float()
+    init = seeded_init(dims, bf16=True)
+    model, net = build_model(dims, p, 'gelu', 'sgd', 1e-2, init, 'bf16', max_batch=B)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, activation=onp.ACT_GELU, opt_kind=OPT['sgd'], lr=1e-2,
+                           emulate_bf16=True)
+    g = torch.Generator().manual_seed(42)
+    for s in range(steps):
+        xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
+        masks = [(torch.rand(B, h, generator=g) >= p).to(torch.uint8) for h in dims[1:-1]]
+        pr, l = model.fit(xb.cuda(), yb.cuda(), masks=[k.cuda() for k in masks])
+        opr, ol = oracle.fit(xb.numpy(), yb.numpy(), [k.numpy() for k in masks])
+        assert (pr.cpu().numpy() != opr).mean() <= 2e-3
+        assert l.item() == pytest.approx(float(ol), rel=1e-2)
+    pr, l = model.evaluate(x[steps * B:].cuda(), y[steps * B:].cuda())
+    opr, ol = oracle.evaluate(x[steps * B:].numpy(), y[steps * B:].numpy())
+    assert (pr.cpu().numpy() != opr).mean() <= 2e-3
+    assert l.item() == pytest.approx(float(ol), rel=1e-2)
+    assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=1e-2, steps=steps, adam=False)

@@ -229,6 +229,7 @@ int forward_hidden(ts_mlp *m, const void *x, int x_dtype, int64_t B, const uint8
             g.B = m->shadow + m->shadow_off[l]; g.b_major = TC_MAJOR_K; g.ldb = in;
             g.M = (int)B; g.N = out; g.K = in;
             g.epi = TC_EPI_FWD; g.out = m->acts[l]; g.ldo = out; g.splits = 1; g.split_stride = 0;
+            g.act = m->act; g.U_out = (__nv_bfloat16 *)m->upre[l];      // GELU: pre-activations kept in bf16
             g.bias = m->params + m->off[2 * l + 1];
             g.drop = ds; g.training = training && m->p > 0.0f;
             rc = launch_tc_gemm(g, m->sm_count, st);
@@ -432,7 +433,8 @@ int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *co
         g.B = m->shadow + m->shadow_off[L - 1]; g.b_major = TC_MAJOR_MN; g.ldb = K;
         g.M = (int)B; g.N = K; g.K = 16;
         g.epi = TC_EPI_ACTGRAD; g.out = m->dh[0]; g.ldo = K; g.splits = 1;
-        g.A_prev = (const __nv_bfloat16 *)a_last;
+        g.act = m->act;
+        g.A_prev = m->act == TS_ACT_RELU ? (const __nv_bfloat16 *)a_last : (const __nv_bfloat16 *)m->upre[L - 2];
         g.drop = drop_spec(m, masks, seed, L - 2, true); g.training = m->p > 0.0f;
         const int tb = 2 * (L - 2) + 1, rows4 = 4 * (int)((B + 127) / 128);
         if (rows4 <= kMaxRowBlocks) {    // db of the last hidden layer = column sums of this dH, taken in the epilogue
@@ -599,7 +601,8 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
                 g.B = m->shadow + m->shadow_off[l]; g.b_major = TC_MAJOR_MN; g.ldb = in;
                 g.M = (int)B; g.N = in; g.K = out;
                 g.epi = TC_EPI_ACTGRAD; g.out = m->dh[cur ^ 1]; g.ldo = in; g.splits = 1;
-                g.A_prev = (const __nv_bfloat16 *)m->acts[l - 1];
+                g.act = m->act;
+                g.A_prev = m->act == TS_ACT_RELU ? (const __nv_bfloat16 *)m->acts[l - 1] : (const __nv_bfloat16 *)m->upre[l - 1];
                 const int tbp = 2 * (l - 1) + 1, rows4 = 4 * (int)((B + 127) / 128);
                 if (rows4 <= kMaxRowBlocks) {    // db of layer l-1 = column sums of the dH this GEMM stores
                     g.colsum_out = m->partials + m->partial_off[tbp]; g.colsum_stride = m->partial_stride[tbp];
@@ -639,7 +642,8 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     for (int i = 1; i < n_dims - 1; ++i)
         TS_REQUIRE(dims[i] % 8 == 0, TS_E_UNSUPPORTED, "hidden width %d must be a multiple of 8", dims[i]);
     if (precision == TS_PREC_BF16) {
-        TS_REQUIRE(activation == TS_ACT_RELU, TS_E_UNSUPPORTED, "TS_PREC_BF16 supports ReLU only (use TS_PREC_F32 for GELU)");
+        TS_REQUIRE(activation == TS_ACT_RELU || dims[n_dims - 1] <= 16, TS_E_UNSUPPORTED,
+                   "TS_PREC_BF16 with GELU needs at most 16 classes (tensor-core last layer); use TS_PREC_F32");
         TS_REQUIRE(dims[0] % 8 == 0, TS_E_UNSUPPORTED, "TS_PREC_BF16 needs an input width that is a multiple of 8 (TMA pitch)");
     }
     int n_dev = 0;
@@ -674,9 +678,10 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
         so += round_up(in * (l < m->n_layers - 1 ? outw : (outw > 16 ? outw : 16)), 128);   // last layer: at least 16 class rows
     }
     m->shadow_total = so;
-    m->fused = precision == TS_PREC_BF16 && m->n_layers == 2 && fused_mlp_supported(dims[0], dims[1], dims[2]);
+    m->fused = precision == TS_PREC_BF16 && m->n_layers == 2 && activation == TS_ACT_RELU && fused_mlp_supported(dims[0], dims[1], dims[2]);
     m->tc_head = precision == TS_PREC_BF16 && !m->fused && dims[n_dims - 1] <= 16;
-    if (const char *e = getenv("TSB200_SIMT_HEAD")) m->tc_head = m->tc_head && atoi(e) == 0;   // A/B switch for measurements
+    if (const char *e = getenv("TSB200_SIMT_HEAD"))      // A/B switch for measurements (GELU always takes the tensor-core last layer)
+        m->tc_head = m->tc_head && (atoi(e) == 0 || activation == TS_ACT_GELU);
     m->total = o;
     m->n_chunks = o / kChunk;
     m->chunk_tensor_host.assign((size_t)m->n_chunks, -1);

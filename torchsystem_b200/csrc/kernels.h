@@ -162,7 +162,9 @@ struct TcGemmArgs {
     int k_chunk;           // K elements per split (multiple of 64); 0 = derive from splits
     int64_t split_stride;  // elements between split outputs
     const float *bias;             // FWD: [N]
-    const __nv_bfloat16 *A_prev;   // ACTGRAD: the layer's own bf16 output [M][ldo]
+    const __nv_bfloat16 *A_prev;   // ACTGRAD: the layer's own bf16 output [M][ldo] (ReLU), or its stored pre-activation (GELU)
+    int act;                       // TS_ACT_RELU / TS_ACT_GELU (FWD and ACTGRAD)
+    __nv_bfloat16 *U_out;          // FWD, GELU: post-dropout pre-activation [M][ldo], kept for the backward pass
     float *colsum_out;             // ACTGRAD (optional): column sums of the stored output per 32-row group -> row (4 * row_tile + quarter)
     int64_t colsum_stride;         //   of this array (the hidden-layer bias gradient partials; fixed order, no atomics)
     DropoutSpec drop;

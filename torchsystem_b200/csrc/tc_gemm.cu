@@ -42,6 +42,8 @@ struct TcParams {
     int64_t ldo, split_stride;
     const float *bias;
     const __nv_bfloat16 *A_prev;
+    __nv_bfloat16 *U_out;
+    int act;
     float *colsum_out;
     int64_t colsum_stride;
     DropoutSpec drop;
@@ -271,9 +273,43 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                             // Linear bias, Dropout, ReLU (mlp.py:14-16), all in fp32 on the accumulator
                             float keep[4] = {1.0f, 1.0f, 1.0f, 1.0f};
                             if (p.training) p.drop.factor4((int64_t)row, n, p.N, keep);
+                            if (p.act == TS_ACT_RELU) {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (j < nv) w[j] = fmaxf((w[j] + p.bias[n + j]) * keep[j], 0.0f);
+                                for (int j = 0; j < 4; ++j)
+                                    if (j < nv) w[j] = fmaxf((w[j] + p.bias[n + j]) * keep[j], 0.0f);
+                            } else {
+                                // GELU: the post-dropout pre-activation is kept (bf16) for the backward pass
+                                float u[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                                for (int j = 0; j < 4; ++j)
+                                    if (j < nv) { u[j] = (w[j] + p.bias[n + j]) * keep[j]; w[j] = gelu_f(u[j]); }
+                                __nv_bfloat16 *uo = p.U_out + (int64_t)row * p.ldo + n;
+                                if (nv == 4 && (p.ldo & 3) == 0) {
+                                    const __nv_bfloat162 ulo = __floats2bfloat162_rn(u[0], u[1]), uhi = __floats2bfloat162_rn(u[2], u[3]);
+                                    uint2 upk;
+                                    upk.x = *reinterpret_cast<const uint32_t *>(&ulo);
+                                    upk.y = *reinterpret_cast<const uint32_t *>(&uhi);
+                                    *reinterpret_cast<uint2 *>(uo) = upk;
+                                } else {
+                                    for (int j = 0; j < nv; ++j) uo[j] = __float2bfloat16_rn(u[j]);
+                                }
+                            }
+                        } else if (p.act != TS_ACT_RELU) {
+                            // dH = dA * gelu'(u) * keep/(1-p), u = the stored pre-activation (a dropped unit has u = 0 and
+                            // gelu'(0) = 1/2, so the keep factor is applied explicitly)
+                            float keep[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+                            if (p.training) p.drop.factor4((int64_t)row, n, p.N, keep);
+                            float u[4];
+                            if (nv == 4 && (p.ldo & 3) == 0) {
+                                const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162 *>(&prev[i].x);
+                                const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162 *>(&prev[i].y);
+                                u[0] = __low2float(lo); u[1] = __high2float(lo); u[2] = __low2float(hi); u[3] = __high2float(hi);
+                            } else {
+                                const __nv_bfloat16 *ap = p.A_prev + (int64_t)row * p.ldo + n;
+                                for (int j = 0; j < 4; ++j) u[j] = j < nv ? __bfloat162float(ap[j]) : 0.0f;
+                            }
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) w[j] = w[j] * gelu_grad_f(u[j]) * keep[j];
                         } else {
                             // dH = dA * relu'(A_prev) / (1-p): A_prev > 0 implies the unit was kept
                             const float sc = p.training ? p.drop.scale : 1.0f;
@@ -437,6 +473,7 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     TS_REQUIRE(a.M >= 1 && a.N >= 1 && a.K >= 1, TS_E_INVALID, "tc gemm: bad shape %d x %d x %d", a.M, a.N, a.K);
     TS_REQUIRE(a.splits >= 1 && (a.splits == 1 || a.epi == TC_EPI_STORE_F32), TS_E_INVALID, "split-K needs the fp32 store epilogue");
     TS_REQUIRE(a.k_chunk % KATOM == 0, TS_E_INVALID, "tc gemm: k_chunk %d is not a multiple of %d", a.k_chunk, KATOM);
+    TS_REQUIRE(a.epi != TC_EPI_FWD || a.act == TS_ACT_RELU || a.U_out != nullptr, TS_E_INVALID, "tc gemm: the GELU forward epilogue needs U_out");
     TcParams p{};
     p.M = a.M; p.N = a.N; p.K = a.K;
     p.a_major = a.a_major; p.b_major = a.b_major;
@@ -470,7 +507,7 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     while ((int)p.acc_stride < p.BN) p.acc_stride <<= 1;
     p.tmem_cols = 2 * p.acc_stride;
     p.out = a.out; p.ldo = a.ldo; p.split_stride = a.split_stride;
-    p.bias = a.bias; p.A_prev = a.A_prev; p.colsum_out = a.colsum_out; p.colsum_stride = a.colsum_stride;
+    p.bias = a.bias; p.A_prev = a.A_prev; p.U_out = a.U_out; p.act = a.act; p.colsum_out = a.colsum_out; p.colsum_stride = a.colsum_stride;
     p.drop = a.drop; p.training = a.training;
     p.dbg = a.dbg;
 
