@@ -50,6 +50,7 @@ extern "C" {
 /* element type of the `inputs` buffer */
 #define TS_DT_F32 0
 #define TS_DT_BF16 1
+#define TS_DT_U8 2 /* raw pixels, mapped through the table given to ts_mlp_set_input_lut */
 
 /* optimizer (examples/tinysys/main.py:62 ships Adam(lr=1e-3); SGD is the north-star addition) */
 #define TS_OPT_SGD 0
@@ -105,6 +106,12 @@ int32_t ts_mlp_destroy(ts_mlp *m);
 
 /* offsets[2*(n_dims-1)] (HOST, in elements) of each parameter tensor in the flat buffers; *total = buffer length. */
 int32_t ts_mlp_param_layout(const ts_mlp *m, int64_t *offsets /*HOST*/, int64_t *total /*HOST*/);
+
+/* uint8 inputs (TS_DT_U8): every byte is replaced by lut256[byte] on its way into the first layer -- the per-sample
+ * ToTensor() + Normalize((0.1307,), (0.3081,)) of the reference's dataset (examples/tinysys/datasets/mnist.py:7) moved
+ * onto the device, so a batch costs 1 byte per pixel of PCIe / HBM traffic instead of 4. lut256: HOST array of 256 floats
+ * (fill it with the host-side arithmetic you want reproduced, e.g. (b / 255 - mean) / std in fp32). */
+int32_t ts_mlp_set_input_lut(ts_mlp *m, const float *lut256 /*HOST*/);
 
 /* Alias the caller's parameter and gradient storage (fp32 master weights stay where torch sees them). */
 int32_t ts_mlp_bind_params(ts_mlp *m, float *params, float *grads);

@@ -271,3 +271,38 @@ def test_errors_are_loud():
     with pytest.raises(TypeError):
         B200Classifier(nn.Sequential(nn.Linear(4, 4), nn.Tanh(), nn.Linear(4, 2)), nn.CrossEntropyLoss(),
                        torch.optim.SGD(net.parameters(), lr=0.1), device='cuda:0')
+
+
+@pytest.mark.parametrize('precision,tol', [('f32', 1e-5), ('bf16', 1e-2)])
+def test_uint8_inputs_reproduce_the_host_transform(precision, tol):
+    """Raw uint8 images with uint8_norm=(mean, std) must give what the reference's dataset transform
+    (ToTensor + Normalize, examples/tinysys/datasets/mnist.py:7) followed by the float path gives."""
+    from torchsystem_b200 import B200Classifier, MLP
+    dims, B, mean, std = [784, 256, 10], 1000, 0.1307, 0.3081
+    g = torch.Generator().manual_seed(3)
+    xu = torch.randint(0, 256, (2 * B, 1, 28, 28), generator=g, dtype=torch.uint8)
+    y = torch.randint(0, 10, (2 * B,), generator=g)
+    xf = xu.to(torch.float32).div(255).sub(mean).div(std)          # what ToTensor() + Normalize produce
+    init = seeded_init(dims, bf16=precision == 'bf16')
+    out = []
+    for raw in (False, True):
+        net = MLP(784, 256, 10, dropout=0.0, activation=nn.ReLU())
+        with torch.no_grad():
+            for p, w in zip([q for lin in net.linears() for q in (lin.weight, lin.bias)], init):
+                p.copy_(torch.from_numpy(np.asarray(w)))
+        model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
+                               device='cuda:0', max_batch=B, uint8_norm=(mean, std) if raw else None)
+        x = xu if raw else xf
+        pr, l = model.fit(x[:B].cuda(), y[:B].cuda())
+        pe, le = model.evaluate(x[B:].cuda(), y[B:].cuda())
+        out.append([pr.cpu(), l.cpu(), pe.cpu(), le.cpu()] + [q.detach().cpu().clone() for q in net.parameters()])
+    for a, b in zip(*out):
+        assert torch.equal(a, b)          # same bits: the table holds exactly the host transform's 256 results
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=precision == 'bf16')
+    opr, ol = oracle.fit(xf[:B].numpy(), y[:B].numpy(), None)
+    assert (out[1][0].numpy() != opr).mean() <= (0.0 if precision == 'f32' else 2e-3)
+    assert out[1][1].item() == pytest.approx(float(ol), rel=tol)
+    with pytest.raises(RuntimeError):
+        out_model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
+                                   device='cuda:0', max_batch=B)
+        out_model.fit(xu[:B].cuda(), y[:B].cuda())        # uint8 without a normalisation table: loud

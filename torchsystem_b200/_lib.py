@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, 'libtsb200.so')
 
 TS_ACT_RELU, TS_ACT_GELU = 0, 1
 TS_PREC_F32, TS_PREC_BF16 = 0, 1
-TS_DT_F32, TS_DT_BF16 = 0, 1
+TS_DT_F32, TS_DT_BF16, TS_DT_U8 = 0, 1, 2
 TS_OPT_SGD, TS_OPT_ADAM = 0, 1
 RECORD_BYTES = 16
 STATE_BYTES = 32
@@ -40,6 +40,7 @@ PROTOTYPES = {
                                   C.c_int32, C.c_int32]),
     'ts_mlp_destroy': (C.c_int32, [C.c_void_p]),
     'ts_mlp_param_layout': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    'ts_mlp_set_input_lut': (C.c_int32, [C.c_void_p, C.POINTER(C.c_float)]),
     'ts_mlp_bind_params': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p]),
     'ts_opt_bind': (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(OptHyper), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     'ts_opt_step_count': (C.c_int64, [C.c_void_p]),

@@ -56,6 +56,9 @@ class B200Classifier(Aggregate):
     precision   'bf16' (tcgen05 tensor cores, fp32 accumulate; parity 1e-2) or 'f32' (SIMT; parity 1e-5)
     dropout_seed  key of the in-kernel counter-based dropout masks (pass `masks=` to `fit` to supply them instead)
     process_group  torch.distributed group for data-parallel training (default: the world, if initialised)
+    uint8_norm  (mean, std): `fit` / `evaluate` then also take uint8 image batches and apply the dataset's
+                ToTensor() + Normalize((mean,), (std,)) (examples/tinysys/datasets/mnist.py:7) on the device, 1 byte per pixel
+                over PCIe / from HBM instead of 4
     dp_mode     'p2p': every rank's optimizer kernel reads all ranks' gradients over NVLink peer mappings (no separate
                 collective; right for gradients of about a megabyte); 'nccl': ts_fit_backward -> NCCL all-reduce of the flat gradient
                 -> ts_opt_apply -- right for large models. Opt-in variants (both measured slower on 8 B200s, see
@@ -66,7 +69,7 @@ class B200Classifier(Aggregate):
 
     def __init__(self, nn: nn.Module, criterion: nn.Module, optimizer: torch.optim.Optimizer, *, precision: str = 'bf16',
                  device: str | torch.device = 'cuda', max_batch: int = 4096, dropout_seed: int = 42, process_group=None,
-                 dp_mode: str = 'p2p'):
+                 dp_mode: str = 'p2p', uint8_norm: tuple[float, float] | None = None):
         super().__init__()
         _check_criterion(criterion)
         spec = inspect_mlp(nn)
@@ -88,6 +91,8 @@ class B200Classifier(Aggregate):
         nn.to(dev)
         self.engine = Engine(spec, precision, dev, max_batch=max_batch)
         self.engine.adopt(self._params)
+        if uint8_norm is not None:        # accept raw uint8 images: ToTensor + Normalize(mean, std) happen on the device
+            self.engine.set_input_normalization(float(uint8_norm[0]), float(uint8_norm[1]))
         step = self._adopt_optimizer_state(kind, hyper)
         self.engine.bind_optimizer(kind, step=step, **hyper)
         self._dp = parallel.DataParallel(process_group)

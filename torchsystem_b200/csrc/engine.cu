@@ -92,6 +92,10 @@ struct ts_mlp {
     __nv_bfloat16 *x_bf16 = nullptr, *shadow = nullptr;
     __nv_bfloat16 *x_bf16_alt = nullptr;   // second input buffer of the fused path: lets the next batch's cast overlap this step's optimizer
     int x_parity = 0;
+    float lut_host[256] = {0};    // uint8 inputs: table applied on the way in (ts_mlp_set_input_lut)
+    bool lut_set = false;
+    float *d_lut = nullptr;       // its device copy (workspace)
+    float *x_f32 = nullptr;       // fp32 mode: uint8 batches are expanded here
     bool first_step = false;      // the step being applied is the first one (SGD momentum buffer := gradient)
     // tensor-core head (bf16 mode, models the fused kernel does not take, <= 16 classes): logits / dZ operand / dW_last^T partials
     bool tc_head = false;
@@ -129,6 +133,8 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
     Carver c(base);
     const int L = m->n_layers;
     m->d_chunk_tensor = (int32_t *)c.take(m->n_chunks * 4);
+    m->d_lut = (float *)c.take(256 * 4);
+    m->x_f32 = m->prec == TS_PREC_F32 ? (float *)c.take(Bm * m->dims[0] * 4) : nullptr;
     m->ticket = (unsigned int *)c.take(256);
     m->head_partials = (HeadPartial *)c.take(sizeof(HeadPartial) * kMaxHeadBlocks);
     int maxH = 0;
@@ -196,8 +202,15 @@ int check_ready(const ts_mlp *m, int64_t B, bool need_opt) {
 int forward_hidden(ts_mlp *m, const void *x, int x_dtype, int64_t B, const uint8_t *const *masks, uint64_t seed,
                    bool training, const void **a0_out, const void **a_last, cudaStream_t st) {
     const void *a_in = x;
-    if (m->prec == TS_PREC_F32) {
-        TS_REQUIRE(x_dtype == TS_DT_F32, TS_E_UNSUPPORTED, "TS_PREC_F32 takes fp32 inputs");
+    if (x_dtype == TS_DT_U8) {
+        TS_REQUIRE(m->lut_set, TS_E_STATE, "uint8 inputs need ts_mlp_set_input_lut first");
+        ProfScope ps(K_CAST, st);
+        const bool f32 = m->prec == TS_PREC_F32;
+        int rc = launch_cast_u8((const uint8_t *)x, f32 ? nullptr : m->x_bf16, f32 ? m->x_f32 : nullptr, B * m->dims[0], m->d_lut, st);
+        if (rc) return rc;
+        a_in = f32 ? (const void *)m->x_f32 : (const void *)m->x_bf16;
+    } else if (m->prec == TS_PREC_F32) {
+        TS_REQUIRE(x_dtype == TS_DT_F32, TS_E_UNSUPPORTED, "TS_PREC_F32 takes fp32 or uint8 inputs");
     } else if (x_dtype == TS_DT_F32) {
         ProfScope ps(K_CAST, st);
         int rc = launch_cast_bf16((const float *)x, m->x_bf16, B * m->dims[0], st);
@@ -337,14 +350,15 @@ int run_optimizer(ts_mlp *m, const int *nsplit, bool update, float grad_scale, c
 int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks, uint64_t seed,
                   bool train, int64_t *pred, ts_batch_record *rec, const void **a0_out, cudaStream_t st) {
     const void *a0 = x;
-    TS_REQUIRE(x_dtype == TS_DT_F32 || x_dtype == TS_DT_BF16, TS_E_INVALID, "unknown inputs dtype %d", x_dtype);
+    TS_REQUIRE(x_dtype == TS_DT_F32 || x_dtype == TS_DT_BF16 || x_dtype == TS_DT_U8, TS_E_INVALID, "unknown inputs dtype %d", x_dtype);
+    TS_REQUIRE(x_dtype != TS_DT_U8 || m->lut_set, TS_E_STATE, "uint8 inputs need ts_mlp_set_input_lut first");
     // fp32 batches: a cast kernel in front, or converted inside the fused kernel (which then also leaves the bf16 copy
     // the dW1 GEMM reads). Measured on B200: on-chip conversion wins when a slab is one CTA (large batches, HBM-bound:
     // 4 B/element read once instead of 4 + 2 + 2), and loses when the slab is a cluster, where every CTA of the cluster
     // would ingest and convert the whole fp32 tile. TSB200_INKERNEL_CAST=0/1 at ts_mlp_create overrides.
     const bool inkernel = m->inkernel_cast >= 0 ? m->inkernel_cast != 0 : fused_cluster_size(B, m->dims[1], m->sm_count) == 1;
     FusedMlpArgs f{};
-    if (x_dtype == TS_DT_F32) m->x_parity ^= 1;      // both fp32 routes alternate between the two bf16 input buffers
+    if (x_dtype != TS_DT_BF16) m->x_parity ^= 1;     // every converting route alternates between the two bf16 input buffers
     __nv_bfloat16 *xb = m->x_parity ? m->x_bf16_alt : m->x_bf16;
     if (x_dtype == TS_DT_F32 && inkernel) {
         f.X_f32 = (const float *)x;
@@ -358,6 +372,12 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
         // wait, i.e. after everything older -- those readers included -- has completed.
         ProfScope ps(K_CAST, st);
         int rc = launch_cast_bf16((const float *)x, xb, B * m->dims[0], st, true);
+        if (rc) return rc;
+        a0 = xb;
+        f.X = xb;
+    } else if (x_dtype == TS_DT_U8) {   // same early-running conversion as the fp32 cast, through the 256-entry table
+        ProfScope ps(K_CAST, st);
+        int rc = launch_cast_u8((const uint8_t *)x, xb, nullptr, B * m->dims[0], m->d_lut, st, true);
         if (rc) return rc;
         a0 = xb;
         f.X = xb;
@@ -771,7 +791,20 @@ int32_t ts_mlp_set_workspace(ts_mlp *m, void *workspace, int64_t bytes, int64_t 
     // one-time set-up copies (synchronous): chunk map, ticket
     TS_CUDA_CHECK(cudaMemcpy(m->d_chunk_tensor, m->chunk_tensor_host.data(), (size_t)m->n_chunks * 4, cudaMemcpyHostToDevice));
     TS_CUDA_CHECK(cudaMemset(m->ticket, 0, 256));
+    if (m->lut_set) TS_CUDA_CHECK(cudaMemcpy(m->d_lut, m->lut_host, sizeof(m->lut_host), cudaMemcpyHostToDevice));
     m->ws_set = true;
+    return TS_OK;
+}
+
+int32_t ts_mlp_set_input_lut(ts_mlp *m, const float *lut256) {
+    TS_REQUIRE(m && lut256, TS_E_INVALID, "null argument");
+    memcpy(m->lut_host, lut256, sizeof(m->lut_host));
+    m->lut_set = true;
+    if (m->ws_set) {
+        TS_CUDA_CHECK(cudaSetDevice(m->device));
+        TS_CUDA_CHECK(cudaDeviceSynchronize());          // a batch converted with the old table may still be in flight
+        TS_CUDA_CHECK(cudaMemcpy(m->d_lut, m->lut_host, sizeof(m->lut_host), cudaMemcpyHostToDevice));
+    }
     return TS_OK;
 }
 

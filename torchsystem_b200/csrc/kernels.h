@@ -132,6 +132,9 @@ struct DpArgs {
 int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, int sm_count, cudaStream_t st);
 
 int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end = false);
+// uint8 -> lut[byte], written as bf16 (dst_bf16) or fp32 (dst_f32); exactly one destination is non-null
+int launch_cast_u8(const uint8_t *src, __nv_bfloat16 *dst_bf16, float *dst_f32, int64_t n, const float *lut, cudaStream_t st,
+                   bool wait_at_end = false);
 
 // ---------------------------------------------------------------- metrics
 int launch_metrics_accumulate(ts_metrics_state *state, const ts_batch_record *ring, int64_t ring_len, int64_t first,

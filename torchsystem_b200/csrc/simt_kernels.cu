@@ -988,6 +988,62 @@ __global__ void __launch_bounds__(256) cast_bf16_kernel(const float *__restrict_
     if (wait_at_end) pdl_wait();
 }
 
+// uint8 pixels -> lut[pixel] (ToTensor + Normalize folded into 256 values), 16 pixels per thread and iteration.
+template <typename OutT>
+__global__ void __launch_bounds__(256) cast_u8_kernel(const uint8_t *__restrict__ src, OutT *__restrict__ dst, int64_t n,
+                                                      const float *__restrict__ lut, int wait_at_end) {
+    __shared__ float s_lut[256];
+    pdl_launch_dependents();
+    if (!wait_at_end) pdl_wait();
+    s_lut[threadIdx.x] = lut[threadIdx.x];
+    __syncthreads();
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 16;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16; i < n; i += stride) {
+        if (i + 16 <= n && ((reinterpret_cast<uintptr_t>(src + i) & 15) == 0)) {
+            const uint4 raw = *reinterpret_cast<const uint4 *>(src + i);
+            const uint32_t wv[4] = {raw.x, raw.y, raw.z, raw.w};
+            float v[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = s_lut[(wv[k >> 2] >> ((k & 3) * 8)) & 0xFFu];
+            if (sizeof(OutT) == 2) {
+                uint32_t pk[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+                    pk[k] = *reinterpret_cast<const uint32_t *>(&h);
+                }
+                uint4 *o = reinterpret_cast<uint4 *>(dst + i);
+                o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            } else {
+                float4 *o = reinterpret_cast<float4 *>(dst + i);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) o[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+            }
+        } else {
+            for (int64_t e = i; e < n && e < i + 16; ++e) from_f32(dst[e], s_lut[src[e]]);
+        }
+    }
+    if (wait_at_end) pdl_wait();
+}
+
+int launch_cast_u8(const uint8_t *src, __nv_bfloat16 *dst_bf16, float *dst_f32, int64_t n, const float *lut, cudaStream_t st,
+                   bool wait_at_end) {
+    if (n <= 0) return TS_OK;
+    TS_REQUIRE((dst_bf16 != nullptr) != (dst_f32 != nullptr) && lut != nullptr, TS_E_INVALID, "cast_u8: one destination and a table");
+    int64_t blocks = (n / 16 + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    if (dst_bf16)
+        TS_CUDA_CHECK(launch_pdl(cast_u8_kernel<__nv_bfloat16>, dim3((unsigned)blocks), dim3(256), 0, st, 1, src, dst_bf16, n, lut,
+                                 wait_at_end ? 1 : 0));
+    else
+        TS_CUDA_CHECK(launch_pdl(cast_u8_kernel<float>, dim3((unsigned)blocks), dim3(256), 0, st, 1, src, dst_f32, n, lut,
+                                 wait_at_end ? 1 : 0));
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
 int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end) {
     if (n <= 0) return TS_OK;
     int64_t blocks = (n / 8 + 255) / 256;

@@ -72,6 +72,14 @@ class Engine:
         self.max_batch = int(max_batch)
         self.sync_weights()
 
+    def set_input_normalization(self, mean: float, std: float) -> None:
+        """uint8 batches are mapped through ToTensor() + Normalize((mean,), (std,)) on the device
+        (/root/reference/examples/tinysys/datasets/mnist.py:7): the 256 possible results are computed here with torch's
+        own fp32 arithmetic, so the device path reproduces the host transform bit for bit."""
+        lut = torch.arange(256, dtype=torch.uint8).to(torch.float32).div(255).sub_(mean).div_(std)
+        arr = (C.c_float * 256)(*lut.tolist())
+        check(lib.ts_mlp_set_input_lut(self.handle, arr), 'ts_mlp_set_input_lut')
+
     def view(self, index: int, shape) -> Tensor:
         o = self.offsets[index]
         n = 1
@@ -135,7 +143,9 @@ class Engine:
             return _lib.TS_DT_F32
         if x.dtype == torch.bfloat16:
             return _lib.TS_DT_BF16
-        raise TypeError(f'inputs must be float32 or bfloat16, got {x.dtype}')
+        if x.dtype == torch.uint8:
+            return _lib.TS_DT_U8          # needs set_input_normalization (the library checks)
+        raise TypeError(f'inputs must be float32, bfloat16 or uint8, got {x.dtype}')
 
     def _check_batch(self, inputs: Tensor, targets: Tensor) -> int:
         B = inputs.shape[0]
