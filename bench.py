@@ -301,6 +301,37 @@ def main():
                                          'frac_of_hbm_peak': v_rate * 3152 / 1e9 / peak,
                                          'note': 'validate handler (inference_mode, evaluate + fused metrics), fp32 inputs resident in HBM'}
 
+    # ---- the GPU incumbent: stock PyTorch eager on the same B200, same model / batch / optimizer,
+    #      fp32 and under autocast(bf16); plain library code, not part of the product
+    if not args.skip_extras and world == 1:
+        def eager(autocast):
+            torch.manual_seed(0)
+            net_e = MLP(DIMS[0], DIMS[1], DIMS[2], dropout=DROPOUT, activation=nn.ReLU()).to(dev)
+            opt_e = torch.optim.SGD(net_e.parameters(), lr=LR)
+            crit = nn.CrossEntropyLoss()
+            def step(i):
+                xb, yb = x[i * BATCH:(i + 1) * BATCH].flatten(1), y[i * BATCH:(i + 1) * BATCH]
+                opt_e.zero_grad()
+                with torch.autocast('cuda', dtype=torch.bfloat16, enabled=autocast):
+                    out = net_e(xb)
+                    loss = crit(out, yb)
+                loss.backward()
+                opt_e.step()
+                return out.argmax(1), loss
+            for i in range(16):
+                step(i)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(args.batches):
+                step(i)
+            e1.record()
+            torch.cuda.synchronize()
+            return n / (e0.elapsed_time(e1) * 1e-3)
+        extras['torch_eager_same_gpu'] = {'fp32': eager(False), 'autocast_bf16': eager(True), 'unit': 'samples/s',
+                                          'note': 'stock PyTorch eager Classifier.fit loop (zero_grad, forward, CrossEntropyLoss, backward, '
+                                                  'SGD.step, argmax) on this GPU, batch 4096, inputs resident: the GPU incumbent'}
+
     # ---- extras for BASELINE.json configs[2] and configs[3] (one GPU only; not the headline)
     if not args.skip_extras and world == 1:
         import time
