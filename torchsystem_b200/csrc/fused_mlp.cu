@@ -1,6 +1,7 @@
 // Fused forward + head (+ backward to dH) for the one-hidden-layer aggregate -- the shape the reference ships
-// (examples/tinysys/main.py:60: MLP(784, 256, 10)). One CTA owns 128 batch rows and the FULL hidden width, so
-// a whole row of the network lives on chip from the input tile to the loss:
+// (examples/tinysys/main.py:60: MLP(784, 256, 10)). A cluster of 1, 2 or 4 CTAs owns 128 batch rows (each CTA a slice
+// of the hidden width; partial logits all-gathered through distributed shared memory), so a whole row of the network
+// lives on chip from the input tile to the loss:
 //
 //   H  = X W1^T                     tcgen05.mma, X and W1 tiles by TMA, accumulator in TMEM (cols 0..H)
 //   A  = relu(dropout(H + b1))      epilogue threads (one row each), written as bf16 into a swizzled smem tile
@@ -8,6 +9,8 @@
 //   loss, argmax, dZ                per-row softmax in registers; loss sum / correct count reduced warp->CTA->grid
 //   dA = dZ W2                      third tcgen05.mma (K = 16 padded classes), overwrites TMEM cols 0..H
 //   dH = dA * relu'(A) / (1-p)      epilogue threads, bf16, coalesced store
+//   dW2^T, db1 partials             A^T dZ and dH^T 1 as MN-major tcgen05.mma over the 128 rows (TMEM cols 272..)
+// Inputs: bf16 by TMA (multicast across the cluster), or fp32 converted on chip when a slab is one CTA.
 //
 // classifier.py:22-27 (forward, loss), :31-35 (fit), :37-39 (evaluate); mlp.py:14-17; metrics.py:14-15.
 // Restrictions (else the engine uses the layer-by-layer path): hidden width 64, 128 or 256,

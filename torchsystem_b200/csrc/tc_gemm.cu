@@ -2,9 +2,11 @@
 //
 //   D[M,N] (fp32 accumulate in tensor memory) = A[M,K] * B[K,N],  bf16 operands
 //
-// One CTA computes one 128 x BN output tile (BN a multiple of 16, <= 256) over a K range (split-K across
-// blockIdx.z). Warp roles: warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + tcgen05.mma issuer (one
-// lane), warps 2..5 = epilogue (TMEM -> registers -> fused epilogue -> global). Operands are staged by
+// Persistent: one CTA per SM walks the 128 x BN output tiles (BN a multiple of 16, <= 256; split-K ranges are further
+// tiles). Warp roles: warp 0 = TMA producer of A, warp 2 = TMA producer of B (one elected lane each), warp 1 = TMEM
+// allocator + tcgen05.mma issuer, warps 3..10 = epilogue (TMEM -> registers -> fused epilogue -> global). The
+// accumulator alternates between two TMEM buffers, so a tile's epilogue overlaps the next tile's main loop.
+// Operands are staged by
 // cp.async.bulk.tensor (TMA) into 128-byte-swizzled shared-memory tiles behind a ring of mbarriers; the same
 // tile layout serves K-major and MN-major operands, which is what lets the three contractions of a Linear layer
 // run without any transposed copy:
