@@ -182,6 +182,18 @@ int32_t ts_dp_reserve_sms(ts_mlp *m, int32_t n_sms);
  * Every rank must call ts_fit_step the same number of times; a rank that never arrives makes the others trap. */
 int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bufs /*HOST*/, uint32_t *const *flag_bufs /*HOST*/);
 
+/* The same for large models, with the reduction done inside the NVSwitch (no counterpart in the reference): gradient,
+ * parameter and (bf16 mode) shadow buffers live in symmetric memory that also has a MULTICAST mapping (`*_mc`, e.g. torch
+ * symmetric memory's multicast_ptr). ts_fit_step's optimizer kernel then, per step: sums this rank's partials into
+ * `grads_local`; rank barrier; for its 1/world of the 1024-element chunks reads the cross-rank gradient sum with one
+ * multimem.ld_reduce per float4, applies SGD / Adam, and stores the new parameters and shadows through the multicast
+ * mappings, i.e. into every rank's buffers at once; rank barrier. `params_local` replaces the buffer given to
+ * ts_mlp_bind_params (copy the weights into it first), the shadow buffer holds ts_mlp_shadow_elems() bf16 elements
+ * (call ts_mlp_sync_weights after binding). flag_bufs as for ts_dp_bind. */
+int64_t ts_mlp_shadow_elems(const ts_mlp *m);
+int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_local, const float *grads_mc, float *params_local,
+                        float *params_mc, void *shadow_local, void *shadow_mc, uint32_t *const *flag_bufs /*HOST*/);
+
 /* Classifier.evaluate (examples/tinysys/tinysys/classifier.py:37-39): dropout off, no state change. */
 int32_t ts_eval_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
                      int64_t *predictions, ts_batch_record *record, void *stream);

@@ -1,6 +1,7 @@
 """Data-parallel path on real GPUs (needs >= 2 devices; skipped otherwise): two ranks over NCCL, each fitting its half
 of every global batch through B200Classifier (dp_mode 'p2p': gradient sum inside the optimizer kernel over peer
-mappings; 'nccl': ts_fit_backward -> all-reduce -> ts_opt_apply), must reproduce the single-process oracle fed the full batch;
+mappings; 'nccl': ts_fit_backward -> all-reduce -> ts_opt_apply; 'nvls': reduction inside the NVSwitch, parameters
+broadcast through multicast stores), must reproduce the single-process oracle fed the full batch;
 B200Metrics.compute() sums the counters of both ranks."""
 import os
 import socket
@@ -37,7 +38,7 @@ def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1
             p.copy_(torch.from_numpy(w))
     model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
                            device=f'cuda:{rank}', max_batch=B, dp_mode=dp_mode)
-    assert (model._p2p is not None) == (dp_mode == 'p2p')
+    assert (model._p2p is not None) == (dp_mode in ('p2p', 'nvls'))
     assert model._overlap == (dp_mode == 'nccl' and os.environ.get('TSB200_DP_OVERLAP', '0') != '0')
     metrics = B200Metrics(device=f'cuda:{rank}', log_every=0)
     half = B // world
@@ -55,7 +56,7 @@ def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
-@pytest.mark.parametrize('dp_mode', ['p2p', 'nccl'])
+@pytest.mark.parametrize('dp_mode', ['p2p', 'nccl', 'nvls'])
 @pytest.mark.parametrize('precision,tol', [('f32', 1e-5), ('bf16', 1e-2)])
 def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, tol, dp_mode):
     import torch.multiprocessing as mp
@@ -84,7 +85,7 @@ def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, to
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
-@pytest.mark.parametrize('overlap', ['buckets', 'backward'])
+@pytest.mark.parametrize('overlap', ['buckets', 'backward', 'nvls'])
 def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
     """'nccl' mode on a net with 2048- and 4096-wide layers: several all-reduce buckets with the optimizer applied bucket by
     bucket (TSB200_DP_BUCKETS=1), or (TSB200_DP_OVERLAP=1) each layer's gradient all-reduced on the side stream while the
@@ -97,7 +98,7 @@ def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
     from tests.golden_util import assert_params_close
     dims, B = (784, 4096, 4096, 2048, 10), 1024
     out = str(tmp_path / 'rank0.npz')
-    mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nccl', out, dims, B), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nvls' if overlap == 'nvls' else 'nccl', out, dims, B), nprocs=2, join=True)
     x, y = synthetic(B * 3)
     x = x.bfloat16().float()
     init = seeded_init(list(dims), seed=0, bf16=True)

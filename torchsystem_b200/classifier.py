@@ -59,7 +59,10 @@ class B200Classifier(Aggregate):
     uint8_norm  (mean, std): `fit` / `evaluate` then also take uint8 image batches and apply the dataset's
                 ToTensor() + Normalize((mean,), (std,)) (examples/tinysys/datasets/mnist.py:7) on the device, 1 byte per pixel
                 over PCIe / from HBM instead of 4
-    dp_mode     'p2p': every rank's optimizer kernel reads all ranks' gradients over NVLink peer mappings (no separate
+    dp_mode     'nvls': like 'p2p' one kernel per step and no separate collective, but for large models: every rank reduces
+                1/world of the gradient inside the NVSwitch (multimem.ld_reduce), updates that share of the parameters and
+                broadcasts them (multimem.st); needs symmetric memory with a multicast mapping.
+                'p2p': every rank's optimizer kernel reads all ranks' gradients over NVLink peer mappings (no separate
                 collective; right for gradients of about a megabyte); 'nccl': ts_fit_backward -> NCCL all-reduce of the flat gradient
                 -> ts_opt_apply -- right for large models. Opt-in variants (both measured slower on 8 B200s, see
                 _fit_bucketed): TSB200_DP_BUCKETS=1 pipelines bucketed all-reduces with per-bucket optimizer updates
@@ -103,6 +106,8 @@ class B200Classifier(Aggregate):
             self.engine.sync_weights()
             if dp_mode == 'p2p':
                 self._p2p = parallel.bind_peer_gradients(self.engine, self._params, self._dp)
+            elif dp_mode == 'nvls':
+                self._p2p = parallel.bind_nvls(self.engine, self._params, self._dp)
             elif dp_mode == 'nccl':
                 # buckets of whole layers, at least 16 M elements each (the last one absorbs what is left)
                 self._comm = torch.cuda.Stream(device=dev)

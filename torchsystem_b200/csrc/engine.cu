@@ -109,6 +109,11 @@ struct ts_mlp {
     int dp_world = 1, dp_rank = 0;
     float *dp_grads[2][kMaxRanks] = {{nullptr}};
     uint32_t *dp_flags[kMaxRanks] = {nullptr};
+    // NVLS variant (ts_dp_bind_nvls): multicast mappings of the symmetric gradient / parameter / shadow buffers
+    bool nvls = false;
+    const float *grads_mc = nullptr;
+    float *params_mc = nullptr;
+    __nv_bfloat16 *shadow_mc = nullptr, *shadow_ext = nullptr;
 
     int hidden_layers() const { return n_layers - 1; }
     int classes() const { return dims[n_layers]; }
@@ -159,6 +164,7 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
         m->x_bf16 = (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2);
         m->x_bf16_alt = m->fused ? (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2) : nullptr;
         m->shadow = (__nv_bfloat16 *)c.take(m->shadow_total * 2);
+        if (m->shadow_ext) m->shadow = m->shadow_ext;      // NVLS data parallel keeps the shadows in symmetric memory
     }
     if (m->tc_head) {
         m->zbuf = (float *)c.take(Bm * 16 * 4);
@@ -421,6 +427,11 @@ int run_dp_optimizer(ts_mlp *m, const int *nsplit, cudaStream_t st) {
     dp.world = m->dp_world; dp.rank = m->dp_rank; dp.step = (uint32_t)m->step;
     for (int r = 0; r < m->dp_world; ++r) { dp.grads[r] = m->dp_grads[parity][r]; dp.flags[r] = m->dp_flags[r]; }
     ProfScope ps(K_OPT, st);
+    if (m->nvls) {
+        o.params_mc = m->params_mc;
+        o.shadow_mc = m->prec == TS_PREC_BF16 ? m->shadow_mc : nullptr;
+        return launch_nvls_optimizer(o, dp, m->grads_mc, m->n_chunks, m->sm_count, st);
+    }
     return launch_dp_optimizer(o, dp, m->n_chunks, m->sm_count, st);
 }
 
@@ -504,7 +515,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     const int L = m->n_layers;
     const bool bf16 = m->prec == TS_PREC_BF16;
     const bool dp = m->dp_world > 1 && update;
-    if (dp) m->grads = m->dp_grads[m->step & 1][m->dp_rank];     // this step's peer-visible gradient buffer
+    if (dp && !m->nvls) m->grads = m->dp_grads[m->step & 1][m->dp_rank];     // this step's peer-visible gradient buffer
     const void *a0 = nullptr, *a_last = nullptr;
     int nsplit[2 * kMaxLayers] = {0};
     if (m->fused) {
@@ -769,6 +780,29 @@ int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bu
     }
     m->dp_world = world;
     m->dp_rank = rank;
+    return TS_OK;
+}
+
+int64_t ts_mlp_shadow_elems(const ts_mlp *m) { return m ? (m->prec == TS_PREC_BF16 ? m->shadow_total : 0) : -1; }
+
+int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_local, const float *grads_mc, float *params_local,
+                        float *params_mc, void *shadow_local, void *shadow_mc, uint32_t *const *flag_bufs) {
+    TS_REQUIRE(m && grads_local && grads_mc && params_local && params_mc && flag_bufs, TS_E_INVALID, "null argument");
+    TS_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, TS_E_INVALID, "rank %d of %d (at most %d ranks)", rank,
+               world, kMaxRanks);
+    TS_REQUIRE(m->prec != TS_PREC_BF16 || (shadow_local && shadow_mc), TS_E_INVALID, "bf16 mode needs the symmetric shadow buffer");
+    for (const void *q : {(const void *)grads_local, (const void *)grads_mc, (const void *)params_local, (const void *)params_mc,
+                          (const void *)shadow_local, (const void *)shadow_mc})
+        TS_REQUIRE(((uintptr_t)q % 256) == 0, TS_E_INVALID, "buffers must be 256-byte aligned");
+    for (int r = 0; r < world; ++r) {
+        TS_REQUIRE(flag_bufs[r] != nullptr, TS_E_INVALID, "flag array of rank %d is null", r);
+        m->dp_flags[r] = flag_bufs[r];
+    }
+    m->params = params_local; m->grads = grads_local;
+    m->grads_mc = grads_mc; m->params_mc = params_mc;
+    m->shadow_ext = (__nv_bfloat16 *)shadow_local; m->shadow_mc = (__nv_bfloat16 *)shadow_mc;
+    if (m->shadow_ext) m->shadow = m->shadow_ext;
+    m->dp_world = world; m->dp_rank = rank; m->nvls = true;
     return TS_OK;
 }
 

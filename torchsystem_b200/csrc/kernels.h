@@ -103,6 +103,8 @@ struct OptArgs {
     const int32_t *chunk_tensor;
     int kind;
     int update;          // 0: only reduce partials into grads (data-parallel backward)
+    float *params_mc;           // NVLS data parallel: multicast mappings of the parameter and shadow buffers; updates are
+    __nv_bfloat16 *shadow_mc;   //   stored through them (multimem.st) and so reach every rank. nullptr: ordinary stores
     int chunk_begin;     // first 1024-element chunk this launch covers (ts_opt_apply_range), 0 for the whole buffer
     int partial_depth;   // partial rows in flight per thread (4 KiB of shared memory each): 16 for small models, 4 for large ones
     float grad_scale;
@@ -130,6 +132,9 @@ struct DpArgs {
     uint32_t step;
 };
 int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, int sm_count, cudaStream_t st);
+// NVLS variant (large models): every rank reduces 1/world of the chunks inside the NVSwitch (multimem.ld_reduce over the
+// multicast mapping `grads_mc`), updates them and broadcasts parameters + bf16 shadows with multimem.st (a.params_mc / a.shadow_mc)
+int launch_nvls_optimizer(const OptArgs &a, const DpArgs &dp, const float *grads_mc, int64_t n_chunks, int sm_count, cudaStream_t st);
 
 int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end = false);
 // uint8 -> lut[byte], written as bf16 (dst_bf16) or fp32 (dst_f32); exactly one destination is non-null

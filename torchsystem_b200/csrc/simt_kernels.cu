@@ -725,13 +725,21 @@ __device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc 
             w[e] = w[e] - p.step_size * (m[e] / denom);                    // param.addcdiv_(exp_avg, denom, value=-step_size)
         }
     }
-    *reinterpret_cast<float4 *>(p.params + i0) = make_float4(w[0], w[1], w[2], w[3]);
+    if (p.params_mc != nullptr)      // one store, delivered to this address in every rank's parameter buffer by the NVSwitch
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p.params_mc + i0), "f"(w[0]), "f"(w[1]),
+                     "f"(w[2]), "f"(w[3]) : "memory");
+    else
+        *reinterpret_cast<float4 *>(p.params + i0) = make_float4(w[0], w[1], w[2], w[3]);
     if (use_m) *reinterpret_cast<float4 *>(p.exp_avg + i0) = make_float4(m[0], m[1], m[2], m[3]);
     if (adam) *reinterpret_cast<float4 *>(p.exp_avg_sq + i0) = make_float4(v[0], v[1], v[2], v[3]);
     if (use_x) *reinterpret_cast<float4 *>(p.max_exp_avg_sq + i0) = make_float4(x[0], x[1], x[2], x[3]);
     if (d.shadow_off >= 0 && p.shadow != nullptr) {
         __nv_bfloat16 *sh = p.shadow + d.shadow_off + j0;
-        if (n == 4 && (((uintptr_t)sh) & 7) == 0) {
+        if (p.shadow_mc != nullptr) {    // the launcher has checked that every shadowed tensor is a whole number of quads
+            __nv_bfloat162 lo = __floats2bfloat162_rn(w[0], w[1]), hi = __floats2bfloat162_rn(w[2], w[3]);
+            asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p.shadow_mc + d.shadow_off + j0),
+                         "r"(*reinterpret_cast<uint32_t *>(&lo)), "r"(*reinterpret_cast<uint32_t *>(&hi)) : "memory");
+        } else if (n == 4 && (((uintptr_t)sh) & 7) == 0) {
             __nv_bfloat162 lo = __floats2bfloat162_rn(w[0], w[1]), hi = __floats2bfloat162_rn(w[2], w[3]);
             uint2 pk;
             pk.x = *reinterpret_cast<uint32_t *>(&lo);
@@ -895,6 +903,80 @@ __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp,
     }
 }
 
+// =====================================================================================
+// Data-parallel optimizer for large models, reduction inside the NVSwitch (NVLS). All buffers involved live in symmetric
+// memory with a multicast mapping. Per step, one kernel:
+//   1. sum the split partials of every chunk into this rank's gradient buffer              (as dp_optimizer_kernel)
+//   2. barrier A across ranks: every rank's gradient is complete
+//   3. this rank owns the chunks c with c % world == rank: one multimem.ld_reduce per float4 returns the sum over all
+//      ranks (added up by the switch), SGD / Adam on it (optimizer state is only ever touched for owned chunks), and
+//      the new parameters + bf16 shadows go out through multimem.st: one store, delivered to every rank's buffer
+//   4. barrier B across ranks: everybody's parameter stores have landed (and everybody is done reading the gradients, so
+//      one gradient buffer suffices)
+// Per GPU and step this moves ~1x the gradient out and ~1.4x in over NVLink and does 1/world of the optimizer work,
+// against all-reduce (2x each way) followed by the full optimizer.
+// =====================================================================================
+__device__ __forceinline__ void rank_barrier(uint32_t *own, const DpArgs &dp, int ticket_slot, uint32_t value, bool sys_fence) {
+    __shared__ bool s_last_b;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (sys_fence) __threadfence_system(); else __threadfence();
+        const uint32_t arrived = atomicAdd(own + ticket_slot, 1u);
+        s_last_b = arrived == gridDim.x - 1;
+        if (s_last_b) own[ticket_slot] = 0u;
+    }
+    __syncthreads();
+    if (s_last_b && threadIdx.x < dp.world)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dp.flags[threadIdx.x] + dp.rank), "r"(value) : "memory");
+    if (threadIdx.x < dp.world) {
+        const uint32_t *mine = own + threadIdx.x;
+        uint32_t spins = 0, seen;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+            if ((int32_t)(seen - value) >= 0) break;
+            __nanosleep(64);
+            if (++spins > (1u << 24)) __trap();                    // a peer never arrived: fail loudly instead of hanging
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) nvls_optimizer_kernel(OptArgs p, DpArgs dp, const float *grads_mc, int n_chunks) {
+    extern __shared__ float4 slots[];
+    pdl_launch_dependents();
+    uint32_t *own = dp.flags[dp.rank];
+    pdl_wait();
+    for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const int tix = p.chunk_tensor[chunk];
+        if (tix < 0) continue;
+        const TensorDesc d = p.t[tix];
+        const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+        const int64_t j0 = i0 - d.offset;
+        if (j0 >= d.count || d.nsplit <= 0) continue;
+        const int n = (int)min((int64_t)4, d.count - j0);
+        float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        sum_partials(p.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, p.partial_depth);
+        *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], n > 1 ? g[1] : 0.0f, n > 2 ? g[2] : 0.0f, n > 3 ? g[3] : 0.0f);
+    }
+    rank_barrier(own, dp, 8, 2u * dp.step, false);
+    const int n_owned = (n_chunks - dp.rank + dp.world - 1) / dp.world;
+    for (int j = blockIdx.x; j < n_owned; j += gridDim.x) {
+        const int chunk = j * dp.world + dp.rank;
+        const int tix = p.chunk_tensor[chunk];
+        if (tix < 0) continue;
+        const TensorDesc d = p.t[tix];
+        const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+        const int64_t j0 = i0 - d.offset;
+        if (j0 >= d.count) continue;
+        const int n = (int)min((int64_t)4, d.count - j0);
+        float g[4];
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(g[0]), "=f"(g[1]), "=f"(g[2]), "=f"(g[3]) : "l"(grads_mc + i0) : "memory");
+        apply_update(p, d, i0, j0, n, g);
+    }
+    rank_barrier(own, dp, 9, 2u * dp.step + 1u, true);
+}
+
 // 64 KiB of dynamic shared memory needs the opt-in attribute, once per device.
 static int ensure_optimizer_smem() {
     static bool done[64] = {false};
@@ -903,6 +985,7 @@ static int ensure_optimizer_smem() {
     if (!done[dev & 63]) {
         TS_CUDA_CHECK(cudaFuncSetAttribute(dp_optimizer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPartialSmem));
         TS_CUDA_CHECK(cudaFuncSetAttribute(optimizer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPartialSmem));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(nvls_optimizer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPartialSmem));
         done[dev & 63] = true;
     }
     return TS_OK;
@@ -953,6 +1036,22 @@ int launch_reduce_partials(float *partials, const ReduceArgs &r, cudaStream_t st
     }
     const dim3 grid((unsigned)((max_count + 1023) / 1024), (unsigned)max_groups, (unsigned)r.n);
     TS_CUDA_CHECK(launch_pdl(reduce_partials_kernel, grid, dim3(256), 0, st, 1, partials, r));
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+int launch_nvls_optimizer(const OptArgs &a, const DpArgs &dp, const float *grads_mc, int64_t n_chunks, int sm_count, cudaStream_t st) {
+    int rc = ensure_optimizer_smem();
+    if (rc) return rc;
+    TS_REQUIRE(grads_mc != nullptr && a.params_mc != nullptr, TS_E_INVALID, "nvls optimizer: multicast mappings missing");
+    for (int t = 0; t < a.n_tensors; ++t)
+        TS_REQUIRE(a.shadow_mc == nullptr || a.t[t].shadow_off < 0 || a.t[t].count % 4 == 0, TS_E_UNSUPPORTED,
+                   "nvls optimizer: weight tensor %d has %lld elements, not a multiple of 4", t, (long long)a.t[t].count);
+    // every CTA spins at the two barriers: the grid must be co-resident (3 CTAs per SM fit at 64 KiB of shared memory each)
+    int64_t grid = (int64_t)sm_count * 2;
+    if (grid > n_chunks) grid = n_chunks;
+    TS_CUDA_CHECK(launch_pdl(nvls_optimizer_kernel, dim3((unsigned)grid), dim3(256), (size_t)a.partial_depth * 4096, st, 1, a, dp, grads_mc,
+                             (int)n_chunks));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }

@@ -73,3 +73,41 @@ def bind_peer_gradients(engine, params, dp: DataParallel):
         o, n = engine.offsets[i], p.numel()
         p.grad = engine.grads[o:o + n].view(p.shape)
     return gbuf, flags, hg, hf
+
+
+def bind_nvls(engine, params, dp: DataParallel):
+    """Data parallel for large models with the gradient reduced inside the NVSwitch: move the flat parameter, gradient and
+    bf16 shadow buffers into torch symmetric memory, take their multicast mappings and hand everything to the library
+    (ts_dp_bind_nvls). Returns the objects that must stay alive; raises if the fabric offers no multicast mapping."""
+    import ctypes as C
+    import torch.distributed._symmetric_memory as symm
+    from ._lib import lib, check
+    group = dp.group if dp.group is not None else dist.group.WORLD
+    dev, total = engine.device, engine.total
+    n_shadow = int(lib.ts_mlp_shadow_elems(engine.handle))
+    with torch.cuda.device(engine.index):
+        gbuf = symm.empty(total, dtype=torch.float32, device=dev)
+        pbuf = symm.empty(total, dtype=torch.float32, device=dev)
+        sbuf = symm.empty(max(n_shadow, 128), dtype=torch.bfloat16, device=dev)
+        flags = symm.empty(64, dtype=torch.int32, device=dev)
+        gbuf.zero_(); sbuf.zero_(); flags.zero_()
+        pbuf.copy_(engine.params)
+        handles = [symm.rendezvous(t, group) for t in (gbuf, pbuf, sbuf, flags)]
+        torch.cuda.synchronize(engine.index)
+    hg, hp, hs, hf = handles
+    if not (hg.multicast_ptr and hp.multicast_ptr and hs.multicast_ptr):
+        raise RuntimeError('symmetric memory on this system has no multicast mapping (NVLS): use dp_mode="nccl"')
+    dist.barrier(group=dp.group)
+    world, rank = dp.world, dp.rank
+    fptrs = (C.c_void_p * world)(*[hf.buffer_ptrs[r] for r in range(world)])
+    check(lib.ts_dp_bind_nvls(engine.handle, rank, world, gbuf.data_ptr(), hg.multicast_ptr, pbuf.data_ptr(), hp.multicast_ptr,
+                              sbuf.data_ptr() if n_shadow else None, hs.multicast_ptr if n_shadow else None, fptrs), 'ts_dp_bind_nvls')
+    engine.params, engine.grads = pbuf, gbuf
+    for i, p in enumerate(params):
+        o, n = engine.offsets[i], p.numel()
+        p.data = pbuf[o:o + n].view(p.shape)
+        p.grad = gbuf[o:o + n].view(p.shape)
+    engine.sync_weights()
+    torch.cuda.synchronize(engine.index)
+    dist.barrier(group=dp.group)
+    return gbuf, pbuf, sbuf, flags, handles
