@@ -960,19 +960,30 @@ __global__ void __launch_bounds__(256) nvls_optimizer_kernel(OptArgs p, DpArgs d
     }
     rank_barrier(own, dp, 8, 2u * dp.step, false);
     const int n_owned = (n_chunks - dp.rank + dp.world - 1) / dp.world;
-    for (int j = blockIdx.x; j < n_owned; j += gridDim.x) {
-        const int chunk = j * dp.world + dp.rank;
-        const int tix = p.chunk_tensor[chunk];
-        if (tix < 0) continue;
-        const TensorDesc d = p.t[tix];
-        const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
-        const int64_t j0 = i0 - d.offset;
-        if (j0 >= d.count) continue;
-        const int n = (int)min((int64_t)4, d.count - j0);
-        float g[4];
-        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                     : "=f"(g[0]), "=f"(g[1]), "=f"(g[2]), "=f"(g[3]) : "l"(grads_mc + i0) : "memory");
-        apply_update(p, d, i0, j0, n, g);
+    // four owned chunks per round: a reduction through the switch takes a few microseconds to come back, so one request per
+    // thread at a time leaves the links mostly idle
+    for (int j = blockIdx.x * 4; j < n_owned; j += gridDim.x * 4) {
+        float g[4][4];
+        int tix[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int chunk = (j + u) * dp.world + dp.rank;
+            tix[u] = (j + u < n_owned) ? p.chunk_tensor[chunk] : -1;
+            if (tix[u] < 0) continue;
+            const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+            if (i0 - p.t[tix[u]].offset >= p.t[tix[u]].count) { tix[u] = -1; continue; }
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(g[u][0]), "=f"(g[u][1]), "=f"(g[u][2]), "=f"(g[u][3]) : "l"(grads_mc + i0) : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (tix[u] < 0) continue;
+            const int chunk = (j + u) * dp.world + dp.rank;
+            const TensorDesc d = p.t[tix[u]];
+            const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+            const int64_t j0 = i0 - d.offset;
+            apply_update(p, d, i0, j0, (int)min((int64_t)4, d.count - j0), g[u]);
+        }
     }
     rank_barrier(own, dp, 9, 2u * dp.step + 1u, true);
 }
@@ -994,10 +1005,17 @@ static int ensure_optimizer_smem() {
 int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, int sm_count, cudaStream_t st) {
     // every CTA must be resident at once (they wait for each other and for the peer GPUs): with up to 64 KiB of shared
     // memory each 3 per SM fit; 2 leaves room for the early-running cast of the next batch
-    int64_t grid = (int64_t)sm_count * 2;
-    if (grid > n_chunks) grid = n_chunks;
     int rc = ensure_optimizer_smem();
     if (rc) return rc;
+    static int cached_dp[17] = {0};       // resident CTAs per SM by partial depth (same binary on every device of the process)
+    int &per_sm_c = cached_dp[a.partial_depth & 15];
+    if (per_sm_c == 0)
+        TS_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_c, dp_optimizer_kernel, 256, (size_t)a.partial_depth * 4096));
+    int per_sm = per_sm_c;
+    TS_REQUIRE(per_sm >= 1, TS_E_CUDA, "data-parallel optimizer kernel does not fit on an SM");
+    if (per_sm > 2) per_sm = 2;
+    int64_t grid = (int64_t)sm_count * per_sm;
+    if (grid > n_chunks) grid = n_chunks;
     TS_CUDA_CHECK(launch_pdl(dp_optimizer_kernel, dim3((unsigned)grid), dim3(256), (size_t)a.partial_depth * 4096, st, 1, a, dp, (int)n_chunks));
     TS_LAUNCH_CHECK();
     return TS_OK;
@@ -1047,8 +1065,16 @@ int launch_nvls_optimizer(const OptArgs &a, const DpArgs &dp, const float *grads
     for (int t = 0; t < a.n_tensors; ++t)
         TS_REQUIRE(a.shadow_mc == nullptr || a.t[t].shadow_off < 0 || a.t[t].count % 4 == 0, TS_E_UNSUPPORTED,
                    "nvls optimizer: weight tensor %d has %lld elements, not a multiple of 4", t, (long long)a.t[t].count);
-    // every CTA spins at the two barriers: the grid must be co-resident (3 CTAs per SM fit at 64 KiB of shared memory each)
-    int64_t grid = (int64_t)sm_count * 2;
+    // every CTA spins at the two barriers: the grid must be co-resident (64 KiB of shared memory per CTA for small models:
+    // 3 per SM; 16 KiB for large ones: the 8 that the thread count allows)
+    static int cached_nvls[17] = {0};
+    int &per_sm_c = cached_nvls[a.partial_depth & 15];
+    if (per_sm_c == 0)
+        TS_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_c, nvls_optimizer_kernel, 256, (size_t)a.partial_depth * 4096));
+    int per_sm = per_sm_c;
+    TS_REQUIRE(per_sm >= 1, TS_E_CUDA, "nvls optimizer kernel does not fit on an SM");
+    if (per_sm > 4) per_sm = 4;           // room for the early-running cast of the next batch
+    int64_t grid = (int64_t)sm_count * per_sm;
     if (grid > n_chunks) grid = n_chunks;
     TS_CUDA_CHECK(launch_pdl(nvls_optimizer_kernel, dim3((unsigned)grid), dim3(256), (size_t)a.partial_depth * 4096, st, 1, a, dp, grads_mc,
                              (int)n_chunks));
