@@ -236,3 +236,42 @@ def test_device_loader_batches_shuffle_and_shards():
     assert all(len(s) == 24 for s in seen) and len(set(torch.cat(seen).tolist())) == 96
     xb, yb = next(iter(DeviceLoader(x, y, 8, device='cpu', dtype=torch.bfloat16)))
     assert xb.dtype == torch.bfloat16 and yb.dtype == torch.int64 and xb.to('cpu') is xb      # .to(device) is a no-op
+
+
+def test_layer_buckets_tile_the_flat_gradient():
+    """All-reduce buckets are whole layers, tile [0, total) without gaps, and merge small layers (config 4's model:
+    784 -> 4096 x 4 -> 10 gives three buckets of 16-20 M elements; the shipped model is one bucket)."""
+    import math
+    from torchsystem_b200.parallel import layer_buckets
+
+    def layout(dims):
+        offs, o = [], 0
+        for l in range(len(dims) - 1):
+            offs.append(o); o += math.ceil(dims[l] * dims[l + 1] / 1024) * 1024
+            offs.append(o); o += math.ceil(dims[l + 1] / 1024) * 1024
+        return offs, o
+
+    offs, total = layout([784, 4096, 4096, 4096, 4096, 10])
+    b = layer_buckets(offs, total)
+    assert [x[:2] for x in b] == [(0, 4), (4, 2), (6, 4)]
+    assert b[0][2] == 0 and all(b[i][2] + b[i][3] == b[i + 1][2] for i in range(len(b) - 1)) and b[-1][2] + b[-1][3] == total
+    assert all(x[3] >= 16 << 20 for x in b)
+    offs, total = layout([784, 256, 10])
+    assert layer_buckets(offs, total) == [(0, 4, 0, total)]
+
+
+def test_optimizer_config_maps_torch_optimizers():
+    """torch.optim.SGD / Adam / AdamW hyper-parameters as the fused optimizer takes them; anything else is refused."""
+    import torch
+    from torchsystem_b200.classifier import _optimizer_config
+    w = [torch.nn.Parameter(torch.zeros(3))]
+    kind, h = _optimizer_config(torch.optim.SGD(w, lr=0.1, momentum=0.9, nesterov=True, weight_decay=1e-4))
+    assert kind == 'sgd' and h == dict(lr=0.1, weight_decay=1e-4, momentum=0.9, dampening=0.0, nesterov=True)
+    kind, h = _optimizer_config(torch.optim.Adam(w, lr=1e-3, amsgrad=True))
+    assert kind == 'adam' and h['amsgrad'] and not h['decoupled_weight_decay'] and h['betas'] == (0.9, 0.999)
+    kind, h = _optimizer_config(torch.optim.AdamW(w, lr=1e-3, weight_decay=0.05))
+    assert kind == 'adam' and h['decoupled_weight_decay'] and h['weight_decay'] == 0.05
+    with pytest.raises(NotImplementedError):
+        _optimizer_config(torch.optim.SGD(w, lr=0.1, maximize=True))
+    with pytest.raises(TypeError):
+        _optimizer_config(torch.optim.RMSprop(w, lr=0.1))

@@ -74,6 +74,8 @@ class B200Classifier(Aggregate):
                  device: str | torch.device = 'cuda', max_batch: int = 4096, dropout_seed: int = 42, process_group=None,
                  dp_mode: str = 'p2p', uint8_norm: tuple[float, float] | None = None):
         super().__init__()
+        if dp_mode not in ('p2p', 'nccl', 'nvls'):
+            raise ValueError(f"dp_mode must be 'p2p', 'nccl' or 'nvls', got {dp_mode!r}")
         _check_criterion(criterion)
         spec = inspect_mlp(nn)
         kind, hyper = _optimizer_config(optimizer)
@@ -111,17 +113,7 @@ class B200Classifier(Aggregate):
             elif dp_mode == 'nccl':
                 # buckets of whole layers, at least 16 M elements each (the last one absorbs what is left)
                 self._comm = torch.cuda.Stream(device=dev)
-                self._buckets, t0, o0 = [], 0, self.engine.offsets[0]
-                n_t = len(self._params)
-                for l in range(len(spec.linears)):
-                    end_t = 2 * l + 2
-                    end_o = self.engine.offsets[end_t] if end_t < n_t else self.engine.total
-                    if end_o - o0 >= (16 << 20) or end_t == n_t:
-                        self._buckets.append((t0, end_t - t0, o0, end_o - o0))
-                        t0, o0 = end_t, end_o
-                if len(self._buckets) > 1 and self._buckets[-1][3] < (4 << 20):       # fold a small tail into its neighbour
-                    a, b = self._buckets[-2], self._buckets.pop()
-                    self._buckets[-1] = (a[0], a[1] + b[1], a[2], a[3] + b[3])
+                self._buckets = parallel.layer_buckets(self.engine.offsets, self.engine.total)
                 self._bucket_events = [torch.cuda.Event() for _ in self._buckets]
                 self._bucketed = os.environ.get('TSB200_DP_BUCKETS', '0') != '0'
             if dp_mode == 'nccl' and os.environ.get('TSB200_DP_OVERLAP', '0') != '0':

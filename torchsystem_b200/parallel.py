@@ -45,6 +45,24 @@ class DataParallel:
         return v[0], int(v[1]), int(v[2]), int(v[3])
 
 
+def layer_buckets(offsets: list[int], total: int, min_elems: int = 16 << 20, small_tail: int = 4 << 20):
+    """All-reduce buckets over the flat gradient buffer: whole layers (weight + bias, torch order W0, b0, W1, ...), merged
+    until a bucket holds at least `min_elems` elements; a last bucket smaller than `small_tail` joins its neighbour.
+    Returns [(first_tensor, n_tensors, first_element, n_elements)]; the buckets tile [0, total) exactly."""
+    n_t = len(offsets)
+    buckets, t0, o0 = [], 0, offsets[0]
+    for l in range(n_t // 2):
+        end_t = 2 * l + 2
+        end_o = offsets[end_t] if end_t < n_t else total
+        if end_o - o0 >= min_elems or end_t == n_t:
+            buckets.append((t0, end_t - t0, o0, end_o - o0))
+            t0, o0 = end_t, end_o
+    if len(buckets) > 1 and buckets[-1][3] < small_tail:
+        a, b = buckets[-2], buckets.pop()
+        buckets[-1] = (a[0], a[1] + b[1], a[2], a[3] + b[3])
+    return buckets
+
+
 def bind_peer_gradients(engine, params, dp: DataParallel):
     """Put the flat gradient buffers (two, alternating with the step parity) and a small flag array into torch
     symmetric memory, exchange the peer mappings and hand them to the library (ts_dp_bind). Returns the objects
