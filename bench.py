@@ -105,18 +105,74 @@ def reference_arm(args):
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region. The region is tens of milliseconds long, shorter than
+    one `nvidia-smi -lms` period, so the samples come from NVML in a thread (every ~2 ms, and always at least one taken
+    while the GPU is busy); nvidia-smi is only the fallback when the NVML binding is missing."""
     Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,'
          'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
 
     def __init__(self, index: int):
-        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        self.sm, self.mx, self.reasons, self.p, self.t = [], [], set(), None, None
         try:
-            self.p = subprocess.Popen(['nvidia-smi', f'--id={index}', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
-                                       '-lms', '100'], stdout=self.f, stderr=subprocess.DEVNULL)
-        except OSError:
-            self.p = None
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            phys = index
+            vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+            if vis:
+                ids = [v.strip() for v in vis.split(',') if v.strip()]
+                if index < len(ids) and ids[index].isdigit():
+                    phys = int(ids[index])
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            import threading
+            self.stop_flag = threading.Event()
+            self.t = threading.Thread(target=self._loop, daemon=True)
+            self.t.start()
+        except Exception:
+            self.nv = None
+            self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+            try:
+                self.p = subprocess.Popen(['nvidia-smi', f'--id={index}', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
+                                           '-lms', '20'], stdout=self.f, stderr=subprocess.DEVNULL)
+            except OSError:
+                self.p = None
+
+    def _sample(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        self.mx.append(self.max_sm)
+        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        for name, bit in (('hw_slowdown', nv.nvmlClocksThrottleReasonHwSlowdown),
+                          ('hw_thermal_slowdown', nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+                          ('sw_thermal_slowdown', nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+                          ('sw_power_cap', nv.nvmlClocksThrottleReasonSwPowerCap)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _loop(self):
+        while not self.stop_flag.is_set():
+            try:
+                self._sample()
+            except Exception:
+                break
+            time.sleep(0.002)
+
+    def sample_now(self):
+        """One sample from the calling thread (called right after the timed launches are enqueued: the GPU is busy)."""
+        if self.nv is not None:
+            try:
+                self._sample()
+            except Exception:
+                pass
 
     def stop(self) -> dict:
+        if self.nv is not None:
+            self.stop_flag.set()
+            self.t.join(timeout=2)
+            sm = sorted(self.sm)
+            return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(self.mx) if self.mx else None,
+                    'reasons': sorted(self.reasons), 'samples': len(sm), 'source': 'nvml'}
         if self.p is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
         self.p.terminate()
@@ -140,7 +196,7 @@ class ClockSampler:
         os.unlink(self.f.name)
         sm.sort()
         return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
-                'reasons': sorted(reasons), 'samples': len(sm)}
+                'reasons': sorted(reasons), 'samples': len(sm), 'source': 'nvidia-smi'}
 
 
 # ----------------------------------------------------------------------------- B200 arm
@@ -214,6 +270,8 @@ def main():
         for _ in range(steps):
             training.service.handle('train', model, loader, metrics); metrics.reset()
         e1.record()
+        if clocks:
+            clocks.sample_now()
         barrier()
         ms = e0.elapsed_time(e1)
         launches = _lib.lib.ts_launch_count() - launches0
