@@ -10,7 +10,8 @@
 //   dA = dZ W2                      third tcgen05.mma (K = 16 padded classes), overwrites TMEM cols 0..H
 //   dH = dA * relu'(A) / (1-p)      epilogue threads, bf16, coalesced store
 //   dW2^T, db1 partials             A^T dZ and dH^T 1 as MN-major tcgen05.mma over the 128 rows (TMEM cols 272..)
-// Inputs: bf16 by TMA (multicast across the cluster), or fp32 converted on chip when a slab is one CTA.
+// Inputs: bf16 by TMA (every CTA of a cluster fetches the slab's X tile itself; the repeats are L2 hits), or fp32
+// converted on chip when a slab is one CTA.
 //
 // classifier.py:22-27 (forward, loss), :31-35 (fit), :37-39 (evaluate); mlp.py:14-17; metrics.py:14-15.
 // Restrictions (else the engine uses the layer-by-layer path): hidden width 64, 128 or 256,
@@ -131,10 +132,9 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     if (threadIdx.x == 0) {
         // a stage is full when the W1 tile has landed and the X tile has landed (bf16 inputs: TMA) or been converted
         // (fp32 inputs: one arrival per converter warp -- 256 per-thread arrivals would serialise on the barrier word)
-        // The X tile (bf16) or its fp32 staging slot is shared by the cluster: every CTA loads 1/ns of the rows and
-        // multicasts them, so a slot is free only when all ns CTAs have released it.
-        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], p.x_f32 ? 1 + kEpiThreads / 32 : 2); mbar_init(&empty_bar[s], p.x_f32 ? 1 : ns); }
-        for (int s = 0; s < p.xstages; ++s) { mbar_init(&xf_full_bar[s], 1); mbar_init(&xf_empty_bar[s], (kEpiThreads / 32) * ns); }
+        // Every CTA of a cluster loads the whole X tile for itself, so all of these barriers are CTA-local.
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], p.x_f32 ? 1 + kEpiThreads / 32 : 2); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < p.xstages; ++s) { mbar_init(&xf_full_bar[s], 1); mbar_init(&xf_empty_bar[s], kEpiThreads / 32); }
         mbar_init(&h_full_bar, 1);
         mbar_init(&w2_full_bar, 1);
         mbar_init(&a_ready_bar, kEpiThreads / 32);      // one arrival per warp: 256 per-thread arrivals serialise on the barrier word
@@ -163,11 +163,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     if (ns > 1 && warp < 3) cluster_arrive();                  // phase 1 (logit exchange): these warps only have to have arrived
     if (warp == 0) {
         // ===================== TMA producer: X tiles (A operand) =====================
-        // In a cluster every CTA needs the same X tile: each loads BM / ns of its rows and multicasts them to all ns CTAs
-        // (a quarter of the TMA requests and of the L2 reads per CTA at ns = 4).
-        const int rows = BM / ns;                                  // rows of the tile this CTA loads
-        const uint32_t slice = (uint32_t)rank * (uint32_t)rows * 128u;
-        const uint16_t mask = (uint16_t)((1u << ns) - 1u);
+        // In a cluster every CTA needs the same X tile and fetches it itself (the source is the caller's pointer).
         int s = 0;
         uint32_t phase = 0;
         for (int kb = 0; kb < p.num_kblocks; ++kb) {
@@ -175,22 +171,15 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 if (!p.x_f32) {
                     mbar_wait(&empty_bar[s], phase ^ 1);
                     mbar_expect_tx(&full_bar[s], a_bytes);
-                    uint8_t *dst = tiles + (size_t)s * stage_bytes + slice;
-                    if (ns == 1) tma_load_2d(&tma_x, &full_bar[s], dst, kb * KATOM, m0);
-                    else tma_load_2d_multicast(&tma_x, &full_bar[s], dst, kb * KATOM, m0 + (int)rank * rows, mask);
+                    tma_load_2d(&tma_x, &full_bar[s], tiles + (size_t)s * stage_bytes, kb * KATOM, m0);
                 } else {
                     // fp32 tile = two boxes of 32 columns (128 B rows) into the staging ring; the epilogue warps convert
                     const int xs = kb % p.xstages;
                     mbar_wait(&xf_empty_bar[xs], ((kb / p.xstages) & 1) ^ 1);
                     mbar_expect_tx(&xf_full_bar[xs], kXBytes);
-                    uint8_t *dst = xstage + (size_t)xs * kXBytes + slice;
-                    if (ns == 1) {
-                        tma_load_2d(&tma_x, &xf_full_bar[xs], dst, kb * KATOM, m0);
-                        tma_load_2d(&tma_x, &xf_full_bar[xs], dst + kXBytes / 2, kb * KATOM + 32, m0);
-                    } else {
-                        tma_load_2d_multicast(&tma_x, &xf_full_bar[xs], dst, kb * KATOM, m0 + (int)rank * rows, mask);
-                        tma_load_2d_multicast(&tma_x, &xf_full_bar[xs], dst + kXBytes / 2, kb * KATOM + 32, m0 + (int)rank * rows, mask);
-                    }
+                    uint8_t *dst = xstage + (size_t)xs * kXBytes;
+                    tma_load_2d(&tma_x, &xf_full_bar[xs], dst, kb * KATOM, m0);
+                    tma_load_2d(&tma_x, &xf_full_bar[xs], dst + kXBytes / 2, kb * KATOM + 32, m0);
                 }
             }
             __syncwarp();
@@ -227,9 +216,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 #pragma unroll
                 for (int k = 0; k < KATOM / UMMA_K; ++k)
                     umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc_main, (kb > 0 || k > 0) ? 1u : 0u);
-                // bf16 inputs in a cluster: the stage's X tile was multicast by all ns CTAs, so all of them are told it is free
-                if (ns == 1 || p.x_f32) umma_commit(&empty_bar[s]);
-                else umma_commit_multicast(&empty_bar[s], (uint16_t)((1u << ns) - 1u));
+                umma_commit(&empty_bar[s]);
                 if (kb == p.num_kblocks - 1) umma_commit(&h_full_bar);
                 if (kb == 0) TRACE(2);
                 if (kb == p.num_kblocks - 1) TRACE(3);
@@ -327,8 +314,7 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                 // not wait for loads that are still in flight, so releasing right behind the loads lets the next TMA
                 // fill overtake them
                 __syncwarp();
-                if (ns == 1) { if (lane == 0) mbar_arrive(&xf_empty_bar[xs]); }
-                else if (lane < ns) mbar_arrive_cluster(map_to_rank(smem_u32(&xf_empty_bar[xs]), (uint32_t)lane));
+                if (lane == 0) mbar_arrive(&xf_empty_bar[xs]);
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&full_bar[s]);
@@ -722,9 +708,9 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     p.partials = a.partials; p.ticket = a.ticket; p.record = a.record;
 
     CUtensorMap mx, mw1, mw2;
-    // X box: BM / ns rows -- every CTA of a cluster loads its share of the tile's rows and multicasts it
-    int rc = p.x_f32 ? get_map(a.X_f32, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, 32, (uint32_t)(BM / p.ns), &mx, 4)
-                     : get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, (uint32_t)(BM / p.ns), &mx);
+    // X box: all BM rows of the slab -- every CTA of a cluster loads the whole tile for itself
+    int rc = p.x_f32 ? get_map(a.X_f32, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, 32, (uint32_t)BM, &mx, 4)
+                     : get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, (uint32_t)BM, &mx);
     if (rc) return rc;
     rc = get_map(a.W1, (uint64_t)a.D, (uint64_t)a.H, (uint64_t)a.D, KATOM, (uint32_t)p.BN, &mw1);
     if (rc) return rc;
