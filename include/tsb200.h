@@ -38,6 +38,7 @@ extern "C" {
 #define TS_E_STATE (-3)     /* call order: parameters / optimizer / workspace not bound */
 #define TS_E_UNSUPPORTED (-4)
 #define TS_E_TOO_LARGE (-5) /* size beyond a stated maximum */
+#define TS_E_TIMEOUT (-6)   /* data parallel: a peer rank did not arrive within the configured time */
 
 /* activation of the hidden layers (examples/tinysys/main.py:60 uses ReLU; tests/test_storage.py:38 GELU) */
 #define TS_ACT_RELU 0
@@ -178,9 +179,17 @@ int32_t ts_dp_reserve_sms(ts_mlp *m, int32_t n_sms);
  *   grad_bufs  HOST array of 2*world device pointers, buffer b of rank r at [b*world + r]; each as long as the flat
  *              parameter buffer (ts_mlp_param_layout), mapped on THIS device (e.g. torch symmetric memory, CUDA IPC)
  *   flag_bufs  HOST array of world device pointers to each rank's flag array: TS_DP_FLAG_WORDS uint32, zero-initialised
- *              (word q < world: last step rank q has published; word 8: arrival ticket; words 16..20: time trace)
- * Every rank must call ts_fit_step the same number of times; a rank that never arrives makes the others trap. */
+ *              (word q < world: last step rank q has published; words 8 and 9: arrival tickets; words 16..23: time trace)
+ * Every rank must call ts_fit_step the same number of times. The kernel's CTAs wait for each other and for the peers, so
+ * its whole grid (at most 2 CTAs per SM, 4 for ts_dp_bind_nvls) must be resident at once: do not run other work that
+ * fills the GPU's SMs concurrently with a data-parallel ts_fit_step. A wait for a peer is bounded by wall-clock time
+ * (ts_dp_set_timeout, default 600 s or TSB200_DP_TIMEOUT_S): when it expires the kernel skips its update and sets a
+ * host-visible error word instead of trapping; the next ts_fit_step (or ts_dp_status) then returns TS_E_TIMEOUT. */
 int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bufs /*HOST*/, uint32_t *const *flag_bufs /*HOST*/);
+/* Bound, in seconds, on how long a data-parallel kernel waits for a peer rank (no counterpart in the reference). */
+int32_t ts_dp_set_timeout(ts_mlp *m, double seconds);
+/* TS_OK, or TS_E_TIMEOUT once a data-parallel kernel has given up waiting for a peer (no counterpart in the reference). */
+int32_t ts_dp_status(const ts_mlp *m);
 
 /* The same for large models, with the reduction done inside the NVSwitch (no counterpart in the reference): gradient,
  * parameter and (bf16 mode) shadow buffers live in symmetric memory that also has a MULTICAST mapping (`*_mc`, e.g. torch

@@ -42,15 +42,18 @@ def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1
     assert model._overlap == (dp_mode == 'nccl' and os.environ.get('TSB200_DP_OVERLAP', '0') != '0')
     metrics = B200Metrics(device=f'cuda:{rank}', log_every=0)
     half = B // world
+    trail = {}
     for s in range(3):
         lo = s * B + rank * half
         xb, yb = x[lo:lo + half].cuda(), y[lo:lo + half].cuda()
+        for i, q in enumerate(q for lin in net.linears() for q in (lin.weight, lin.bias)):
+            trail[f'pre_{s}_{i}'] = q.detach().cpu().numpy().copy()        # this replica's weights BEFORE step s
         p, l = model.fit(xb, yb)
+        trail[f'pred_{s}'] = p.cpu().numpy()
         metrics.update(s + 1, l, p, yb)
     counters = metrics.counters()
-    if rank == 0:
-        np.savez(out, *[q.detach().cpu().numpy() for lin in net.linears() for q in (lin.weight, lin.bias)],
-                 counters=np.array(counters, dtype=np.float64))
+    np.savez(out.replace('rank0', f'rank{rank}'), *[q.detach().cpu().numpy() for lin in net.linears() for q in (lin.weight, lin.bias)],
+             counters=np.array(counters, dtype=np.float64), **trail)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -71,17 +74,28 @@ def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, to
         x = x.bfloat16().float()
     init = seeded_init(dims, seed=0, bf16=precision == 'bf16')
     oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=precision == 'bf16')
-    correct, total = 0, 0
+    from tests.parity_util import assert_predictions_explained
+    got = [np.load(out.replace('rank0', f'rank{r}')) for r in range(2)]
+    correct, total, half = 0, 0, B // 2
     for s in range(3):
         xb, yb = x[s * B:(s + 1) * B].numpy(), y[s * B:(s + 1) * B].numpy()
-        p, _ = oracle.evaluate(xb, yb)
-        correct += int((p == yb).sum()); total += B
+        pre = [got[0][f'pre_{s}_{i}'] for i in range(4)]
+        for i in range(4):      # replicas are bit-identical before every step (same reduction order on every rank)
+            assert np.array_equal(pre[i], got[1][f'pre_{s}_{i}']), f'step {s}: replicas differ in tensor {i}'
+        pred = np.concatenate([got[r][f'pred_{s}'] for r in range(2)])       # rank r fitted rows [r * half, (r+1) * half)
+        if precision == 'f32':
+            p, _ = oracle.evaluate(xb, yb)
+            assert np.array_equal(pred, p)
+        else:       # exact under the replicas' own weights; differences from the oracle trajectory explained row by row
+            assert_predictions_explained(pred, oracle, pre, xb, None, f'{dp_mode} step {s}')
+        correct += int((pred == yb).sum()); total += B
         oracle.fit(xb, yb, None)
-    got = np.load(out)
-    assert_params_close([got[f'arr_{i}'] for i in range(4)], oracle.parameters(), tol, adam=False)
-    loss_sum, n_batches, n_correct, n_total = got['counters']
+    for i in range(4):
+        assert np.array_equal(got[0][f'arr_{i}'], got[1][f'arr_{i}']), 'final replicas differ'
+    assert_params_close([got[0][f'arr_{i}'] for i in range(4)], oracle.parameters(), tol, adam=False)
+    loss_sum, n_batches, n_correct, n_total = got[0]['counters']
     assert (n_batches, n_total) == (6, total)
-    assert abs(n_correct - correct) <= (0 if precision == 'f32' else 3)
+    assert n_correct == correct         # the all-reduced fused counters are exactly the count of both ranks' predictions
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')

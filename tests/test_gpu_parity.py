@@ -300,7 +300,11 @@ def test_uint8_inputs_reproduce_the_host_transform(precision, tol):
         assert torch.equal(a, b)          # same bits: the table holds exactly the host transform's 256 results
     oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=precision == 'bf16')
     opr, ol = oracle.fit(xf[:B].numpy(), y[:B].numpy(), None)
-    assert (out[1][0].numpy() != opr).mean() <= (0.0 if precision == 'f32' else 2e-3)
+    # both sides hold the same (initial) weights here: exact, fp32 summation-order ties excepted and reported
+    from tests.parity_util import assert_predictions_explained
+    fresh = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=precision == 'bf16')
+    excepted = assert_predictions_explained(out[1][0].numpy(), fresh, init, xf[:B].numpy(), None, f'uint8 {precision}')
+    assert precision == 'bf16' or len(excepted) == 0
     assert out[1][1].item() == pytest.approx(float(ol), rel=tol)
     with pytest.raises(RuntimeError):
         out_model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,

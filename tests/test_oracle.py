@@ -84,10 +84,15 @@ def test_mask_predraw_matches_dropout():
 def test_bf16_emulation_stays_within_tolerance():
     """bf16 operand rounding (the tensor-core mode) must keep loss within 1e-2 of the fp32 reference run."""
     case = load_case('tinysys_adam_b32')
+    from tests.parity_util import LockstepF32
     engine = make_oracle(case, emulate_bf16=True)
-    losses, preds, _ = replay(case, engine, onp.OracleMetrics())
+    walker = LockstepF32(engine, engine.parameters, make_oracle(case))
+    losses, preds, _ = replay(case, walker, onp.OracleMetrics())
     np.testing.assert_allclose(losses, case.raw['batch_loss'], rtol=1e-2)
-    assert (preds == case.raw['batch_pred']).mean() > 0.97
+    # exact or explained, never a rate: a row may leave the fp32 reference's prediction only where its fp32 top-2 margin
+    # is below the bf16 rounding noise of its logits (tests/parity_util.py)
+    assert (preds != case.raw['batch_pred']).sum() == len(walker.flips)
+    print(f'{len(walker.flips)} of {len(preds)} rows flipped; (margin, bound): {walker.flips[:5]}')
 
 
 def test_bf16_round_ties_to_even():

@@ -66,6 +66,14 @@ def test_static_evaluate_matches_workspace_evaluate_twice_in_a_row():
             assert np.array_equal(ps, pw), 'predictions differ between the static and the workspace entry point'
             assert ls == pytest.approx(lw, rel=1e-5)
             assert (cs, ns) == (cw, nw) == (int((pw == y.cpu().numpy()).sum()), B)
+            # and against the CPU oracle, so this file stands on its own: same weights, fp32 arithmetic
+            from oracle import mlp_numpy as onp
+            host = params.cpu().numpy()
+            tensors = [host[o:o + int(np.prod(sh))].reshape(sh) for o, sh in zip(offs, shapes)]
+            oracle = onp.OracleMLP(weights=tensors[0::2], biases=tensors[1::2])
+            opred, oloss = oracle.evaluate(x.cpu().numpy(), y.cpu().numpy())
+            assert np.array_equal(ps, opred), 'static entry point: predictions differ from the oracle'
+            assert ls == pytest.approx(float(oloss), rel=1e-5)
 
         # beyond the stated maximum: refused with a clear message, nothing launched
         B = 20000                                                 # 20000 * 256 * 4 = 20.5 MB > 16 MiB

@@ -100,9 +100,14 @@ class B200Classifier(Aggregate):
             self.engine.set_input_normalization(float(uint8_norm[0]), float(uint8_norm[1]))
         step = self._adopt_optimizer_state(kind, hyper)
         self.engine.bind_optimizer(kind, step=step, **hyper)
+        self._hyper_key = self._param_group_key()
+        # optimizer.state_dict() must show the live step count (the moments alias the engine's buffers already)
+        optimizer.register_state_dict_pre_hook(self._before_state_dict)
+        self._state_gathered_at = -1
         self._dp = parallel.DataParallel(process_group)
         self._p2p = None
         self._overlap = False
+        self._nvls = dp_mode == 'nvls' and self._dp.world > 1
         if self._dp.world > 1:
             self._dp.broadcast_(self.engine.params)          # same initial weights on every rank
             self.engine.sync_weights()
@@ -134,6 +139,10 @@ class B200Classifier(Aggregate):
     def onphase(self) -> None:
         # weights may have been replaced between phases (repository.restore -> load_state_dict)
         self.engine.sync_weights()
+        # data parallel: line the ranks up on the host at every phase boundary. Rank 0 may come out of an I/O consumer
+        # (storage.py:84-86 saves on every Iterated) seconds after the others; they then wait here, in the process group's
+        # barrier, not inside a spinning optimizer kernel.
+        self._dp.barrier()
 
     def sync(self) -> None:
         """Call after editing `nn`'s weights by hand; re-derives the bf16 operand copies."""
@@ -172,16 +181,43 @@ class B200Classifier(Aggregate):
         return step
 
     def sync_optimizer_state(self) -> None:
-        """Refresh the `step` entries torch's optimizer.state_dict() reports (the moments alias live buffers)."""
+        """Refresh the `step` entries torch's optimizer.state_dict() reports (the moments alias live buffers). Runs
+        automatically before every optimizer.state_dict()."""
         step = self.engine.step_count
         for p in self._params:
             st = self.optimizer.state.get(p)
             if st is not None and 'step' in st:
                 st['step'] = torch.tensor(float(step))
 
+    def gather_optimizer_state(self) -> None:
+        """dp_mode='nvls' only, COLLECTIVE (every rank must call it): each rank updates the optimizer moments of its own
+        1/world of the 1024-element chunks, so before a checkpoint the owned chunks are summed into every rank's buffers."""
+        eng = self.engine
+        if self._dp.world > 1 and self._nvls:
+            own = (torch.arange(eng.total // 1024, device=eng.device) % self._dp.world == self._dp.rank)
+            own = own.repeat_interleave(1024).to(torch.float32)
+            for buf in (eng.exp_avg, eng.exp_avg_sq, eng.max_exp_avg_sq):
+                if buf is not None:
+                    buf.mul_(own)
+                    self._dp.all_reduce_sum_(buf)
+        self._state_gathered_at = eng.step_count
+
+    def _before_state_dict(self, optimizer) -> None:
+        if self._dp.world > 1 and self._nvls and self.engine.opt_kind is not None and self.engine.exp_avg is not None \
+                and self._state_gathered_at != self.engine.step_count:
+            raise RuntimeError("dp_mode='nvls' shards the optimizer moments over the ranks: call model.gather_optimizer_state() "
+                               'on EVERY rank (a collective) after the last step, then optimizer.state_dict()')
+        self.sync_optimizer_state()
+
+    def _param_group_key(self) -> tuple:
+        g = self.optimizer.param_groups[0]
+        return (g['lr'], g.get('weight_decay'), g.get('momentum'), g.get('dampening'), g.get('nesterov'), g.get('betas'),
+                g.get('eps'), g.get('amsgrad'), g.get('maximize'), g.get('decoupled_weight_decay'))
+
     def _refresh_hyper(self) -> None:
-        kind, hyper = _optimizer_config(self.optimizer)      # follows lr schedulers / manual edits
+        kind, hyper = _optimizer_config(self.optimizer)      # follows lr schedulers / manual edits of the param group
         self.engine.bind_optimizer(kind, step=self.engine.step_count, **hyper)
+        self._hyper_key = self._param_group_key()
 
     # ------------------------------------------------------------------ the hot path
     def forward(self, input: Tensor) -> Tensor:
@@ -190,8 +226,7 @@ class B200Classifier(Aggregate):
     def fit(self, inputs: Tensor, targets: Tensor, *, masks=None) -> tuple[Tensor, Tensor]:
         """One optimisation step on a batch; returns (argmax of the pre-update logits, mean CE loss).
         `masks`: optional list of [B, hidden] 0/1 keep-masks, one per hidden layer (parity runs)."""
-        g = self.optimizer.param_groups[0]
-        if g['lr'] != self.engine._hyper[1]:
+        if self._param_group_key() != self._hyper_key:       # lr schedulers, manual edits of any hyper-parameter
             self._refresh_hyper()
         if self._dp.world == 1:
             return self.engine.fit(inputs, targets, masks, self.dropout_seed)

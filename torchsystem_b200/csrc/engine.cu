@@ -1,10 +1,13 @@
 // C ABI of the tsb200 engine (include/tsb200.h): handle management, workspace carving and the
 // per-batch kernel sequences behind Classifier.fit / Classifier.evaluate / Metrics.
 #include <cmath>
+#include <climits>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -110,6 +113,8 @@ struct ts_mlp {
     float *dp_grads[2][kMaxRanks] = {{nullptr}};
     uint32_t *dp_flags[kMaxRanks] = {nullptr};
     // NVLS variant (ts_dp_bind_nvls): multicast mappings of the symmetric gradient / parameter / shadow buffers
+    uint32_t *dp_err_host = nullptr, *dp_err_dev = nullptr;   // mapped pinned word the DP kernels set when a peer never arrives
+    double dp_timeout_s = 600.0;                               // TSB200_DP_TIMEOUT_S / ts_dp_set_timeout
     bool nvls = false;
     const float *grads_mc = nullptr;
     float *params_mc = nullptr;
@@ -425,6 +430,8 @@ int run_dp_optimizer(ts_mlp *m, const int *nsplit, cudaStream_t st) {
     fill_update(m, o);
     DpArgs dp{};
     dp.world = m->dp_world; dp.rank = m->dp_rank; dp.step = (uint32_t)m->step;
+    dp.timeout_ns = (unsigned long long)(m->dp_timeout_s * 1e9);
+    dp.err = m->dp_err_dev;
     for (int r = 0; r < m->dp_world; ++r) { dp.grads[r] = m->dp_grads[parity][r]; dp.flags[r] = m->dp_flags[r]; }
     ProfScope ps(K_OPT, st);
     if (m->nvls) {
@@ -506,6 +513,23 @@ int mark_layer_ready(ts_mlp *m, int l, const int *nsplit, cudaStream_t st) {
     return TS_OK;
 }
 
+// The word the data-parallel kernels write when a wait for a peer times out: pinned host memory mapped into the device.
+int ensure_dp_error_word(ts_mlp *m) {
+    if (m->dp_err_host != nullptr) return TS_OK;
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    void *h = nullptr, *d = nullptr;
+    TS_CUDA_CHECK(cudaHostAlloc(&h, 64, cudaHostAllocMapped));
+    memset(h, 0, 64);
+    TS_CUDA_CHECK(cudaHostGetDevicePointer(&d, h, 0));
+    m->dp_err_host = (uint32_t *)h;
+    m->dp_err_dev = (uint32_t *)d;
+    if (const char *e = getenv("TSB200_DP_TIMEOUT_S")) {
+        const double v = atof(e);
+        if (v > 0.0) m->dp_timeout_s = v;
+    }
+    return TS_OK;
+}
+
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
              uint64_t seed, int64_t *pred, ts_batch_record *rec, cudaStream_t st, bool update) {
     int rc = check_ready(m, B, update);
@@ -515,6 +539,10 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     const int L = m->n_layers;
     const bool bf16 = m->prec == TS_PREC_BF16;
     const bool dp = m->dp_world > 1 && update;
+    TS_REQUIRE(!dp || m->dp_err_host == nullptr || *(volatile uint32_t *)m->dp_err_host == 0u, TS_E_TIMEOUT,
+               "data parallel: a peer rank did not arrive within %.0f s at step %u; that step's update was skipped and the "
+               "replicas are no longer in step (ts_dp_set_timeout / TSB200_DP_TIMEOUT_S set the bound)",
+               m->dp_timeout_s, *(volatile uint32_t *)m->dp_err_host);
     if (dp && !m->nvls) m->grads = m->dp_grads[m->step & 1][m->dp_rank];     // this step's peer-visible gradient buffer
     const void *a0 = nullptr, *a_last = nullptr;
     int nsplit[2 * kMaxLayers] = {0};
@@ -724,6 +752,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
 }
 
 int32_t ts_mlp_destroy(ts_mlp *m) {
+    if (m && m->dp_err_host) cudaFreeHost(m->dp_err_host);
     delete m;
     return TS_OK;
 }
@@ -780,6 +809,20 @@ int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bu
     }
     m->dp_world = world;
     m->dp_rank = rank;
+    return ensure_dp_error_word(m);
+}
+
+int32_t ts_dp_set_timeout(ts_mlp *m, double seconds) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    TS_REQUIRE(seconds > 0.0 && seconds < 1e7, TS_E_INVALID, "timeout %g s", seconds);
+    m->dp_timeout_s = seconds;
+    return TS_OK;
+}
+
+int32_t ts_dp_status(const ts_mlp *m) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    TS_REQUIRE(m->dp_err_host == nullptr || *(volatile uint32_t *)m->dp_err_host == 0u, TS_E_TIMEOUT,
+               "data parallel: a peer rank did not arrive within %.0f s at step %u", m->dp_timeout_s, *(volatile uint32_t *)m->dp_err_host);
     return TS_OK;
 }
 
@@ -803,7 +846,7 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
     m->shadow_ext = (__nv_bfloat16 *)shadow_local; m->shadow_mc = (__nv_bfloat16 *)shadow_mc;
     if (m->shadow_ext) m->shadow = m->shadow_ext;
     m->dp_world = world; m->dp_rank = rank; m->nvls = true;
-    return TS_OK;
+    return ensure_dp_error_word(m);
 }
 
 int64_t ts_mlp_workspace_bytes(const ts_mlp *m, int64_t max_batch) {
@@ -1015,7 +1058,8 @@ const char *ts_profile_kind_name(int32_t kind) { return (kind >= 0 && kind < K_C
 namespace {
 constexpr int64_t kStaticScratchBytes = 16ll << 20;   // 16 MiB, resident on every GPU that loads the library
 constexpr int kStaticMaxDevices = 64;
-void *g_static_scratch_addr[kStaticMaxDevices] = {nullptr};   // device address of the array, per device
+std::atomic<void *> g_static_scratch_addr[kStaticMaxDevices];   // device address of the array, per device (null until resolved)
+std::mutex g_static_scratch_mu;
 }  // namespace
 
 // In host code this name is only a handle for cudaGetSymbolAddress; kernels get the resolved device address.
@@ -1035,22 +1079,29 @@ extern "C" int32_t ts_eval_step_static(ts_mlp *m, const void *inputs, int32_t in
     const int L = m->n_layers;
 
     // how much of the array this call needs: ticket | head partials | per hidden layer: activation (+ GELU pre-activation)
+    // (the batch is bounded first, so the products below cannot overflow)
     int64_t need = 256 + round_up((int64_t)sizeof(HeadPartial) * kMaxHeadBlocks, 256);
-    for (int l = 0; l < L - 1; ++l)
+    const bool batch_sane = batch <= kStaticScratchBytes / 4;
+    for (int l = 0; l < L - 1 && batch_sane; ++l)
         need += round_up(batch * m->dims[l + 1] * 4, 256) * (m->act == TS_ACT_GELU ? 2 : 1);
+    if (!batch_sane) need = INT64_MAX;
     TS_REQUIRE(need <= kStaticScratchBytes, TS_E_TOO_LARGE,
                "ts_eval_step_static: batch %lld needs %lld bytes of scratch, the built-in array holds %lld (batch * sum of hidden "
                "widths * 4 must stay below about 16 MiB); use ts_eval_step with a caller workspace for larger batches",
                (long long)batch, (long long)need, (long long)kStaticScratchBytes);
 
     TS_CUDA_CHECK(cudaSetDevice(m->device));
-    if (g_static_scratch_addr[m->device] == nullptr) {   // set-up, once per device, with that device current
-        void *addr = nullptr;
-        TS_CUDA_CHECK(cudaGetSymbolAddress(&addr, g_static_scratch));
-        TS_REQUIRE(addr != nullptr, TS_E_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
-        g_static_scratch_addr[m->device] = addr;
+    void *scratch = g_static_scratch_addr[m->device].load(std::memory_order_acquire);
+    if (scratch == nullptr) {   // set-up, once per device, with that device current (host threads may race here: one lock)
+        std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+        scratch = g_static_scratch_addr[m->device].load(std::memory_order_relaxed);
+        if (scratch == nullptr) {
+            TS_CUDA_CHECK(cudaGetSymbolAddress(&scratch, g_static_scratch));
+            TS_REQUIRE(scratch != nullptr, TS_E_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+            g_static_scratch_addr[m->device].store(scratch, std::memory_order_release);
+        }
     }
-    Carver c(g_static_scratch_addr[m->device]);
+    Carver c(scratch);
     unsigned int *ticket = (unsigned int *)c.take(256);
     HeadPartial *partials = (HeadPartial *)c.take(sizeof(HeadPartial) * kMaxHeadBlocks);
     // the array keeps whatever the previous call left: the completion ticket is the one thing that must start at zero
@@ -1069,6 +1120,7 @@ extern "C" int32_t ts_eval_step_static(ts_mlp *m, const void *inputs, int32_t in
         g.bias = m->params + m->off[2 * l + 1];
         g.U_out = u_out; g.act = m->act; g.training = 0;
         g.drop = drop_spec(m, nullptr, 0, l, false);
+        ProfScope ps(K_FWD_GEMM, st);
         int rc = launch_sgemm(EPI_FWD, g, 1, st);
         if (rc) return rc;
         a_in = a_out;
@@ -1078,5 +1130,6 @@ extern "C" int32_t ts_eval_step_static(ts_mlp *m, const void *inputs, int32_t in
     h.a_is_bf16 = 0; h.round_w_bf16 = 0;
     h.partials = partials; h.ticket = ticket;
     h.drop = drop_spec(m, nullptr, 0, L - 2, false);
+    ProfScope ps(K_HEAD, st);
     return launch_head(h, m->sm_count, st);
 }

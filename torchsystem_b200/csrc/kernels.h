@@ -130,6 +130,8 @@ struct DpArgs {
     uint32_t *flags[kMaxRanks];      // rank r's flag array: entry q = last step whose gradient rank q has published; [8] arrival ticket
     int world, rank;
     uint32_t step;
+    unsigned long long timeout_ns;   // how long a wait for a peer may last before the kernel gives up (no trap)
+    uint32_t *err;                   // host-visible (mapped pinned) word: set to the step number on a timeout
 };
 int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, int sm_count, cudaStream_t st);
 // NVLS variant (large models): every rank reduces 1/world of the chunks inside the NVSwitch (multimem.ld_reduce over the

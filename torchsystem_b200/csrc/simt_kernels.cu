@@ -822,6 +822,29 @@ __device__ __forceinline__ uint32_t global_ns32() {
     return (uint32_t)t;
 }
 
+// Wait until *flag has reached `value` (release/acquire at system scope: the flag is written by a peer GPU). The wait is
+// bounded by wall-clock time (dp.timeout_ns on %globaltimer, minutes by default like a collective library's watchdog, not
+// by a poll count: a peer may legitimately be seconds late, e.g. while rank 0 writes a checkpoint). On expiry the step
+// number goes into the host-visible error word and the caller skips its update; nothing traps, the context stays usable.
+__device__ __forceinline__ bool wait_for_flag(const uint32_t *flag, uint32_t value, const DpArgs &dp) {
+    unsigned long long t0 = 0;
+    for (uint32_t spins = 0;; ++spins) {
+        uint32_t seen;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
+        if ((int32_t)(seen - value) >= 0) return true;
+        __nanosleep(32);
+        if ((spins & 1023u) == 1023u) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > dp.timeout_ns) {
+                if (dp.err != nullptr) *reinterpret_cast<volatile uint32_t *>(dp.err) = dp.step ? dp.step : 1u;
+                return false;
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp, int n_chunks) {
     extern __shared__ float4 slots[];
     pdl_launch_dependents();
@@ -852,7 +875,8 @@ __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp,
     // 2. one handshake per step: the last CTA of this rank to finish part 1 publishes "my gradient of step s is
     //    complete" into every rank's flag array (release, system scope). Per-CTA system-scope releases, or a full system
     //    fence in every CTA, cost several microseconds each while the next batch's cast streams through the same SMs.
-    __shared__ bool s_last;
+    __shared__ bool s_last, s_timed_out;
+    if (threadIdx.x == 0) s_timed_out = false;
     __syncthreads();
     if (tracer) trace[5] = global_ns32();
     if (threadIdx.x == 0) {
@@ -867,17 +891,9 @@ __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp,
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dp.flags[threadIdx.x] + dp.rank), "r"(dp.step) : "memory");
         if (threadIdx.x == 0) trace[7] = global_ns32();
     }
-    if (threadIdx.x < dp.world) {
-        const uint32_t *mine = own + threadIdx.x;
-        uint32_t spins = 0, seen;
-        for (;;) {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
-            if ((int32_t)(seen - dp.step) >= 0) break;
-            __nanosleep(32);
-            if (++spins > (1u << 25)) __trap();                    // a peer never arrived: fail loudly instead of hanging
-        }
-    }
+    if (threadIdx.x < dp.world && !wait_for_flag(own + threadIdx.x, dp.step, dp)) s_timed_out = true;
     __syncthreads();
+    if (s_timed_out) return;                // a peer never arrived: nothing is updated, the host reports TS_E_TIMEOUT
     if (tracer) trace[2] = global_ns32();
 
     // 3. all ranks' gradient chunk in rank order (identical order on every rank), scaled update
@@ -916,8 +932,9 @@ __global__ void __launch_bounds__(256) dp_optimizer_kernel(OptArgs p, DpArgs dp,
 // Per GPU and step this moves ~1x the gradient out and ~1.4x in over NVLink and does 1/world of the optimizer work,
 // against all-reduce (2x each way) followed by the full optimizer.
 // =====================================================================================
-__device__ __forceinline__ void rank_barrier(uint32_t *own, const DpArgs &dp, int ticket_slot, uint32_t value, bool sys_fence) {
-    __shared__ bool s_last_b;
+__device__ __forceinline__ bool rank_barrier(uint32_t *own, const DpArgs &dp, int ticket_slot, uint32_t value, bool sys_fence) {
+    __shared__ bool s_last_b, s_timed_out_b;
+    if (threadIdx.x == 0) s_timed_out_b = false;
     __syncthreads();
     if (threadIdx.x == 0) {
         if (sys_fence) __threadfence_system(); else __threadfence();
@@ -928,17 +945,9 @@ __device__ __forceinline__ void rank_barrier(uint32_t *own, const DpArgs &dp, in
     __syncthreads();
     if (s_last_b && threadIdx.x < dp.world)
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dp.flags[threadIdx.x] + dp.rank), "r"(value) : "memory");
-    if (threadIdx.x < dp.world) {
-        const uint32_t *mine = own + threadIdx.x;
-        uint32_t spins = 0, seen;
-        for (;;) {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
-            if ((int32_t)(seen - value) >= 0) break;
-            __nanosleep(64);
-            if (++spins > (1u << 24)) __trap();                    // a peer never arrived: fail loudly instead of hanging
-        }
-    }
+    if (threadIdx.x < dp.world && !wait_for_flag(own + threadIdx.x, value, dp)) s_timed_out_b = true;
     __syncthreads();
+    return !s_timed_out_b;                  // false: a peer never arrived (error word written); the caller returns
 }
 
 __global__ void __launch_bounds__(256) nvls_optimizer_kernel(OptArgs p, DpArgs dp, const float *grads_mc, int n_chunks) {
@@ -958,7 +967,7 @@ __global__ void __launch_bounds__(256) nvls_optimizer_kernel(OptArgs p, DpArgs d
         sum_partials(p.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, p.partial_depth);
         *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], n > 1 ? g[1] : 0.0f, n > 2 ? g[2] : 0.0f, n > 3 ? g[3] : 0.0f);
     }
-    rank_barrier(own, dp, 8, 2u * dp.step, false);
+    if (!rank_barrier(own, dp, 8, 2u * dp.step, false)) return;
     const int n_owned = (n_chunks - dp.rank + dp.world - 1) / dp.world;
     // four owned chunks per round: a reduction through the switch takes a few microseconds to come back, so one request per
     // thread at a time leaves the links mostly idle
@@ -985,7 +994,7 @@ __global__ void __launch_bounds__(256) nvls_optimizer_kernel(OptArgs p, DpArgs d
             apply_update(p, d, i0, j0, (int)min((int64_t)4, d.count - j0), g[u]);
         }
     }
-    rank_barrier(own, dp, 9, 2u * dp.step + 1u, true);
+    (void)rank_barrier(own, dp, 9, 2u * dp.step + 1u, true);
 }
 
 // 64 KiB of dynamic shared memory needs the opt-in attribute, once per device.

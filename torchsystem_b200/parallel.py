@@ -31,6 +31,10 @@ class DataParallel:
         if self.world > 1:
             dist.broadcast(flat, src=src, group=self.group)
 
+    def barrier(self) -> None:
+        if self.world > 1:
+            dist.barrier(group=self.group)
+
     def all_reduce_sum_(self, flat: Tensor) -> None:
         if self.world > 1:
             dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
