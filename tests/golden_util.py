@@ -95,7 +95,7 @@ def golden_phase_results(case: GoldenCase):
     return [(float(l), float(a)) for n, l, a in zip(names, losses, accs) if str(n) != 'Iterated']
 
 
-def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weights'):
+def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weights', tie_units=()):
     """Updated-weight tolerance of the north star (1e-5 relative in fp32 mode, 1e-2 in bf16 mode),
     applied per element as |got - want| <= tol * (|want| + rms(want)).
 
@@ -104,12 +104,20 @@ def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weight
     depends on summation order, in the reference as much as here. For Adam at most 1e-3 of the
     elements of a tensor (or 2 elements of a small one) may therefore leave the band, and none by more than lr * steps (the hard
     bound on any Adam trajectory difference)."""
+    tie_units = sorted(tie_units)
     for i, (g, w) in enumerate(zip(got, want)):
         g = np.asarray(g, dtype=np.float64); w = np.asarray(w, dtype=np.float64)
         assert g.shape == w.shape, f'{what}[{i}]: shape {g.shape} vs {w.shape}'
         rms = np.sqrt(np.mean(w * w)) if w.size else 0.0
         dev = np.abs(g - w)
         bad = dev > tol * (np.abs(w) + rms) + 1e-9
+        if tie_units and i < 3:
+            # first hidden units with a ReLU gate tie (tests/parity_util.relu_gate_ties): their W1 row / b1 element / W2
+            # column may carry one row's contribution more or less; held to 1e-3 instead (a real error moves far more)
+            sel = (tie_units,) if i < 2 else (slice(None), tie_units)
+            loose = dev[sel] > 1e-3 * (np.abs(w[sel]) + rms) + 1e-9
+            assert not loose.any(), f'{what}[{i}]: gate-tie units {tie_units} off beyond 1e-3'
+            bad[sel] = False
         if not adam:
             assert not bad.any(), f'{what}[{i}]: {bad.sum()} elements off, max |d|={dev.max():.3e}'
         else:

@@ -126,3 +126,15 @@ class LockstepF32:
         p, l = self.engine.evaluate(x, y)
         self._check(p, z, bound)
         return p, l
+
+
+def relu_gate_ties(oracle: onp.OracleMLP, x, masks, rel: float = 2e-6) -> set:
+    """Hidden units of the FIRST hidden layer whose pre-activation sits at fp32 round-off distance from zero for some
+    row of this batch (|u| < rel * max|u|): a different summation order can put such a value on the other side of ReLU's
+    gate, which switches that row's whole contribution to the unit's weight row on or off. Same nature as an argmax tie;
+    returned so the weight comparison can name the units it treats loosely (tests report them)."""
+    _, _, pre = oracle._forward(x, masks)
+    u = pre[0]
+    live = np.ones_like(u, dtype=bool) if masks is None or oracle.dropout == 0.0 else masks[0].astype(bool)
+    near = (np.abs(u) < rel * np.abs(u).max()) & live
+    return set(np.nonzero(near.any(axis=0))[0].tolist())

@@ -9,7 +9,7 @@ import torch
 from oracle import mlp_numpy as onp
 from tests.golden_util import load_case, replay, assert_params_close
 from tests.test_gpu_parity import build_model, seeded_init, synthetic, net_params, EngineAdapter, OPT
-from tests.parity_util import assert_predictions_explained, LockstepF32
+from tests.parity_util import assert_predictions_explained, LockstepF32, relu_gate_ties
 
 pytestmark = pytest.mark.gpu
 
@@ -231,9 +231,11 @@ def test_number_of_classes(C, precision, tol):
     init = seeded_init(dims, bf16=bf16)
     model, net = build_model(dims, p, 'relu', 'sgd', 0.05, init, precision, max_batch=B)
     oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=onp.OPT_SGD, lr=0.05, emulate_bf16=bf16)
+    ties = set()
     for s in range(steps):
         xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
         mask = (torch.rand(B, 256, generator=g) >= p).to(torch.uint8)
+        ties |= relu_gate_ties(oracle, xb.numpy(), [mask.numpy()])
         if bf16:
             fit_checked(model, net, oracle, xb, yb, [mask], f'C={C} step {s}')
         else:
@@ -248,7 +250,9 @@ def test_number_of_classes(C, precision, tol):
         pr, l = model.evaluate(xb.cuda(), yb.cuda())
         opr, ol = oracle.evaluate(xb.numpy(), yb.numpy())
         assert np.array_equal(pr.cpu().numpy(), opr) and l.item() == pytest.approx(float(ol), rel=tol)
-    assert_params_close(net_params(net), oracle.parameters(), tol, lr=0.05, steps=steps, adam=False)
+    if ties:
+        print(f'[parity] C={C} {precision}: ReLU gate ties at hidden units {sorted(ties)}')
+    assert_params_close(net_params(net), oracle.parameters(), tol, lr=0.05, steps=steps, adam=False, tie_units=ties)
 
 
 def test_bf16_config4_model_at_a_batch_the_oracle_finishes():
