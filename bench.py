@@ -46,6 +46,7 @@ def parse():
     ap.add_argument('--precision', default=os.environ.get('TSB_BENCH_PRECISION', 'bf16'), choices=['bf16', 'f32'])
     ap.add_argument('--optimizer', default='sgd', choices=['sgd', 'adam'])
     ap.add_argument('--batches', type=int, default=BATCHES_PER_STEP, help='batches of 4096 per step')
+    ap.add_argument('--dp-mode', default='auto', choices=['auto', 'p2p', 'nvls', 'nccl'], help='gradient exchange at N > 1')
     ap.add_argument('--e2e-steps', type=int, default=5)
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the cpu_baseline leg')
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -373,10 +374,42 @@ def main():
     teacher = torch.randn(784, 10, generator=torch.Generator(device=dev).manual_seed(99), device=dev)
     y = torch.argmax(x.flatten(1) @ teacher, dim=1)
 
-    torch.manual_seed(0)
-    net = MLP(DIMS[0], DIMS[1], DIMS[2], dropout=DROPOUT, activation=nn.ReLU())
-    opt = torch.optim.SGD(net.parameters(), lr=LR) if args.optimizer == 'sgd' else torch.optim.Adam(net.parameters(), lr=1e-3)
-    model = B200Classifier(net, nn.CrossEntropyLoss(), opt, precision=args.precision, device=dev, max_batch=BATCH)
+    def make_model(dp_mode):
+        torch.manual_seed(0)
+        net = MLP(DIMS[0], DIMS[1], DIMS[2], dropout=DROPOUT, activation=nn.ReLU())
+        opt = torch.optim.SGD(net.parameters(), lr=LR) if args.optimizer == 'sgd' else torch.optim.Adam(net.parameters(), lr=1e-3)
+        return B200Classifier(net, nn.CrossEntropyLoss(), opt, precision=args.precision, device=dev, max_batch=BATCH, dp_mode=dp_mode)
+
+    # N > 1: which gradient exchange the S model uses is decided by a short trial of both one-kernel modes on this box
+    # ('p2p': every rank reads all gradients over peer mappings; 'nvls': reduce-scatter / all-gather through the NVSwitch)
+    dp_trial = None
+    dp_mode = args.dp_mode
+    if world > 1 and dp_mode == 'auto':
+        dp_trial = {}
+        for mode in ('p2p', 'nvls'):
+            try:
+                cand = make_model(mode)
+                def run(k):
+                    for i in range(k):
+                        cand.fit(x[(i % args.batches) * BATCH:(i % args.batches + 1) * BATCH], y[(i % args.batches) * BATCH:(i % args.batches + 1) * BATCH])
+                run(32)
+                dist.barrier(); torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); run(128); e1.record()
+                torch.cuda.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1) / 128 * 1e3], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dp_trial[mode] = t.item()
+                del cand
+            except Exception as e:
+                dp_trial[mode] = None
+                dp_trial[mode + '_error'] = repr(e)[:200]
+        ok = {k: v for k, v in dp_trial.items() if isinstance(v, float)}
+        # every rank saw the same all-reduced numbers, so every rank picks the same mode
+        dp_mode = min(ok, key=ok.get) if ok else 'p2p'
+    elif dp_mode == 'auto':
+        dp_mode = 'p2p'
+    model = make_model(dp_mode)
     metrics = B200Metrics(device=dev, log_every=0)
     training.provider.override(training.device, lambda: dev)
     results = []
@@ -576,6 +609,56 @@ def main():
             'note': 'MLP 784-4096x4-10, Adam, batch 8192 per step, fp32 inputs resident; dense-layer FLOPs only'}
         del modelL, netL
 
+    # ---- BASELINE.json configs[3] at its real global batch, every N (SURVEY.md section 8d "Config 4", section 8e)
+    parity = None
+    if not args.skip_extras:
+        extras['config4_dp'] = config4_dp(torch, dist, dev, world, rank, x, y, args.precision, peaks or {})
+        if world > 1:
+            try:
+                parity = dp_parity(torch, dist, dev, world, rank, args.precision, dp_mode)
+            except Exception as e:
+                parity = {'error': repr(e)[:300]}
+    if not args.skip_extras and world == 1:
+        # the GPU incumbent for the L model: stock PyTorch eager (cuBLASLt GEMMs), same model / batch / optimizer
+        def eager_L(autocast):
+            BL = 8192
+            torch.manual_seed(0)
+            net_e = MLP(L_DIMS[0], L_DIMS[1:-1], L_DIMS[-1], dropout=DROPOUT, activation=nn.ReLU()).to(dev)
+            opt_e = torch.optim.Adam(net_e.parameters(), lr=1e-3)
+            crit = nn.CrossEntropyLoss()
+            def step(i):
+                xb, yb = x[(i % 4) * BL:(i % 4 + 1) * BL].flatten(1), y[(i % 4) * BL:(i % 4 + 1) * BL]
+                opt_e.zero_grad()
+                with torch.autocast('cuda', dtype=torch.bfloat16, enabled=autocast):
+                    out = net_e(xb)
+                    loss = crit(out, yb)
+                loss.backward()
+                opt_e.step()
+                return out.argmax(1), loss
+            for i in range(3):
+                step(i)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(8):
+                step(i)
+            e1.record()
+            torch.cuda.synchronize()
+            ms_e = e0.elapsed_time(e1) / 8
+            del net_e, opt_e
+            return {'ms_per_step': ms_e, 'value': BL / (ms_e * 1e-3), 'tflops': BL * L_FLOP_PER_SAMPLE / (ms_e * 1e-3) / 1e12}
+        try:
+            inc = {'fp32': eager_L(False), 'autocast_bf16': eager_L(True), 'unit': 'samples/s',
+                   'note': 'stock PyTorch eager fit loop of MLP 784-4096x4-10 (Adam, batch 8192) on this GPU: the L-model incumbent'}
+            mine = extras.get('config4_L_model_one_gpu', {}).get('value')
+            if mine:
+                inc['this_repo_over_autocast_bf16'] = mine / inc['autocast_bf16']['value']
+                inc['this_repo_over_fp32'] = mine / inc['fp32']['value']
+            extras['torch_eager_L_model_same_gpu'] = inc
+        except Exception as e:
+            extras['torch_eager_L_model_same_gpu'] = {'error': repr(e)[:300]}
+        torch.cuda.empty_cache()
+
     # ---- e2e: host buffers, H2D every step, result read back
     if args.skip_e2e:
         e2e = None
@@ -599,8 +682,13 @@ def main():
                                               'note': 'PinnedLoader over uint8 images, B200Classifier(uint8_norm=(0.1307, 0.3081)): the '
                                                       "dataset's ToTensor + Normalize applied on the device, 792 B/sample over PCIe"}
           del pin8, xu8
-      e2e = {'value': world * n * args.e2e_steps / (e_ms * 1e-3), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d_per_step,
+      ceiling = h2d_ceiling(torch, dist if world > 1 else None, dev, world)
+      e2e_rate = world * n * args.e2e_steps / (e_ms * 1e-3)
+      e2e = {'value': e2e_rate, 'unit': 'samples/s', 'h2d_bytes_per_step': h2d_per_step,
            'd2h_bytes_per_step': 32, 'steps': args.e2e_steps, 'ms_per_step': e_ms / args.e2e_steps,
+           'h2d_gbs_per_gpu': h2d_per_step / (e_ms / args.e2e_steps * 1e-3) / 1e9,
+           'h2d_ceiling_gbs_per_gpu': ceiling, 'frac_of_h2d_ceiling': h2d_per_step / (e_ms / args.e2e_steps * 1e-3) / 1e9 / ceiling,
+           'ceiling_note': f'pinned host -> device copies of 256 MiB, all {world} rank(s) at once, slowest rank',
            'path': 'training.service.handle("train") over PinnedLoader (pinned host -> device on a copy stream, 3 batches ahead)'}
 
     # ---- cpu_baseline (rank 0, N=1 only)
@@ -609,6 +697,15 @@ def main():
         r = cpu_reference_run(1000, 1, 16, args.cpu_seconds, args.optimizer)
         cpu = {'value': r['value'], 'unit': 'samples/s', 'cores': r['cores'], 'kind': 'port', 'sample': r['sample']}
 
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not args.skip_extras:
+        # the reference's CPU path at the batch sizes of configs[0] (256) and configs[2] (32, as shipped)
+        for name, b, nb in (('cpu_reference_batch256_adam', 256, 64), ('cpu_reference_batch32_adam', 32, 256)):
+            try:
+                r = cpu_reference_run(1000, 1, nb, 4.0, 'adam', batch=b)
+                extras[name] = {'value': r['value'], 'unit': 'samples/s', 'cores': r['cores'], 'us_per_batch': b / r['value'] * 1e6,
+                                'sample': r['sample']}
+            except Exception as e:
+                extras[name] = {'error': repr(e)[:300]}
     if rank == 0:
         line = {
             'metric': 'train_samples_per_sec', 'value': value, 'unit': 'samples/s', 'n_gpus': world, 'steps': args.steps,
@@ -617,10 +714,10 @@ def main():
             'config': {'workload': f'tinysys train handler: MLP(784,256,10) dropout 0.1 ReLU, CrossEntropyLoss, {args.optimizer}, '
                                    f'batch {BATCH}, {args.batches} batches per step per GPU (BASELINE.json configs[1])',
                        'batch': BATCH, 'samples_per_step_per_gpu': n, 'optimizer': args.optimizer, 'precision': args.precision,
-                       'parallelism': f'dp{world}', 'l2': f'inputs of one step ({n * 3136 / 1e9:.2f} GB per GPU) exceed the 126 MB L2',
+                       'parallelism': f'dp{world}', 'dp_mode': dp_mode if world > 1 else None, 'dp_mode_trial_us_per_batch': dp_trial, 'l2': f'inputs of one step ({n * 3136 / 1e9:.2f} GB per GPU) exceed the 126 MB L2',
                        'last_train_result': results[-1] if results else None},
             'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline, 'cpu_baseline': cpu,
-            'extras': extras,
+            'parity': parity, 'extras': extras,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -95,7 +95,17 @@ def golden_phase_results(case: GoldenCase):
     return [(float(l), float(a)) for n, l, a in zip(names, losses, accs) if str(n) != 'Iterated']
 
 
-def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weights', tie_units=()):
+def band_fraction(got, want, tol):
+    """Per tensor: fraction of elements with |got - want| > tol * (|want| + rms(want))."""
+    out = []
+    for g, w in zip(got, want):
+        g = np.asarray(g, dtype=np.float64); w = np.asarray(w, dtype=np.float64)
+        rms = np.sqrt(np.mean(w * w)) if w.size else 0.0
+        out.append(float(np.mean(np.abs(g - w) > tol * (np.abs(w) + rms) + 1e-9)))
+    return out
+
+
+def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weights', tie_units=(), noise_floor=None):
     """Updated-weight tolerance of the north star (1e-5 relative in fp32 mode, 1e-2 in bf16 mode),
     applied per element as |got - want| <= tol * (|want| + rms(want)).
 
@@ -103,7 +113,14 @@ def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weight
     itself at round-off level (|g| near eps = 1e-8) moves by up to `lr` per step in a direction that
     depends on summation order, in the reference as much as here. For Adam at most 1e-3 of the
     elements of a tensor (or 2 elements of a small one) may therefore leave the band, and none by more than lr * steps (the hard
-    bound on any Adam trajectory difference)."""
+    bound on any Adam trajectory difference).
+
+    `noise_floor` (Adam, deep bf16 nets): per-tensor fractions by which the bf16-EMULATING oracle itself leaves the band
+    around the fp32 oracle (band_fraction). Rounding decisions in a chain of wide bf16 layers decorrelate after a few layers
+    (a flipped rounding perturbs the next layer's sums, which flips more), so two correct bf16 evaluations of the same
+    gradient differ by bf16 noise, and Adam turns every gradient element below that noise into a +-lr step. The engine may
+    then leave the band for at most 1.5x the fraction the emulating oracle does against fp32 -- it must be as close to the
+    emulation as the emulation is to the reference -- still never by more than lr * steps."""
     tie_units = sorted(tie_units)
     for i, (g, w) in enumerate(zip(got, want)):
         g = np.asarray(g, dtype=np.float64); w = np.asarray(w, dtype=np.float64)
@@ -121,5 +138,6 @@ def assert_params_close(got, want, tol, lr=0.0, steps=0, adam=True, what='weight
         if not adam:
             assert not bad.any(), f'{what}[{i}]: {bad.sum()} elements off, max |d|={dev.max():.3e}'
         else:
-            assert bad.sum() <= max(2, 1e-3 * bad.size), f'{what}[{i}]: {bad.sum()}/{bad.size} elements off (tol {tol})'
+            allowed = max(2, 1e-3 * bad.size, (1.5 * noise_floor[i] * bad.size) if noise_floor is not None else 0)
+            assert bad.sum() <= allowed, f'{what}[{i}]: {bad.sum()}/{bad.size} elements off (tol {tol}, allowed {allowed:.0f})'
             assert dev.max() <= lr * steps + 1e-9, f'{what}[{i}]: max |d|={dev.max():.3e} beyond lr*steps'

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import mlp_numpy as onp
-from tests.golden_util import load_case, replay, assert_params_close
+from tests.golden_util import load_case, replay, assert_params_close, band_fraction
 from tests.test_gpu_parity import build_model, seeded_init, synthetic, net_params, EngineAdapter, OPT
 from tests.parity_util import assert_predictions_explained, LockstepF32, relu_gate_ties
 
@@ -264,11 +264,18 @@ def test_bf16_config4_model_at_a_batch_the_oracle_finishes():
     init = seeded_init(dims, bf16=True)
     model, net = build_model(dims, p, 'relu', 'adam', 1e-3, init, 'bf16', max_batch=B)
     oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=onp.OPT_ADAM, lr=1e-3, emulate_bf16=True)
+    f32 = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=onp.OPT_ADAM, lr=1e-3)
     g = torch.Generator().manual_seed(9)
     for s in range(2):
         masks = [(torch.rand(B, h, generator=g) >= p).to(torch.uint8) for h in dims[1:-1]]
-        fit_checked(model, net, oracle, x[s * B:(s + 1) * B], y[s * B:(s + 1) * B], masks, f'L model step {s}')
-    assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=1e-3, steps=2)
+        xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
+        f32.fit(xb.numpy(), yb.numpy(), [k.numpy() for k in masks])
+        fit_checked(model, net, oracle, xb, yb, masks, f'L model step {s}')
+    # four 4096-wide bf16 layers: the emulation and the engine are two draws of the same bf16 noise (golden_util docstring)
+    floor = band_fraction(oracle.parameters(), f32.parameters(), 1e-2)
+    print(f'[parity] L model: emulating oracle vs fp32 oracle leaves the 1e-2 band for {[round(f, 4) for f in floor]} of each tensor; '
+          f'engine vs emulating oracle: {[round(f, 4) for f in band_fraction(net_params(net), oracle.parameters(), 1e-2)]}')
+    assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=1e-3, steps=2, noise_floor=floor)
 
 
 @pytest.mark.parametrize('precision', ['bf16', 'f32'])
@@ -288,8 +295,8 @@ def test_inkernel_hash_dropout_keep_rate(precision, p):
         model.fit(x.cuda(), y.cuda())
         gw2 = net.linears()[1].weight.grad.detach().cpu().numpy().astype(np.float64)
         rnd = onp.bf16_round if precision == 'bf16' else (lambda t: np.asarray(t, dtype=np.float32))
-        dz0 = float(rnd(np.float32((np.float32(1.0) / np.float32(C) - np.float32(1.0)) / np.float32(B))))
-        a_kept = float(rnd(np.float32(1.0) / np.float32(1.0 - p)))
+        dz0 = float(np.asarray(rnd(np.float32((np.float32(1.0) / np.float32(C) - np.float32(1.0)) / np.float32(B)))).reshape(-1)[0])
+        a_kept = float(np.asarray(rnd(np.float32(1.0) / np.float32(1.0 - p))).reshape(-1)[0])
         kept = gw2[0] / (dz0 * a_kept)                                  # rows that kept unit k
         assert np.abs(kept - np.round(kept)).max() < 0.05, 'dW2 row 0 is not an integer multiple of dZ * a'
         counts.append(np.round(kept))

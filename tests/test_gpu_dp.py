@@ -19,7 +19,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1024):
+def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1024, optimizer='sgd'):
     import torch.distributed as dist
     from torch import nn
     os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
@@ -36,7 +36,8 @@ def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1
     with torch.no_grad():
         for p, w in zip([q for lin in net.linears() for q in (lin.weight, lin.bias)], init):
             p.copy_(torch.from_numpy(w))
-    model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
+    opt = torch.optim.SGD(net.parameters(), lr=0.05) if optimizer == 'sgd' else torch.optim.Adam(net.parameters(), lr=1e-3)
+    model = B200Classifier(net, nn.CrossEntropyLoss(), opt, precision=precision,
                            device=f'cuda:{rank}', max_batch=B, dp_mode=dp_mode)
     assert (model._p2p is not None) == (dp_mode in ('p2p', 'nvls'))
     assert model._overlap == (dp_mode == 'nccl' and os.environ.get('TSB200_DP_OVERLAP', '0') != '0')
@@ -52,6 +53,15 @@ def _worker(rank, world, port, precision, dp_mode, out, dims=(784, 256, 10), B=1
         trail[f'pred_{s}'] = p.cpu().numpy()
         metrics.update(s + 1, l, p, yb)
     counters = metrics.counters()
+    if optimizer == 'adam':
+        assert model.engine.step_count == 3
+        if dp_mode == 'nvls':       # the moments are sharded over the ranks: state_dict refuses until they are gathered
+            with pytest.raises(RuntimeError):
+                model.optimizer.state_dict()
+            model.gather_optimizer_state()
+        sd = model.optimizer.state_dict()
+        assert all(int(st['step']) == 3 for st in sd['state'].values())
+        trail['exp_avg_0'] = sd['state'][0]['exp_avg'].cpu().numpy()
     np.savez(out.replace('rank0', f'rank{rank}'), *[q.detach().cpu().numpy() for lin in net.linears() for q in (lin.weight, lin.bias)],
              counters=np.array(counters, dtype=np.float64), **trail)
     dist.barrier()
@@ -99,20 +109,23 @@ def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, to
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
-@pytest.mark.parametrize('overlap', ['buckets', 'backward', 'nvls'])
+@pytest.mark.parametrize('overlap', ['buckets', 'backward', 'nvls', 'nvls_one_kernel'])
 def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
     """'nccl' mode on a net with 2048- and 4096-wide layers: several all-reduce buckets with the optimizer applied bucket by
     bucket (TSB200_DP_BUCKETS=1), or (TSB200_DP_OVERLAP=1) each layer's gradient all-reduced on the side stream while the
     backward pass is still running, biases in a packed all-reduce at the end. Must match the full-batch oracle."""
     monkeypatch.setenv('TSB200_DP_OVERLAP', '1' if overlap == 'backward' else '0')
     monkeypatch.setenv('TSB200_DP_BUCKETS', '1' if overlap == 'buckets' else '0')
+    # 'nvls': each layer's in-switch reduce + update on a side stream under the rest of the backward pass (the default for
+    # nets on the layer-by-layer path); 'nvls_one_kernel': the whole buffer in one kernel after the backward pass
+    monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', '0' if overlap == 'nvls_one_kernel' else '16')
     import torch.multiprocessing as mp
     from oracle import mlp_numpy as onp
     from tests.test_gpu_parity import synthetic, seeded_init
     from tests.golden_util import assert_params_close
     dims, B = (784, 4096, 4096, 2048, 10), 1024
     out = str(tmp_path / 'rank0.npz')
-    mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nvls' if overlap == 'nvls' else 'nccl', out, dims, B), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nvls' if overlap.startswith('nvls') else 'nccl', out, dims, B), nprocs=2, join=True)
     x, y = synthetic(B * 3)
     x = x.bfloat16().float()
     init = seeded_init(list(dims), seed=0, bf16=True)
@@ -121,3 +134,24 @@ def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
         oracle.fit(x[s * B:(s + 1) * B].numpy(), y[s * B:(s + 1) * B].numpy(), None)
     got = np.load(out)
     assert_params_close([got[f'arr_{i}'] for i in range(8)], oracle.parameters(), 1e-2, adam=False)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
+def test_two_gpu_nvls_overlap_is_bit_identical_to_one_kernel_adam(tmp_path, monkeypatch):
+    """The per-layer overlapped exchange does the same arithmetic as the single whole-buffer kernel (same in-switch sums, same
+    chunk ownership, Adam bias correction advanced once per step): after three Adam steps on a 4-layer net the replicas and
+    the gathered first moments must agree bit for bit between the two schedules."""
+    import torch.multiprocessing as mp
+    dims, B = (784, 2048, 2048, 1024, 10), 1024
+    outs = []
+    for sms in ('16', '0'):
+        monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', sms)
+        out = str(tmp_path / f'sms{sms}_rank0.npz')
+        mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nvls', out, dims, B, 'adam'), nprocs=2, join=True)
+        outs.append([np.load(out.replace('rank0', f'rank{r}')) for r in range(2)])
+    for r in range(2):
+        for i in range(8):
+            assert np.array_equal(outs[0][r][f'arr_{i}'], outs[1][r][f'arr_{i}']), f'rank {r} tensor {i}: overlap != one kernel'
+            assert np.array_equal(outs[0][0][f'arr_{i}'], outs[0][1][f'arr_{i}']), f'tensor {i}: replicas differ'
+        assert np.array_equal(outs[0][r]['exp_avg_0'], outs[1][r]['exp_avg_0'])
+    assert np.array_equal(outs[0][0]['exp_avg_0'], outs[0][1]['exp_avg_0']), 'gathered moments differ between ranks'

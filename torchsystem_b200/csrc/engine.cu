@@ -113,6 +113,11 @@ struct ts_mlp {
     float *dp_grads[2][kMaxRanks] = {{nullptr}};
     uint32_t *dp_flags[kMaxRanks] = {nullptr};
     // NVLS variant (ts_dp_bind_nvls): multicast mappings of the symmetric gradient / parameter / shadow buffers
+    // nvls overlap: each layer's reduce + update runs on a side stream, on a few SMs, under the backward pass of the layers below
+    cudaStream_t dp_stream = nullptr;
+    cudaEvent_t dp_ev_layer[kMaxLayers] = {nullptr}, dp_ev_done = nullptr;
+    int nvls_overlap_ctas = 0;            // 0: one whole-buffer kernel after the backward pass
+    uint32_t dp_seq = 0;                  // launch counter of the nvls kernels: the rank barriers count in it
     uint32_t *dp_err_host = nullptr, *dp_err_dev = nullptr;   // mapped pinned word the DP kernels set when a peer never arrives
     double dp_timeout_s = 600.0;                               // TSB200_DP_TIMEOUT_S / ts_dp_set_timeout
     bool nvls = false;
@@ -281,7 +286,7 @@ void fill_head(const ts_mlp *m, HeadArgs &h, const void *a_last, const int64_t *
 
 // Tensor table of the optimizer kernels. Tensors with many row-block partials (batches beyond 16,384 rows) are summed in
 // groups of kReduceFan by one extra launch first; the optimizer then sums the groups.
-int fill_tensor_table(ts_mlp *m, const int *nsplit, OptArgs &o, bool *any_partial, cudaStream_t st) {
+int fill_tensor_table(ts_mlp *m, const int *nsplit, OptArgs &o, bool *any_partial, cudaStream_t st, int t_begin = 0, int t_end = 1 << 30) {
     o.n_tensors = m->n_tensors;
     *any_partial = false;
     for (int t = 0; t < m->n_tensors; ++t) {
@@ -289,7 +294,7 @@ int fill_tensor_table(ts_mlp *m, const int *nsplit, OptArgs &o, bool *any_partia
         o.t[t].partial_off = m->partial_off[t]; o.t[t].partial_stride = m->partial_stride[t];
         const int l = t / 2;
         o.t[t].shadow_off = (m->prec == TS_PREC_BF16 && t % 2 == 0) ? m->shadow_off[l] : -1;
-        o.t[t].nsplit = nsplit ? nsplit[t] : 0;
+        o.t[t].nsplit = (nsplit && t >= t_begin && t < t_end) ? nsplit[t] : 0;    // tensors outside the range: not this launch's business
         *any_partial |= o.t[t].nsplit > 0;
     }
     ReduceArgs r{};
@@ -435,6 +440,7 @@ int run_dp_optimizer(ts_mlp *m, const int *nsplit, cudaStream_t st) {
     for (int r = 0; r < m->dp_world; ++r) { dp.grads[r] = m->dp_grads[parity][r]; dp.flags[r] = m->dp_flags[r]; }
     ProfScope ps(K_OPT, st);
     if (m->nvls) {
+        dp.step = ++m->dp_seq;
         o.params_mc = m->params_mc;
         o.shadow_mc = m->prec == TS_PREC_BF16 ? m->shadow_mc : nullptr;
         return launch_nvls_optimizer(o, dp, m->grads_mc, m->n_chunks, m->sm_count, st);
@@ -530,6 +536,30 @@ int ensure_dp_error_word(ts_mlp *m) {
     return TS_OK;
 }
 
+// nvls overlap: reduce + update of layer l's tensors (weight and bias) on the side stream, ordered behind everything
+// enqueued on `st` so far. Called once the layer's gradients are enqueued AND nothing enqueued later reads its weights.
+int exchange_layer(ts_mlp *m, int l, const int *nsplit, bool first_of_step, cudaStream_t st) {
+    OptArgs o{};
+    bool any_partial = false;
+    int rc = fill_tensor_table(m, nsplit, o, &any_partial, st, 2 * l, 2 * l + 2);
+    if (rc) return rc;
+    o.update = 1; o.grad_scale = 1.0f / (float)m->dp_world;
+    fill_update(m, o, first_of_step);
+    o.params_mc = m->params_mc;
+    o.shadow_mc = m->prec == TS_PREC_BF16 ? m->shadow_mc : nullptr;
+    o.partial_depth = 4;
+    o.chunk_begin = (int)(m->off[2 * l] / kChunk);
+    const int64_t chunk_end = (m->off[2 * l + 1] + round_up(m->cnt[2 * l + 1], kChunk)) / kChunk;
+    DpArgs dp{};
+    dp.world = m->dp_world; dp.rank = m->dp_rank; dp.step = ++m->dp_seq;
+    dp.timeout_ns = (unsigned long long)(m->dp_timeout_s * 1e9);
+    dp.err = m->dp_err_dev;
+    for (int r = 0; r < m->dp_world; ++r) dp.flags[r] = m->dp_flags[r];
+    TS_CUDA_CHECK(cudaEventRecord(m->dp_ev_layer[l], st));
+    TS_CUDA_CHECK(cudaStreamWaitEvent(m->dp_stream, m->dp_ev_layer[l], 0));
+    return launch_nvls_layer(o, dp, m->grads_mc, chunk_end - o.chunk_begin, m->nvls_overlap_ctas, m->dp_stream);
+}
+
 int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B, const uint8_t *const *masks,
              uint64_t seed, int64_t *pred, ts_batch_record *rec, cudaStream_t st, bool update) {
     int rc = check_ready(m, B, update);
@@ -602,6 +632,12 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     }
     rc = mark_layer_ready(m, L - 1, nsplit, st);
     if (rc) return rc;
+    // nvls overlap (wide nets, tensor-core last layer): W_last was last read by tc_head_backward, already enqueued
+    const bool ov = dp && m->nvls && m->nvls_overlap_ctas > 0 && tc_head;
+    if (ov) {
+        rc = exchange_layer(m, L - 1, nsplit, true, st);
+        if (rc) return rc;
+    }
     int cur = 0;
     for (int l = L - 2; l >= 0; --l) {
         const int in = m->dims[l], out = m->dims[l + 1];
@@ -673,6 +709,15 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
             if (rc) return rc;
             cur ^= 1;
         }
+        if (ov) {   // layer l: dW_l and db_l are enqueued, and so is the dX GEMM above, the last reader of W_l in this step
+            rc = exchange_layer(m, l, nsplit, false, st);
+            if (rc) return rc;
+        }
+    }
+    if (ov) {       // the next forward pass reads every parameter: the compute stream waits for the last exchange
+        TS_CUDA_CHECK(cudaEventRecord(m->dp_ev_done, m->dp_stream));
+        TS_CUDA_CHECK(cudaStreamWaitEvent(st, m->dp_ev_done, 0));
+        return TS_OK;
     }
     if (!dp) return run_optimizer(m, nsplit, update, 1.0f, st);
     return run_dp_optimizer(m, nsplit, st);
@@ -753,6 +798,12 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
 
 int32_t ts_mlp_destroy(ts_mlp *m) {
     if (m && m->dp_err_host) cudaFreeHost(m->dp_err_host);
+    if (m && m->dp_stream) {
+        cudaStreamSynchronize(m->dp_stream);
+        for (int l = 0; l < m->n_layers; ++l) cudaEventDestroy(m->dp_ev_layer[l]);
+        cudaEventDestroy(m->dp_ev_done);
+        cudaStreamDestroy(m->dp_stream);
+    }
     delete m;
     return TS_OK;
 }
@@ -846,6 +897,22 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
     m->shadow_ext = (__nv_bfloat16 *)shadow_local; m->shadow_mc = (__nv_bfloat16 *)shadow_mc;
     if (m->shadow_ext) m->shadow = m->shadow_ext;
     m->dp_world = world; m->dp_rank = rank; m->nvls = true;
+    // Wide nets (layer-by-layer tensor-core path): exchange each layer on a side stream while the backward pass of the
+    // layers below is still running, on TSB200_NVLS_OVERLAP_SMS SMs (default 16, 0 = off) that the backward GEMMs leave free.
+    int ov_sms = 16;
+    if (const char *e = getenv("TSB200_NVLS_OVERLAP_SMS")) ov_sms = atoi(e);
+    if (world > 1 && ov_sms > 0 && ov_sms < m->sm_count / 2 && m->tc_head && !m->fused && m->n_layers > 2) {
+        TS_CUDA_CHECK(cudaSetDevice(m->device));
+        if (m->dp_stream == nullptr) {
+            int lo = 0, hi = 0;
+            TS_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            TS_CUDA_CHECK(cudaStreamCreateWithPriority(&m->dp_stream, cudaStreamNonBlocking, hi));   // its few CTAs go first
+            for (int l = 0; l < m->n_layers; ++l) TS_CUDA_CHECK(cudaEventCreateWithFlags(&m->dp_ev_layer[l], cudaEventDisableTiming));
+            TS_CUDA_CHECK(cudaEventCreateWithFlags(&m->dp_ev_done, cudaEventDisableTiming));
+        }
+        m->nvls_overlap_ctas = ov_sms;
+        m->bwd_sms = m->sm_count - ov_sms;
+    }
     return ensure_dp_error_word(m);
 }
 

@@ -138,6 +138,9 @@ int launch_dp_optimizer(const OptArgs &a, const DpArgs &dp, int64_t n_chunks, in
 // multicast mapping `grads_mc`), updates them and broadcasts parameters + bf16 shadows with multimem.st (a.params_mc / a.shadow_mc)
 int launch_nvls_optimizer(const OptArgs &a, const DpArgs &dp, const float *grads_mc, int64_t n_chunks, int sm_count, cudaStream_t st);
 
+// one layer's chunk range [a.chunk_begin, a.chunk_begin + n_chunks) of the same exchange, on `n_ctas` CTAs (side stream, overlap)
+int launch_nvls_layer(const OptArgs &a, const DpArgs &dp, const float *grads_mc, int64_t n_chunks, int n_ctas, cudaStream_t st);
+
 int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end = false);
 // uint8 -> lut[byte], written as bf16 (dst_bf16) or fp32 (dst_f32); exactly one destination is non-null
 int launch_cast_u8(const uint8_t *src, __nv_bfloat16 *dst_bf16, float *dst_f32, int64_t n, const float *lut, cudaStream_t st,

@@ -759,18 +759,19 @@ __device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc 
 // 4096) are the critical path of the whole launch.
 constexpr int kPartialDepth = 16;                          // small models; large ones run 4 deep to keep 8 CTAs per SM
 constexpr int kPartialSmem = kPartialDepth * 256 * 16;     // most dynamic shared memory of the optimizer kernels
-__device__ __forceinline__ void sum_partials(const float *q, int64_t stride, int nsplit, float (&g)[4], float4 *slots, int depth) {
+__device__ __forceinline__ void sum_partials(const float *q, int64_t stride, int nsplit, float (&g)[4], float4 *slots, int depth,
+                                             uint32_t nthreads = 256u) {
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(slots + threadIdx.x);
     for (int s = 0; s < nsplit; s += depth) {
 #pragma unroll
         for (int u = 0; u < kPartialDepth; ++u)
             if (u < depth && s + u < nsplit)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(base + (uint32_t)u * 256u * 16u), "l"(q + (int64_t)(s + u) * stride) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(base + (uint32_t)u * nthreads * 16u), "l"(q + (int64_t)(s + u) * stride) : "memory");
         asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 #pragma unroll
         for (int u = 0; u < kPartialDepth; ++u)
             if (u < depth && s + u < nsplit) {
-                const float4 v = slots[u * 256 + threadIdx.x];
+                const float4 v = slots[u * nthreads + threadIdx.x];
                 g[0] += v.x; g[1] += v.y; g[2] += v.z; g[3] += v.w;
             }
     }
@@ -995,6 +996,83 @@ __global__ void __launch_bounds__(256) nvls_optimizer_kernel(OptArgs p, DpArgs d
         }
     }
     (void)rank_barrier(own, dp, 9, 2u * dp.step + 1u, true);
+}
+
+// =====================================================================================
+// The same exchange for ONE LAYER's chunk range [chunk_begin, chunk_begin + n_chunks), meant to run on a side stream
+// next to the backward GEMMs of the earlier layers (engine.cu, nvls overlap). The GEMMs are persistent CTAs that own a
+// whole SM each, so this kernel must stay on the few SMs they leave free: its grid is one 1024-thread CTA per reserved
+// SM (the link, not the SM count, bounds a multimem reduction), each CTA working as four 256-thread groups that take
+// one 1024-element chunk each and keep two reductions in flight per thread.
+// =====================================================================================
+constexpr int kLayerThreads = 1024, kLayerGroups = kLayerThreads / 256, kLayerUnroll = 2;
+__global__ void __launch_bounds__(kLayerThreads, 1) nvls_layer_kernel(OptArgs p, DpArgs dp, const float *grads_mc, int n_chunks) {
+    extern __shared__ float4 slots[];
+    uint32_t *own = dp.flags[dp.rank];
+    const int tid = threadIdx.x & 255, grp = threadIdx.x >> 8;
+    const int vblock = blockIdx.x * kLayerGroups + grp, vgrid = gridDim.x * kLayerGroups;
+    // 1. this rank's split partials of the range (hidden-layer bias gradients in bf16 mode) into its gradient buffer
+    for (int c = vblock; c < n_chunks; c += vgrid) {
+        const int chunk = p.chunk_begin + c;
+        const int tix = p.chunk_tensor[chunk];
+        if (tix < 0) continue;
+        const TensorDesc d = p.t[tix];
+        const int64_t i0 = (int64_t)chunk * kChunk + tid * 4;
+        const int64_t j0 = i0 - d.offset;
+        if (j0 >= d.count || d.nsplit <= 0) continue;
+        const int n = (int)min((int64_t)4, d.count - j0);
+        float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        sum_partials(p.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, p.partial_depth, kLayerThreads);
+        *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], n > 1 ? g[1] : 0.0f, n > 2 ? g[2] : 0.0f, n > 3 ? g[3] : 0.0f);
+    }
+    if (!rank_barrier(own, dp, 8, 2u * dp.step, false)) return;
+    // 2. owned chunks of the range: chunk % world == rank, as in the whole-buffer kernel (the optimizer state of a chunk
+    //    always lives on the same rank, whichever kernel updates it)
+    const int first = ((dp.rank - p.chunk_begin) % dp.world + dp.world) % dp.world;
+    const int n_owned = n_chunks > first ? (n_chunks - first + dp.world - 1) / dp.world : 0;
+    for (int j = vblock * kLayerUnroll; j < n_owned; j += vgrid * kLayerUnroll) {
+        float g[kLayerUnroll][4];
+        int tix[kLayerUnroll];
+#pragma unroll
+        for (int u = 0; u < kLayerUnroll; ++u) {
+            const int chunk = p.chunk_begin + first + (j + u) * dp.world;
+            tix[u] = (j + u < n_owned) ? p.chunk_tensor[chunk] : -1;
+            if (tix[u] < 0) continue;
+            const int64_t i0 = (int64_t)chunk * kChunk + tid * 4;
+            if (i0 - p.t[tix[u]].offset >= p.t[tix[u]].count) { tix[u] = -1; continue; }
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(g[u][0]), "=f"(g[u][1]), "=f"(g[u][2]), "=f"(g[u][3]) : "l"(grads_mc + i0) : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < kLayerUnroll; ++u) {
+            if (tix[u] < 0) continue;
+            const int chunk = p.chunk_begin + first + (j + u) * dp.world;
+            const TensorDesc d = p.t[tix[u]];
+            const int64_t i0 = (int64_t)chunk * kChunk + tid * 4;
+            const int64_t j0 = i0 - d.offset;
+            apply_update(p, d, i0, j0, (int)min((int64_t)4, d.count - j0), g[u]);
+        }
+    }
+    (void)rank_barrier(own, dp, 9, 2u * dp.step + 1u, true);
+}
+
+int launch_nvls_layer(const OptArgs &a, const DpArgs &dp, const float *grads_mc, int64_t n_chunks, int n_ctas, cudaStream_t st) {
+    TS_REQUIRE(grads_mc != nullptr && a.params_mc != nullptr, TS_E_INVALID, "nvls optimizer: multicast mappings missing");
+    TS_REQUIRE(n_ctas >= 1 && n_chunks >= 1, TS_E_INVALID, "nvls layer exchange: %d CTAs, %lld chunks", n_ctas, (long long)n_chunks);
+    const size_t smem = (size_t)a.partial_depth * kLayerThreads * 16;
+    static bool done[64] = {false};
+    int dev = 0;
+    TS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!done[dev & 63]) {
+        TS_CUDA_CHECK(cudaFuncSetAttribute(nvls_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kLayerThreads * 16));
+        done[dev & 63] = true;
+    }
+    TS_REQUIRE(a.partial_depth <= 4, TS_E_INVALID, "nvls layer exchange runs at partial depth <= 4");
+    int64_t grid = (n_chunks + kLayerGroups - 1) / kLayerGroups;
+    if (grid > n_ctas) grid = n_ctas;
+    nvls_layer_kernel<<<dim3((unsigned)grid), dim3(kLayerThreads), smem, st>>>(a, dp, grads_mc, (int)n_chunks);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
 }
 
 // 64 KiB of dynamic shared memory needs the opt-in attribute, once per device.
