@@ -347,3 +347,66 @@ def test_bf16_checkpoint_roundtrip_and_adam_resume():
     for a, b in zip(net.parameters(), net3.parameters()):
         assert torch.equal(a.detach().cpu(), b.detach().cpu()), 'resumed run diverged from the uninterrupted one'
     assert int(resumed.optimizer.state_dict()['state'][0]['step']) == 4
+
+
+# ------------------------------------------------------------------ the single-kernel step (batches of at most 64 rows)
+@pytest.mark.parametrize('H,B,optimizer,lr,x_bf16', [(256, 32, 'adam', 1e-3, False), (256, 64, 'sgd', 0.05, False), (256, 1, 'adam', 1e-3, False),
+                                                     (256, 33, 'adam', 1e-3, True), (128, 7, 'sgd', 0.05, False), (64, 32, 'adam', 1e-3, True),
+                                                     (256, 32, 'sgd', 0.05, True)])
+def test_single_kernel_step_against_oracle_and_launch_count(H, B, optimizer, lr, x_bf16):
+    """ts_fit_step on a small batch of the shipped shape class runs as ONE kernel (forward, loss, backward, optimizer update):
+    exactly one launch per fit, predictions exact-or-explained, loss and weights within 1e-2 of the emulating oracle over four
+    steps (dropout masks supplied), and evaluate afterwards sees the refreshed bf16 operand copies."""
+    from torchsystem_b200 import _lib
+    dims, p, steps = [784, H, 10], 0.1, 4
+    x, y = synthetic(B * steps + 50, seed=17)
+    x = x.bfloat16().float()
+    init = seeded_init(dims, bf16=True)
+    model, net = build_model(dims, p, 'relu', optimizer, lr, init, 'bf16', max_batch=64)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], dropout=p, opt_kind=OPT[optimizer], lr=lr, emulate_bf16=True)
+    g = torch.Generator().manual_seed(7)
+    ties = set()
+    for s in range(steps):
+        xb, yb = x[s * B:(s + 1) * B], y[s * B:(s + 1) * B]
+        mask = (torch.rand(B, H, generator=g) >= p).to(torch.uint8)
+        ties |= relu_gate_ties(oracle, xb.numpy(), [mask.numpy()])
+        before = _lib.lib.ts_launch_count()
+        fit_checked(model, net, oracle, xb.flatten(1).bfloat16() if x_bf16 else xb, yb, [mask], f'step kernel H={H} B={B} step {s}')
+        assert _lib.lib.ts_launch_count() - before == 1, 'a small-batch fit must be a single kernel launch'
+    evaluate_checked(model, net, oracle, x[steps * B:], y[steps * B:], f'step kernel H={H} evaluate')
+    assert_params_close(net_params(net), oracle.parameters(), 1e-2, lr=lr, steps=steps, adam=optimizer == 'adam', tie_units=ties)
+    # param.grad stays observable: the last step's gradient of W2 is what the oracle computed
+    assert net.linears()[1].weight.grad is not None and torch.isfinite(net.linears()[1].weight.grad).all()
+
+
+@pytest.mark.parametrize('kind', ['sgd_momentum_nesterov', 'adamw_amsgrad'])
+def test_single_kernel_step_equals_multi_kernel_path(monkeypatch, kind):
+    """The one-kernel step and the four-kernel sequence apply the same update rule (opt_math.cuh): same predictions, loss and
+    weights to fp32 round-off (the gradient sums are taken in a different order), in-kernel hash dropout included."""
+    from torchsystem_b200 import B200Classifier, MLP
+    dims, B, steps = [784, 256, 10], 32, 5
+    x, y = synthetic(B * steps, seed=23)
+    init = seeded_init(dims, bf16=True)
+    outs = []
+    for flag in ('1', '0'):
+        monkeypatch.setenv('TSB200_STEP_KERNEL', flag)
+        net = MLP(784, 256, 10, dropout=0.1, activation=torch.nn.ReLU())
+        with torch.no_grad():
+            for q, w in zip([t for lin in net.linears() for t in (lin.weight, lin.bias)], init):
+                q.copy_(torch.from_numpy(np.asarray(w)))
+        if kind == 'sgd_momentum_nesterov':
+            opt = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9, nesterov=True, weight_decay=1e-4)
+        else:
+            opt = torch.optim.AdamW(net.parameters(), lr=1e-3, weight_decay=1e-2, amsgrad=True)
+        model = B200Classifier(net, torch.nn.CrossEntropyLoss(), opt, precision='bf16', device='cuda:0', max_batch=B, dropout_seed=5)
+        got = []
+        for s in range(steps):
+            pr, l = model.fit(x[s * B:(s + 1) * B].cuda(), y[s * B:(s + 1) * B].cuda())
+            got.append((pr.cpu().numpy(), l.item()))
+        outs.append((got, net_params(net), model.engine.step_count))
+    (ga, wa, sa), (gb, wb, sb) = outs
+    assert sa == sb == steps
+    for (pa, la), (pb, lb) in zip(ga, gb):
+        assert np.array_equal(pa, pb)
+        assert la == pytest.approx(lb, rel=1e-5)
+    assert_params_close(wa, wb, 1e-4, lr=1e-3, steps=steps, adam=kind != 'sgd_momentum_nesterov')

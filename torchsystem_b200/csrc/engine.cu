@@ -28,9 +28,9 @@ void set_error(const char *fmt, ...) {
 static inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
 // ---- optional per-kernel timing: CUDA events recorded on the launching stream around each launch.
-enum { K_CAST = 0, K_FWD_GEMM, K_HEAD, K_HEAD_WGRAD, K_COLSUM, K_DW_GEMM, K_DX_GEMM, K_OPT, K_FUSED, K_COUNT };
+enum { K_CAST = 0, K_FWD_GEMM, K_HEAD, K_HEAD_WGRAD, K_COLSUM, K_DW_GEMM, K_DX_GEMM, K_OPT, K_FUSED, K_STEP, K_COUNT };
 static const char *const kKindNames[K_COUNT] = {"cast_bf16", "fwd_gemm", "head", "head_wgrad", "colsum",
-                                                "dw_gemm",   "dx_gemm",  "optimizer", "fused_fwd_head"};
+                                                "dw_gemm",   "dx_gemm",  "optimizer", "fused_fwd_head", "fit_step_small"};
 struct ProfPair { int kind; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfPair> g_prof;
@@ -64,6 +64,7 @@ struct ts_mlp {
     int bwd_sms = 148;            // SMs the backward GEMMs use: fewer than sm_count leaves room for a concurrently running collective
     cudaEvent_t *ov_events = nullptr;   // per-call (ts_fit_backward_overlap): event of layer l recorded once its gradients are enqueued
     int32_t *ov_final = nullptr;        // per-call out: gradient tensor t is final in `grads` when its layer's event fires
+    int step_kernel = 1;          // batches of at most 64 rows: the whole fit step in one kernel (TSB200_STEP_KERNEL=0: off)
     int inkernel_cast = -1;       // fp32 batches converted inside the fused kernel: 1 always, 0 never (cast kernel in front), -1 by batch size
 
     // flat parameter layout (torch order: W0, b0, W1, b1, ...)
@@ -576,6 +577,26 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     if (dp && !m->nvls) m->grads = m->dp_grads[m->step & 1][m->dp_rank];     // this step's peer-visible gradient buffer
     const void *a0 = nullptr, *a_last = nullptr;
     int nsplit[2 * kMaxLayers] = {0};
+    if (m->fused && m->step_kernel && update && !dp && (x_dtype == TS_DT_F32 || x_dtype == TS_DT_BF16) &&
+        fit_step_supported(m->dims[0], m->dims[1], m->dims[2], B)) {
+        // small batch (the size the reference ships): forward, loss, backward and the optimizer update in ONE kernel
+        FitStepArgs f{};
+        if (x_dtype == TS_DT_F32) f.X_f32 = (const float *)x; else f.X = (const __nv_bfloat16 *)x;
+        f.W1 = m->shadow + m->shadow_off[0]; f.W2p = m->shadow + m->shadow_off[1];
+        f.y = y; f.B = B; f.D = m->dims[0]; f.H = m->dims[1]; f.C = m->dims[2];
+        f.pred = pred; f.record = rec;
+        f.drop = drop_spec(m, masks, seed, 0, true);
+        f.training = m->p > 0.0f;
+        f.off_w1 = m->off[0]; f.off_b1 = m->off[1]; f.off_w2 = m->off[2]; f.off_b2 = m->off[3];
+        f.sh_w1 = m->shadow_off[0]; f.sh_w2 = m->shadow_off[1];
+        bool any_partial = false;
+        rc = fill_tensor_table(m, nullptr, f.opt, &any_partial, st);
+        if (rc) return rc;
+        f.opt.update = 1; f.opt.grad_scale = 1.0f;
+        fill_update(m, f.opt);
+        ProfScope ps(K_STEP, st);
+        return launch_fit_step(f, st);
+    }
     if (m->fused) {
         rc = fused_forward(m, x, x_dtype, y, B, masks, seed, true, pred, rec, &a0, st);
         if (rc) return rc;
@@ -765,6 +786,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     m->act = activation; m->p = dropout_p; m->scale = 1.0f / (float)(1.0 - (double)dropout_p);
     m->prec = precision; m->device = device; m->sm_count = sms; m->bwd_sms = sms;
     if (const char *e = getenv("TSB200_INKERNEL_CAST")) m->inkernel_cast = atoi(e) != 0 ? 1 : 0;
+    if (const char *e = getenv("TSB200_STEP_KERNEL")) m->step_kernel = atoi(e) != 0 ? 1 : 0;
     m->n_tensors = 2 * m->n_layers;
     int64_t o = 0, so = 0;
     for (int l = 0; l < m->n_layers; ++l) {
@@ -1088,6 +1110,12 @@ int32_t ts_test_fused_trace(uint64_t *out) {
     TS_REQUIRE(out, TS_E_INVALID, "null argument");
     TS_CUDA_CHECK(cudaDeviceSynchronize());
     return read_fused_trace((unsigned long long *)out);
+}
+
+int32_t ts_test_step_trace(uint64_t *out) {
+    TS_REQUIRE(out, TS_E_INVALID, "null argument");
+    TS_CUDA_CHECK(cudaDeviceSynchronize());
+    return read_step_trace((unsigned long long *)out);
 }
 
 int32_t ts_profile_begin(void) {

@@ -209,6 +209,26 @@ struct FusedMlpArgs {
     unsigned int *ticket;
     ts_batch_record *record;
 };
+// ---------------------------------------------------------------- single-kernel fit step for small batches (step_kernel.cu)
+struct FitStepArgs {
+    const __nv_bfloat16 *X;     // [B, D] bf16 inputs, or nullptr when X_f32 is given
+    const float *X_f32;         // [B, D] fp32 inputs, converted on chip
+    const __nv_bfloat16 *W1;    // [H, D] bf16 shadow of layer-0 weight (rewritten by the kernel)
+    const __nv_bfloat16 *W2p;   // [16, H] bf16 shadow of the last weight (rewritten by the kernel)
+    const int64_t *y;
+    int64_t B;
+    int D, H, C;
+    int64_t *pred;
+    DropoutSpec drop;
+    int training;
+    ts_batch_record *record;
+    int64_t off_w1, off_b1, off_w2, off_b2, sh_w1, sh_w2;
+    OptArgs opt;                // flat buffers and this update's hyper-parameters (tensor table unused)
+};
+bool fit_step_supported(int D, int H, int C, int64_t B);
+int launch_fit_step(const FitStepArgs &a, cudaStream_t st);
+int read_step_trace(unsigned long long *out_host);
+
 bool fused_mlp_supported(int D, int H, int C);
 inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }
 int fused_cluster_size(int64_t B, int H, int sm_count);   // CTAs per 128-row slab the launcher will use

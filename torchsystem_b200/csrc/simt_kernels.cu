@@ -1,6 +1,7 @@
 // SIMT kernels of the tsb200 engine: the fp32 dense path (1e-5 parity mode), the fused head
 // (last Linear + cross-entropy + argmax + dZ + dA, shared by both precision modes), gradient
 // reductions, the flat optimizer and the metric accumulators. sm_100a only.
+#include "opt_math.cuh"
 #include "kernels.h"
 
 namespace tsb {
@@ -700,31 +701,8 @@ __device__ __forceinline__ void apply_update(const OptArgs &p, const TensorDesc 
     float w[4] = {w4.x, w4.y, w4.z, w4.w}, m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
     float x[4] = {x4.x, x4.y, x4.z, x4.w};
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-        if (e >= n) continue;
-        float grad = g[e] * p.grad_scale;
-        if (!adam) {                                                       // sgd.py _single_tensor_sgd
-            if (p.weight_decay != 0.0f) grad = grad + p.weight_decay * w[e];   // grad.add(param, alpha=weight_decay)
-            if (p.momentum != 0.0f) {
-                // buf = clone(grad) on the first step, else buf.mul_(momentum).add_(grad, alpha=1 - dampening)
-                m[e] = p.first_step ? grad : m[e] * p.momentum + p.one_minus_dampening * grad;
-                grad = p.nesterov ? grad + p.momentum * m[e] : m[e];
-            }
-            w[e] = w[e] - p.lr * grad;                                     // param.add_(grad, alpha=-lr)
-        } else {                                                           // adam.py _single_tensor_adam
-            if (p.weight_decay != 0.0f) {
-                if (p.decoupled) w[e] = w[e] * p.wd_mul;                   // param.mul_(1 - lr * weight_decay)   (AdamW)
-                else grad = grad + p.weight_decay * w[e];
-            }
-            m[e] = m[e] + p.one_minus_beta1 * (grad - m[e]);               // exp_avg.lerp_(grad, 1 - beta1)
-            v[e] = v[e] * p.beta2;                                         // exp_avg_sq.mul_(beta2)
-            v[e] = v[e] + p.one_minus_beta2 * (grad * grad);               //   .addcmul_(grad, grad, value=1 - beta2)
-            float second = v[e];
-            if (p.amsgrad) { x[e] = fmaxf(x[e], v[e]); second = x[e]; }    // torch.maximum(max_exp_avg_sq, exp_avg_sq)
-            const float denom = sqrtf(second) / p.bc2_sqrt + p.eps;        // (sqrt(.) / sqrt(bias_correction2)).add_(eps)
-            w[e] = w[e] - p.step_size * (m[e] / denom);                    // param.addcdiv_(exp_avg, denom, value=-step_size)
-        }
-    }
+    for (int e = 0; e < 4; ++e)
+        if (e < n) opt_update_element(p, g[e], w[e], m[e], v[e], x[e]);
     if (p.params_mc != nullptr)      // one store, delivered to this address in every rank's parameter buffer by the NVSwitch
         asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p.params_mc + i0), "f"(w[0]), "f"(w[1]),
                      "f"(w[2]), "f"(w[3]) : "memory");
