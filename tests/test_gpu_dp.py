@@ -116,9 +116,9 @@ def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
     backward pass is still running, biases in a packed all-reduce at the end. Must match the full-batch oracle."""
     monkeypatch.setenv('TSB200_DP_OVERLAP', '1' if overlap == 'backward' else '0')
     monkeypatch.setenv('TSB200_DP_BUCKETS', '1' if overlap == 'buckets' else '0')
-    # 'nvls': each layer's in-switch reduce + update on a side stream under the rest of the backward pass (the default for
-    # nets on the layer-by-layer path); 'nvls_one_kernel': the whole buffer in one kernel after the backward pass
-    monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', '0' if overlap == 'nvls_one_kernel' else '16')
+    # 'nvls': each layer's in-switch reduce + update on a side stream under the rest of the backward pass (TSB200_NVLS_OVERLAP_SMS,
+    # for nets on the layer-by-layer path); 'nvls_one_kernel': the whole buffer in one kernel after the backward pass
+    monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', '0' if overlap == 'nvls_one_kernel' else '20')
     import torch.multiprocessing as mp
     from oracle import mlp_numpy as onp
     from tests.test_gpu_parity import synthetic, seeded_init
@@ -144,7 +144,7 @@ def test_two_gpu_nvls_overlap_is_bit_identical_to_one_kernel_adam(tmp_path, monk
     import torch.multiprocessing as mp
     dims, B = (784, 2048, 2048, 1024, 10), 1024
     outs = []
-    for sms in ('16', '0'):
+    for sms in ('20', '0'):
         monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', sms)
         out = str(tmp_path / f'sms{sms}_rank0.npz')
         mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nvls', out, dims, B, 'adam'), nprocs=2, join=True)
