@@ -64,6 +64,7 @@ struct ts_mlp {
     int bwd_sms = 148;            // SMs the backward GEMMs use: fewer than sm_count leaves room for a concurrently running collective
     cudaEvent_t *ov_events = nullptr;   // per-call (ts_fit_backward_overlap): event of layer l recorded once its gradients are enqueued
     int32_t *ov_final = nullptr;        // per-call out: gradient tensor t is final in `grads` when its layer's event fires
+    unsigned int step_flag = 0;   // value of the single-kernel step's gradient-ready counter after the launches so far
     int step_kernel = 1;          // batches of at most 64 rows: the whole fit step in one kernel (TSB200_STEP_KERNEL=0: off)
     int inkernel_cast = -1;       // fp32 batches converted inside the fused kernel: 1 always, 0 never (cast kernel in front), -1 by batch size
 
@@ -594,6 +595,9 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         if (rc) return rc;
         f.opt.update = 1; f.opt.grad_scale = 1.0f;
         fill_update(m, f.opt);
+        m->step_flag += (unsigned int)(m->dims[1] / 64);       // every CTA of the compute cluster adds one
+        f.flag = m->ticket + 16; f.flag_target = m->step_flag;
+        f.n_chunks = (int)m->n_chunks; f.sm_count = m->sm_count;
         ProfScope ps(K_STEP, st);
         return launch_fit_step(f, st);
     }
@@ -958,6 +962,7 @@ int32_t ts_mlp_set_workspace(ts_mlp *m, void *workspace, int64_t bytes, int64_t 
     // one-time set-up copies (synchronous): chunk map, ticket
     TS_CUDA_CHECK(cudaMemcpy(m->d_chunk_tensor, m->chunk_tensor_host.data(), (size_t)m->n_chunks * 4, cudaMemcpyHostToDevice));
     TS_CUDA_CHECK(cudaMemset(m->ticket, 0, 256));
+    m->step_flag = 0;
     if (m->lut_set) TS_CUDA_CHECK(cudaMemcpy(m->d_lut, m->lut_host, sizeof(m->lut_host), cudaMemcpyHostToDevice));
     m->ws_set = true;
     return TS_OK;

@@ -223,7 +223,10 @@ struct FitStepArgs {
     int training;
     ts_batch_record *record;
     int64_t off_w1, off_b1, off_w2, off_b2, sh_w1, sh_w2;
-    OptArgs opt;                // flat buffers and this update's hyper-parameters (tensor table unused)
+    OptArgs opt;                // flat buffers, tensor table (nsplit 0: gradients final in `grads`) and this update's hyper-parameters
+    unsigned int *flag;         // device counter the compute cluster raises by `ns` per step; the updater CTAs wait for flag_target
+    unsigned int flag_target;
+    int n_chunks, sm_count;
 };
 bool fit_step_supported(int D, int H, int C, int64_t B);
 int launch_fit_step(const FitStepArgs &a, cudaStream_t st);

@@ -9,12 +9,16 @@
 //   A, Z, loss, argmax, dZ, dA, dH, dW2^T, db1   exactly as fused_mlp.cu (partial logits all-gathered over DSMEM)
 //   dW1^T slice  = X^T dH: the resident X blocks re-read as MN-major A operands (M = input feature, K = batch row), the dH
 //                tile as the MN-major B operand; 7 M-tiles x 64 columns in TMEM
-//   update       epilogue threads apply SGD / Adam (opt_math.cuh, the arithmetic of the flat optimizer kernel) straight
-//                from TMEM: TMEM lane = input feature d, so a warp touches 32 consecutive elements of one W1 row; they
-//                also write `grads` (param.grad stays observable) and refresh the bf16 shadows
+//   gradients    epilogue threads store them from TMEM into `grads` (TMEM lane = input feature d, so a warp writes 32
+//                consecutive elements of one W1 row), then the cluster raises a flag
+//   update       the optimizer state is 30 bytes per parameter of memory traffic, far more than four SMs can move in a few
+//                microseconds (measured: 52 us when the compute cluster did it alone). So the SAME launch carries ~128 more
+//                CTAs, one per SM, that do nothing but the update: they fetch their share of the parameters and moments into
+//                registers while the compute cluster is still working, wait for the flag, read their share of the gradient
+//                from L2, apply SGD / Adam (opt_math.cuh: the arithmetic of the flat optimizer kernel) and refresh the bf16
+//                shadows. One launch, one dependency edge inside it, no second kernel.
 //
-// Every parameter is owned by exactly one CTA of the cluster (its 64 hidden units; cluster rank 0 also owns b2), so the
-// step needs no grid-wide synchronisation. classifier.py:29-35; mlp.py:14-17; torch/optim/adam.py, sgd.py.
+// classifier.py:29-35; mlp.py:14-17; torch/optim/adam.py, sgd.py.
 #include <cstdlib>
 
 #include "opt_math.cuh"
@@ -28,7 +32,7 @@ namespace {
 
 constexpr int kThreads = 352;    // warp 0: X producer (bf16 inputs), 1: MMA issuer + TMEM owner, 2: W2 / W1 producer, 3..10: epilogue
 constexpr int kEpiThreads = 256;
-constexpr int kMaxStages = 6;
+constexpr int kMaxStages = 13;   // the whole W1 slice in flight when shared memory allows
 constexpr int CP = 16;           // classes padded to one UMMA N / K step
 constexpr int BN = 64;           // hidden units per CTA
 constexpr int kXBlocks = 14;     // 64-column blocks of X kept resident (13 hold data for D <= 832, one more is over-read only)
@@ -51,7 +55,11 @@ struct StepParams {
     ts_batch_record *record;
     int64_t off_w1, off_b1, off_w2, off_b2;       // element offsets in the flat buffers
     int64_t sh_w1, sh_w2;                         // element offsets in the bf16 shadow buffer
-    OptArgs opt;                                  // flat buffers + hyper-parameters of this update
+    OptArgs opt;                                  // flat buffers, tensor table (gradients final in `grads`) + hyper-parameters
+    unsigned int *flag;                           // monotonic counter: += ns per step once the gradients are in `grads`
+    unsigned int flag_target;
+    int n_chunks;                                 // 1024-element chunks of the flat buffers
+    int n_updaters;                               // CTAs behind the compute cluster
 };
 
 __device__ unsigned long long g_step_trace[32];
@@ -76,20 +84,80 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
-// One parameter element: read state, update (opt_math.cuh), write parameter / state / gradient.
-__device__ __forceinline__ float update_scalar(const OptArgs &o, int64_t idx, float g) {
+constexpr int kUpdQuads = 4;                      // float4 quads an updater thread can own
+
+// ---- updater CTAs: parameters and moments into registers early, then gradient -> update -> store once the flag is up
+__device__ __forceinline__ void updater_role(const StepParams &p, int u) {
+    const OptArgs &o = p.opt;
     const bool adam = o.kind != TS_OPT_SGD;
     const bool use_m = adam || o.momentum != 0.0f;
     const bool use_x = adam && o.amsgrad;
-    float w = o.params[idx], m = use_m ? o.exp_avg[idx] : 0.0f, v = adam ? o.exp_avg_sq[idx] : 0.0f;
-    float x = use_x ? o.max_exp_avg_sq[idx] : 0.0f;
-    opt_update_element(o, g, w, m, v, x);
-    o.params[idx] = w;
-    o.grads[idx] = g;
-    if (use_m) o.exp_avg[idx] = m;
-    if (adam) o.exp_avg_sq[idx] = v;
-    if (use_x) o.max_exp_avg_sq[idx] = x;
-    return w;
+    const int64_t nq = (int64_t)p.n_chunks * (kChunk / 4);
+    const int64_t stride = (int64_t)p.n_updaters * blockDim.x;
+    float4 w[kUpdQuads], m[kUpdQuads], v[kUpdQuads], x[kUpdQuads];
+    int tix[kUpdQuads];
+    pdl_wait();                 // the previous step's updaters have written the state this one reads
+    pdl_launch_dependents();
+#pragma unroll
+    for (int r = 0; r < kUpdQuads; ++r) {
+        const int64_t q = (int64_t)u * blockDim.x + threadIdx.x + r * stride;
+        tix[r] = -1;
+        w[r] = m[r] = v[r] = x[r] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (q < nq) {
+            const int t = o.chunk_tensor[q / (kChunk / 4)];
+            if (t >= 0 && q * 4 - o.t[t].offset < o.t[t].count) {
+                tix[r] = t;
+                w[r] = *reinterpret_cast<const float4 *>(o.params + q * 4);
+                if (use_m) m[r] = *reinterpret_cast<const float4 *>(o.exp_avg + q * 4);
+                if (adam) v[r] = *reinterpret_cast<const float4 *>(o.exp_avg_sq + q * 4);
+                if (use_x) x[r] = *reinterpret_cast<const float4 *>(o.max_exp_avg_sq + q * 4);
+            }
+        }
+    }
+    if (threadIdx.x == 0) {
+        unsigned long long t0 = 0;
+        for (uint32_t spins = 0;; ++spins) {
+            unsigned int seen;
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.flag) : "memory");
+            if ((int)(seen - p.flag_target) >= 0) break;
+            if ((spins & 4095u) == 4095u) {          // only a protocol bug gets here: fail loudly instead of hanging
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now; else if (now - t0 > 10000000000ull) __trap();
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kUpdQuads; ++r) {
+        if (tix[r] < 0) continue;
+        const int64_t i0 = ((int64_t)u * blockDim.x + threadIdx.x + r * stride) * 4;
+        const TensorDesc d = o.t[tix[r]];
+        const int64_t j0 = i0 - d.offset;
+        const int n = (int)min((int64_t)4, d.count - j0);
+        const float4 g4 = __ldcg(reinterpret_cast<const float4 *>(o.grads + i0));     // written by another SM: read it from L2
+        const float g[4] = {g4.x, g4.y, g4.z, g4.w};
+        float ww[4] = {w[r].x, w[r].y, w[r].z, w[r].w}, mm[4] = {m[r].x, m[r].y, m[r].z, m[r].w};
+        float vv[4] = {v[r].x, v[r].y, v[r].z, v[r].w}, xx[4] = {x[r].x, x[r].y, x[r].z, x[r].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            if (e < n) opt_update_element(o, g[e], ww[e], mm[e], vv[e], xx[e]);
+        *reinterpret_cast<float4 *>(o.params + i0) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+        if (use_m) *reinterpret_cast<float4 *>(o.exp_avg + i0) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        if (adam) *reinterpret_cast<float4 *>(o.exp_avg_sq + i0) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        if (use_x) *reinterpret_cast<float4 *>(o.max_exp_avg_sq + i0) = make_float4(xx[0], xx[1], xx[2], xx[3]);
+        if (d.shadow_off >= 0) {
+            __nv_bfloat16 *sh = o.shadow + d.shadow_off + j0;
+            if (n == 4 && ((reinterpret_cast<uintptr_t>(sh) & 7) == 0)) {
+                uint2 pk;
+                pk.x = pack_bf16(ww[0], ww[1]);
+                pk.y = pack_bf16(ww[2], ww[3]);
+                *reinterpret_cast<uint2 *>(sh) = pk;
+            } else {
+                for (int e = 0; e < n; ++e) sh[e] = __float2bfloat16_rn(ww[e]);
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -104,7 +172,7 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
     __shared__ float s_loss[4];
     __shared__ int s_corr[4];
 
-    // shared memory: [A tile | dH tile | dZ tile] (16 KiB each) | W2 tile 2 KiB | b1 slice | partial logits [ns][128][16] |
+    // shared memory: [A tile | dH tile | dZ tile] (16 KiB each) | W2 tile 2 KiB | b1 slice | partial logits [ns][rbox][16] |
     //                resident X: kXBlocks x (rbox x 128 B) | W1 ring: stages x 8 KiB. The forward MMAs address every X block
     //                as 128 rows; what they read past the block's rbox rows (the next blocks, the head of the ring) only
     //                reaches TMEM lanes >= rbox, which nobody reads.
@@ -115,12 +183,17 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
     float *b1s = reinterpret_cast<float *>(w2_tile + 2048);
     float *zbuf = b1s + BN;
     const uint32_t xkb_bytes = (uint32_t)p.rbox * 128u;
-    uint8_t *xres = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(zbuf + (p.ns > 1 ? p.ns * BM * CP : 0)) + 1023) & ~(uintptr_t)1023);
+    uint8_t *xres = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(zbuf + (p.ns > 1 ? p.ns * p.rbox * CP : 0)) + 1023) & ~(uintptr_t)1023);
     uint8_t *ring = xres + (size_t)kXBlocks * xkb_bytes;            // 1024-aligned: xkb_bytes is a multiple of 4096
     const uint32_t b_bytes = BN * 128;
+    const bool w1_resident = p.stages >= p.num_kblocks;
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int ns = p.ns;
+    if ((int)blockIdx.x >= ns) {           // every cluster behind the first one only updates
+        updater_role(p, (int)blockIdx.x - ns);
+        return;
+    }
     const uint32_t rank = ns > 1 ? cluster_rank() : 0u;
     const int n0 = (int)rank * BN;
     if (threadIdx.x == 0) STRACE(0);
@@ -166,16 +239,25 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
             tma_load_2d(&tma_w2, &w2_full_bar, w2_tile, n0, 0);
         }
         __syncwarp();
-        int s = 0;
-        uint32_t phase = 0;
-        for (int kb = 0; kb < p.num_kblocks; ++kb) {
+        if (w1_resident) {
+            // the whole W1 slice fits: every block goes out at once against one barrier, no stage is ever reused
             if (elect_one()) {
-                mbar_wait(&empty_bar[s], phase ^ 1);
-                mbar_expect_tx(&full_bar[s], b_bytes);
-                tma_load_2d(&tma_w1, &full_bar[s], ring + (size_t)s * b_bytes, kb * KATOM, n0);
+                mbar_expect_tx(&full_bar[0], (uint32_t)p.num_kblocks * b_bytes);
+                for (int kb = 0; kb < p.num_kblocks; ++kb) tma_load_2d(&tma_w1, &full_bar[0], ring + (size_t)kb * b_bytes, kb * KATOM, n0);
             }
             __syncwarp();
-            if (++s == p.stages) { s = 0; phase ^= 1; }
+        } else {
+            int s = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < p.num_kblocks; ++kb) {
+                if (elect_one()) {
+                    mbar_wait(&empty_bar[s], phase ^ 1);
+                    mbar_expect_tx(&full_bar[s], b_bytes);
+                    tma_load_2d(&tma_w1, &full_bar[s], ring + (size_t)s * b_bytes, kb * KATOM, n0);
+                }
+                __syncwarp();
+                if (++s == p.stages) { s = 0; phase ^= 1; }
+            }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
@@ -188,14 +270,16 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
         uint32_t phase = 0;
         for (int kb = 0; kb < p.num_kblocks; ++kb) {
             if (elect_one()) {
-                mbar_wait(&full_bar[s], phase);
-                tc_fence_after();
+                if (!w1_resident || kb == 0) {
+                    mbar_wait(&full_bar[s], phase);
+                    tc_fence_after();
+                }
                 const uint64_t adesc = make_desc(smem_u32(xres + (size_t)kb * xkb_bytes), TC_MAJOR_K, KATOM);
-                const uint64_t bdesc = make_desc(smem_u32(ring + (size_t)s * b_bytes), TC_MAJOR_K, KATOM);
+                const uint64_t bdesc = make_desc(smem_u32(ring + (size_t)(w1_resident ? kb : s) * b_bytes), TC_MAJOR_K, KATOM);
 #pragma unroll
                 for (int k = 0; k < KATOM / UMMA_K; ++k)
                     umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc_main, (kb > 0 || k > 0) ? 1u : 0u);
-                umma_commit(&empty_bar[s]);
+                if (!w1_resident) umma_commit(&empty_bar[s]);
                 if (kb == p.num_kblocks - 1) umma_commit(&h_full_bar);
                 if (kb == 0) STRACE(2);
             }
@@ -258,6 +342,7 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
             //      and features >= D become zeros (they meet zero-filled W1 columns / zero dH rows, which must not see NaNs)
             const int chunks = p.num_kblocks * 8;
             const int total = p.rbox * chunks;
+#pragma unroll 4
             for (int idx = et; idx < total; idx += kEpiThreads) {
                 const int r = idx / chunks, cc = idx - r * chunks;
                 const int d = cc * 8;
@@ -346,8 +431,9 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
             float z[CP];
             tmem_ld16(t_lane + (uint32_t)kZCol, z);
             if (ns > 1) {
-                const uint32_t mine = smem_u32(zbuf + ((size_t)rank * BM + r_local) * CP);
-                for (int t = 0; t < (ns >> 1); ++t) {
+                const bool in_box = r_local < p.rbox;             // rows past the padded batch hold nothing anybody reads
+                const uint32_t mine = smem_u32(zbuf + ((size_t)rank * p.rbox + (in_box ? r_local : 0)) * CP);
+                for (int t = 0; t < (ns >> 1) && in_box; ++t) {
                     const uint32_t dst = map_to_rank(mine, (uint32_t)t);
 #pragma unroll
                     for (int c = 0; c < CP; c += 4) st_cluster_v4(dst + c * 4, z[c], z[c + 1], z[c + 2], z[c + 3]);
@@ -356,8 +442,8 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
                 cluster_wait();
 #pragma unroll
                 for (int c = 0; c < CP; ++c) z[c] = 0.0f;
-                for (int t = 0; t < ns; ++t) {
-                    const float4 *src = reinterpret_cast<const float4 *>(zbuf + ((size_t)t * BM + r_local) * CP);
+                for (int t = 0; t < ns && in_box; ++t) {
+                    const float4 *src = reinterpret_cast<const float4 *>(zbuf + ((size_t)t * p.rbox + r_local) * CP);
 #pragma unroll
                     for (int c = 0; c < CP; c += 4) {
                         const float4 v4 = src[c >> 2];
@@ -425,8 +511,9 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
             tc_fence_after();
             float z[CP];
             tmem_ld16(t_lane + (uint32_t)kZCol, z);
-            const uint32_t mine = smem_u32(zbuf + ((size_t)rank * BM + r_local) * CP);
-            for (int t = ns >> 1; t < ns; ++t) {
+            const bool in_box = r_local < p.rbox;
+            const uint32_t mine = smem_u32(zbuf + ((size_t)rank * p.rbox + (in_box ? r_local : 0)) * CP);
+            for (int t = ns >> 1; t < ns && in_box; ++t) {
                 const uint32_t dst = map_to_rank(mine, (uint32_t)t);
 #pragma unroll
                 for (int c = 0; c < CP; c += 4) st_cluster_v4(dst + c * 4, z[c], z[c + 1], z[c + 2], z[c + 3]);
@@ -477,13 +564,13 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
             }
         }
 
-        // ===================== the update, straight from TMEM =====================
+        // ===================== gradients: TMEM -> `grads`, then the flag the updater CTAs wait for =====================
         if (elect_one()) mbar_wait(&g_full_bar, 0);
         __syncwarp();
         tc_fence_after();
         if (et == 0) STRACE(11);
-        const OptArgs &o = p.opt;
-        // W2 slice and b1 slice: TMEM lane = hidden unit (lanes 0..63), owned by the half-0 warps of quarters 0 and 1
+        float *grads = p.opt.grads;
+        // W2 slice and b1 slice: TMEM lane = hidden unit (lanes 0..63), held by the half-0 warps of quarters 0 and 1
         if (half == 0 && r_local < BN) {
             const int h = n0 + r_local;
             float gw[CP], gb[CP];
@@ -491,51 +578,28 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
             tmem_ld16(t_lane + (uint32_t)kGbCol, gb);
 #pragma unroll
             for (int c = 0; c < CP; ++c)
-                if (c < p.C) {
-                    const float w = update_scalar(o, p.off_w2 + (int64_t)c * p.H + h, gw[c]);
-                    o.shadow[p.sh_w2 + (int64_t)c * p.H + h] = __float2bfloat16_rn(w);
-                }
-            update_scalar(o, p.off_b1 + h, gb[CP - 1]);
+                if (c < p.C) grads[p.off_w2 + (int64_t)c * p.H + h] = gw[c];
+            grads[p.off_b1 + h] = gb[CP - 1];
         }
         if (rank == 0 && half == 0 && q == 0 && lane < p.C)           // s_db2 was filled before named barrier 2 above
-            update_scalar(o, p.off_b2 + lane, (s_db2[0][lane] + s_db2[1][lane]) + (s_db2[2][lane] + s_db2[3][lane]));
-        // W1 slice: M-tile t, TMEM lane = input feature d; this warp's 32 hidden columns, 16 at a time (48 loads in flight)
+            grads[p.off_b2 + lane] = (s_db2[0][lane] + s_db2[1][lane]) + (s_db2[2][lane] + s_db2[3][lane]);
+        // W1 slice: M-tile t, TMEM lane = input feature d, this warp's 32 hidden columns: 32 lanes = 128 contiguous bytes
 #pragma unroll 1
         for (int t = 0; t < kMTiles; ++t) {
             const int d = t * BM + r_local;
             if (t * BM + q * 32 >= p.D) break;               // warp-uniform: this quarter's features are all padding
-#pragma unroll 1
-            for (int cc = 0; cc < 32; cc += 16) {
-                float g[16];
-                tmem_ld16(t_lane + (uint32_t)(t * BN + cbeg + cc), g);
-                if (d < p.D) {
-                    const int64_t base = p.off_w1 + (int64_t)(n0 + cbeg + cc) * p.D + d;
-                    const bool adam = o.kind != TS_OPT_SGD;
-                    const bool use_m = adam || o.momentum != 0.0f;
-                    const bool use_x = adam && o.amsgrad;
-                    float w[16], m[16], v[16], x[16];
+            float g[32];
+            tmem_ld16(t_lane + (uint32_t)(t * BN + cbeg), *reinterpret_cast<float(*)[16]>(&g[0]));
+            tmem_ld16(t_lane + (uint32_t)(t * BN + cbeg + 16), *reinterpret_cast<float(*)[16]>(&g[16]));
+            if (d < p.D) {
+                float *dst = grads + p.off_w1 + (int64_t)(n0 + cbeg) * p.D + d;
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int64_t idx = base + (int64_t)j * p.D;
-                        w[j] = o.params[idx];
-                        m[j] = use_m ? o.exp_avg[idx] : 0.0f;
-                        v[j] = adam ? o.exp_avg_sq[idx] : 0.0f;
-                        x[j] = use_x ? o.max_exp_avg_sq[idx] : 0.0f;
-                    }
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int64_t idx = base + (int64_t)j * p.D;
-                        opt_update_element(o, g[j], w[j], m[j], v[j], x[j]);
-                        o.params[idx] = w[j];
-                        o.grads[idx] = g[j];
-                        if (use_m) o.exp_avg[idx] = m[j];
-                        if (adam) o.exp_avg_sq[idx] = v[j];
-                        if (use_x) o.max_exp_avg_sq[idx] = x[j];
-                        o.shadow[p.sh_w1 + (int64_t)(n0 + cbeg + cc + j) * p.D + d] = __float2bfloat16_rn(w[j]);
-                    }
-                }
+                for (int j = 0; j < 32; ++j) dst[(int64_t)j * p.D] = g[j];
             }
         }
+        __threadfence();                                     // this thread's gradient stores before the flag
+        named_bar_sync(3, kEpiThreads);
+        if (et == 0) atomicAdd(p.flag, 1u);
         if (et == 0) STRACE(12);
     }
     __syncwarp();
@@ -578,10 +642,20 @@ int launch_fit_step(const FitStepArgs &a, cudaStream_t st) {
     p.y = a.y; p.pred = a.pred; p.drop = a.drop; p.training = a.training; p.record = a.record;
     p.off_w1 = a.off_w1; p.off_b1 = a.off_b1; p.off_w2 = a.off_w2; p.off_b2 = a.off_b2; p.sh_w1 = a.sh_w1; p.sh_w2 = a.sh_w2;
     p.opt = a.opt;
-    TS_REQUIRE(p.opt.params && p.opt.grads && p.opt.shadow, TS_E_INVALID, "single-kernel step: flat buffers missing");
+    TS_REQUIRE(p.opt.params && p.opt.grads && p.opt.shadow && p.opt.chunk_tensor && a.flag, TS_E_INVALID, "single-kernel step: buffers missing");
+    p.flag = a.flag; p.flag_target = a.flag_target; p.n_chunks = a.n_chunks;
+    // updater CTAs: one per SM next to the compute cluster (every CTA of the launch reserves the same ~200 KB of shared
+    // memory, so they land on distinct SMs and all of them are resident: the compute cluster never waits for an SM)
+    int upd_clusters = (a.sm_count - 16) / p.ns - 1;
+    if (upd_clusters * p.ns > 96) upd_clusters = 96 / p.ns;      // leaves whole GPCs' worth of SMs free: the compute cluster always finds its four
+    const int64_t quads = (int64_t)a.n_chunks * (kChunk / 4);
+    const int need = (int)((quads + (int64_t)kThreads * kUpdQuads - 1) / ((int64_t)kThreads * kUpdQuads));
+    TS_REQUIRE(upd_clusters >= 1 && upd_clusters * p.ns >= need, TS_E_UNSUPPORTED, "single-kernel step: %d updater CTAs cannot cover %lld parameters",
+               upd_clusters * p.ns, (long long)quads * 4);
+    p.n_updaters = upd_clusters * p.ns;
 
     const uint32_t xkb_bytes = (uint32_t)p.rbox * 128u;
-    const size_t fixed = 3 * (size_t)BM * 128 + 2048 + (size_t)BN * 4 + (p.ns > 1 ? (size_t)p.ns * BM * CP * 4 : 0) + 1024 +
+    const size_t fixed = 3 * (size_t)BM * 128 + 2048 + (size_t)BN * 4 + (p.ns > 1 ? (size_t)p.ns * p.rbox * CP * 4 : 0) + 1024 +
                          (size_t)kXBlocks * xkb_bytes + 1024 + 64;
     p.stages = (int)((226u * 1024u - fixed) / (BN * 128));
     if (p.stages > kMaxStages) p.stages = kMaxStages;
@@ -607,7 +681,7 @@ int launch_fit_step(const FitStepArgs &a, cudaStream_t st) {
         TS_CUDA_CHECK(cudaFuncSetAttribute(fit_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_set[dev & 63] = true;
     }
-    TS_CUDA_CHECK(launch_pdl(fit_step_kernel, dim3((unsigned)p.ns), dim3(kThreads), smem, st, (unsigned)p.ns, mx, mw1, mw2, p));
+    TS_CUDA_CHECK(launch_pdl(fit_step_kernel, dim3((unsigned)(p.ns + p.n_updaters)), dim3(kThreads), smem, st, (unsigned)p.ns, mx, mw1, mw2, p));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
