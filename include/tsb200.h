@@ -105,6 +105,13 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims /*HOST*/, int32_t n_dims
                       float dropout_p, int32_t precision, int32_t device);
 int32_t ts_mlp_destroy(ts_mlp *m);
 
+/* TS_OK, or TS_E_INVALID once a batch has held a target outside [0, classes) -- e.g. CrossEntropyLoss's default
+ * ignore_index -100 (examples/tinysys/main.py:61), which this engine does not implement: such a batch's loss is NaN, the
+ * head kernel records the row in a host-visible word, and every later ts_fit_step / ts_eval_step (and this call, which a
+ * host can make after any synchronisation, as B200Metrics.compute does) fails until ts_mlp_clear_status. */
+int32_t ts_mlp_status(const ts_mlp *m);
+int32_t ts_mlp_clear_status(ts_mlp *m);
+
 /* offsets[2*(n_dims-1)] (HOST, in elements) of each parameter tensor in the flat buffers; *total = buffer length. */
 int32_t ts_mlp_param_layout(const ts_mlp *m, int64_t *offsets /*HOST*/, int64_t *total /*HOST*/);
 

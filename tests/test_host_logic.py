@@ -67,6 +67,36 @@ def test_identity_hash_goldens():
     assert compat.gethash(_MLP(784, 256, 10, dropout=0.5, activation=relu())) == 'af51a51a38f7ad81f9523360fafe7068'
 
 
+def test_named_registration_matches_the_reference_registry():
+    """`@register('name')` (torchsystem/registry/accessors.py:150-174): the name replaces the class name in gethash. The
+    stand-in must produce the id the reference's own registry produces (compared directly when /root/reference is here)."""
+    import importlib.util, os, sys
+    def build(register):
+        @register('encoder-v2')
+        class Net:
+            def __init__(self, width: int, depth: int = 2):
+                pass
+
+        @register
+        class Plain:
+            def __init__(self, width: int):
+                pass
+        return Net(64, depth=3), Plain(8)
+    from hashlib import md5
+    from json import dumps
+    named, plain = build(compat.register)
+    assert compat.gethash(named) == md5(('encoder-v2' + dumps({'width': 64, 'depth': 3})).encode()).hexdigest()
+    assert compat.gethash(plain) == md5(('Plain' + dumps({'width': 8})).encode()).hexdigest()
+    if os.path.isdir('/root/reference/torchsystem'):
+        sys.path.insert(0, '/root/reference')
+        try:
+            from torchsystem.registry import register as ref_register, gethash as ref_gethash
+            r_named, r_plain = build(ref_register)
+            assert ref_gethash(r_named) == compat.gethash(named) and ref_gethash(r_plain) == compat.gethash(plain)
+        finally:
+            sys.path.remove('/root/reference')
+
+
 def test_shard_bounds_equal_and_disjoint():
     spans = [shard_bounds(1_048_576 + 123, r, 8, 4096) for r in range(8)]
     assert all(hi - lo == spans[0][1] - spans[0][0] for lo, hi in spans)

@@ -39,6 +39,8 @@ PROTOTYPES = {
     'ts_mlp_create': (C.c_int32, [C.POINTER(C.c_void_p), C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_float,
                                   C.c_int32, C.c_int32]),
     'ts_mlp_destroy': (C.c_int32, [C.c_void_p]),
+    'ts_mlp_status': (C.c_int32, [C.c_void_p]),
+    'ts_mlp_clear_status': (C.c_int32, [C.c_void_p]),
     'ts_mlp_param_layout': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     'ts_mlp_set_input_lut': (C.c_int32, [C.c_void_p, C.POINTER(C.c_float)]),
     'ts_mlp_bind_params': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p]),

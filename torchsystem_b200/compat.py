@@ -2,8 +2,8 @@
 
 TorchSystem itself (Aggregate, Depends, Service, Producer/Consumer, Compiler, registry) is pure
 Python and stays UNCHANGED: when `torchsystem` is importable it is used as is, and every class in
-this package plugs into it (tests/test_dropin_reference.py runs the reference's own handlers and
-test-suite against this package).
+this package plugs into it (tests/test_host_logic.py runs the reference's own handlers and its
+test-suite with this package loaded, in the container that holds the reference tree).
 
 The GPU box has no copy of the reference, so for the benchmark and the `-m gpu` tests this module
 carries the few lines of behaviour the hot path touches, written from the documented semantics:
@@ -171,8 +171,16 @@ except ImportError:
             return {'name': name, 'arguments': args} if args else name
         return arg
 
-    def register(cls: type, excluded_args: list[int] | None = None, excluded_kwargs: set[str] | None = None) -> type:
-        """Record constructor arguments on instances as `__model__arguments__` (identity for gethash)."""
+    def register(cls: type | str, excluded_args: list[int] | None = None, excluded_kwargs: set[str] | None = None):
+        """Record constructor arguments on instances as `__model__arguments__` (identity for gethash). `@register` on a
+        class, or `@register('name')` to also set `__model__name__`, the name gethash uses instead of the class name
+        (torchsystem/registry/accessors.py:150-174, core.py cls_override_init)."""
+        if isinstance(cls, str):
+            name = cls
+            return lambda klass: _register(klass, excluded_args, excluded_kwargs, name)
+        return _register(cls, excluded_args, excluded_kwargs, None)
+
+    def _register(cls: type, excluded_args, excluded_kwargs, name):
         excluded_args, excluded_kwargs = excluded_args or [], excluded_kwargs or set()
         init = cls.__init__
         names = list(inspect.signature(cls).parameters)
@@ -182,6 +190,8 @@ except ImportError:
             captured = {n: _describe(a) for i, (a, n) in enumerate(zip(args, names)) if i not in excluded_args}
             captured |= {k: _describe(v) for k, v in kwargs.items() if k not in excluded_kwargs}
             object.__setattr__(self, '__model__arguments__', captured)
+            if name:
+                object.__setattr__(self, '__model__name__', name)
         cls.__init__ = __init__
         return cls
 

@@ -120,6 +120,7 @@ struct ts_mlp {
     cudaEvent_t dp_ev_layer[kMaxLayers] = {nullptr}, dp_ev_done = nullptr;
     int nvls_overlap_ctas = 0;            // 0: one whole-buffer kernel after the backward pass
     uint32_t dp_seq = 0;                  // launch counter of the nvls kernels: the rank barriers count in it
+    uint32_t *status_host = nullptr, *status_dev = nullptr;   // mapped pinned words: [0] = row + 1 of a target outside [0, C)
     uint32_t *dp_err_host = nullptr, *dp_err_dev = nullptr;   // mapped pinned word the DP kernels set when a peer never arrives
     double dp_timeout_s = 600.0;                               // TSB200_DP_TIMEOUT_S / ts_dp_set_timeout
     bool nvls = false;
@@ -206,6 +207,15 @@ DropoutSpec drop_spec(const ts_mlp *m, const uint8_t *const *masks, uint64_t see
     return d;
 }
 
+// An earlier batch held a target outside [0, classes): its loss is NaN; say so instead of training on.
+int target_status(const ts_mlp *m) {
+    const uint32_t bad = m->status_host ? *(volatile uint32_t *)m->status_host : 0u;
+    TS_REQUIRE(bad == 0u, TS_E_INVALID,
+               "a target outside [0, %d) was seen (row %u of its batch): CrossEntropyLoss's ignore_index (-100) is not implemented, "
+               "targets must be class indices; the loss of that batch is NaN (ts_mlp_clear_status resets this)", m->classes(), bad - 1u);
+    return TS_OK;
+}
+
 int check_ready(const ts_mlp *m, int64_t B, bool need_opt) {
     TS_REQUIRE(m != nullptr, TS_E_INVALID, "null handle");
     TS_REQUIRE(m->params && m->grads, TS_E_STATE, "parameters not bound: call ts_mlp_bind_params first");
@@ -213,7 +223,7 @@ int check_ready(const ts_mlp *m, int64_t B, bool need_opt) {
     TS_REQUIRE(!need_opt || m->opt_bound, TS_E_STATE, "optimizer not bound: call ts_opt_bind first");
     TS_REQUIRE(B >= 1 && B <= m->max_batch, TS_E_INVALID, "batch %lld outside [1, %lld] (workspace capacity)",
                (long long)B, (long long)m->max_batch);
-    return TS_OK;
+    return target_status(m);
 }
 
 // Forward through the hidden layers; *a_last receives the last hidden activation.
@@ -284,6 +294,7 @@ void fill_head(const ts_mlp *m, HeadArgs &h, const void *a_last, const int64_t *
     h.pred = pred; h.dz = nullptr; h.dH = nullptr; h.U_prev = nullptr;
     h.act = m->act;
     h.partials = m->head_partials; h.ticket = m->ticket; h.record = rec;
+    h.bad_target = m->status_dev;
 }
 
 // Tensor table of the optimizer kernels. Tensors with many row-block partials (batches beyond 16,384 rows) are summed in
@@ -420,7 +431,7 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     }
     f.drop = drop_spec(m, masks, seed, 0, train);
     f.training = train && m->p > 0.0f;
-    f.partials = m->head_partials; f.ticket = m->ticket; f.record = rec;
+    f.partials = m->head_partials; f.ticket = m->ticket; f.record = rec; f.bad_target = m->status_dev;
     ProfScope ps(K_FUSED, st);
     return launch_fused_mlp(f, m->sm_count, st);
 }
@@ -465,7 +476,7 @@ int tc_head_forward(ts_mlp *m, const void *a_last, const int64_t *y, int64_t B, 
     int rc = launch_tc_gemm(g, m->sm_count, st);
     if (rc) return rc;
     return launch_logits_head(m->zbuf, m->params + m->off[2 * (L - 1) + 1], y, B, m->dims[L], pred, train ? m->dz : nullptr, m->dzb,
-                              m->head_partials, m->ticket, rec, st);
+                              m->head_partials, m->ticket, rec, m->status_dev, st);
 }
 
 // Backward of the last layer on the tensor cores: dH = (dZ W_last) * act'(A_last) / (1 - p) with the activation gradient
@@ -585,7 +596,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         if (x_dtype == TS_DT_F32) f.X_f32 = (const float *)x; else f.X = (const __nv_bfloat16 *)x;
         f.W1 = m->shadow + m->shadow_off[0]; f.W2p = m->shadow + m->shadow_off[1];
         f.y = y; f.B = B; f.D = m->dims[0]; f.H = m->dims[1]; f.C = m->dims[2];
-        f.pred = pred; f.record = rec;
+        f.pred = pred; f.record = rec; f.bad_target = m->status_dev;
         f.drop = drop_spec(m, masks, seed, 0, true);
         f.training = m->p > 0.0f;
         f.off_w1 = m->off[0]; f.off_b1 = m->off[1]; f.off_w2 = m->off[2]; f.off_b2 = m->off[3];
@@ -812,6 +823,15 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     m->tc_head = precision == TS_PREC_BF16 && !m->fused && dims[n_dims - 1] <= 16;
     if (const char *e = getenv("TSB200_SIMT_HEAD"))      // A/B switch for measurements (GELU always takes the tensor-core last layer)
         m->tc_head = m->tc_head && (atoi(e) == 0 || activation == TS_ACT_GELU);
+    {   // status word the head kernels can reach: pinned host memory mapped into the device
+        void *h = nullptr, *d = nullptr;
+        if (cudaSetDevice(device) == cudaSuccess && cudaHostAlloc(&h, 64, cudaHostAllocMapped) == cudaSuccess) {
+            memset(h, 0, 64);
+            if (cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) { m->status_host = (uint32_t *)h; m->status_dev = (uint32_t *)d; }
+            else cudaFreeHost(h);
+        }
+        (void)cudaGetLastError();
+    }
     m->total = o;
     m->n_chunks = o / kChunk;
     m->chunk_tensor_host.assign((size_t)m->n_chunks, -1);
@@ -823,6 +843,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
 }
 
 int32_t ts_mlp_destroy(ts_mlp *m) {
+    if (m && m->status_host) cudaFreeHost(m->status_host);
     if (m && m->dp_err_host) cudaFreeHost(m->dp_err_host);
     if (m && m->dp_stream) {
         cudaStreamSynchronize(m->dp_stream);
@@ -831,6 +852,17 @@ int32_t ts_mlp_destroy(ts_mlp *m) {
         cudaStreamDestroy(m->dp_stream);
     }
     delete m;
+    return TS_OK;
+}
+
+int32_t ts_mlp_status(const ts_mlp *m) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    return target_status(m);
+}
+
+int32_t ts_mlp_clear_status(ts_mlp *m) {
+    TS_REQUIRE(m, TS_E_INVALID, "null handle");
+    if (m->status_host) *(volatile uint32_t *)m->status_host = 0u;
     return TS_OK;
 }
 

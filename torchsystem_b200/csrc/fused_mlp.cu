@@ -58,6 +58,7 @@ struct FusedParams {
     HeadPartial *partials;
     unsigned int *ticket;
     ts_batch_record *record;
+    uint32_t *bad_target;
 };
 
 // clock64 trace of CTA 0 of the most recent launch (read back by the ts_test_fused_trace hook)
@@ -482,7 +483,10 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             for (int c = 0; c < CP; ++c)
                 if (c == yy) zy = z[c];
             float row_loss = lse - zy;
-            if (yy < 0 || yy >= p.C) row_loss = __int_as_float(0x7fc00000);
+            if (yy < 0 || yy >= p.C) {                       // target outside [0, C): poison the loss, tell the host
+                row_loss = __int_as_float(0x7fc00000);
+                if (row_ok && rank == 0 && p.bad_target != nullptr) *reinterpret_cast<volatile uint32_t *>(p.bad_target) = (uint32_t)row + 1u;
+            }
             loss_acc = row_ok ? row_loss : 0.0f;
             corr_acc = (row_ok && arg == yy) ? 1 : 0;
             if (row_ok && rank == 0) p.pred[row] = arg;
@@ -702,7 +706,7 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     p.w2_stride = a.w2_stride; p.b2_stride = a.b2_stride; p.b1_stride = a.b1_stride;
     p.b1 = a.b1; p.b2 = a.b2; p.y = a.y; p.pred = a.pred; p.dz = a.dz; p.A_out = a.A_out; p.dH_out = a.dH_out;
     p.drop = a.drop; p.training = a.training;
-    p.partials = a.partials; p.ticket = a.ticket; p.record = a.record;
+    p.partials = a.partials; p.ticket = a.ticket; p.record = a.record; p.bad_target = a.bad_target;
 
     CUtensorMap mx, mw1, mw2;
     // X box: all BM rows of the slab -- every CTA of a cluster loads the whole tile for itself

@@ -61,13 +61,15 @@ struct HeadArgs {
     HeadPartial *partials;
     unsigned int *ticket;
     ts_batch_record *record;
+    uint32_t *bad_target;  // optional host-visible word: set to row + 1 when a target lies outside [0, C) (e.g. ignore_index)
 };
 int launch_head(const HeadArgs &a, int sm_count, cudaStream_t st);
 
 // Tensor-core head (bf16 mode, wide hidden layers): softmax / NLL / argmax / dZ from the logits GEMM's output, and the
 // fold of the transposed dW_last partials + db_last into `grads` (the contractions themselves are tc_gemm launches).
 int launch_logits_head(const float *Z, const float *bias, const int64_t *y, int64_t B, int C, int64_t *pred, float *dz,
-                       __nv_bfloat16 *dzb, HeadPartial *partials, unsigned int *ticket, ts_batch_record *record, cudaStream_t st);
+                       __nv_bfloat16 *dzb, HeadPartial *partials, unsigned int *ticket, ts_batch_record *record, uint32_t *bad_target,
+                       cudaStream_t st);
 int launch_wlast_finish(const float *wt, int64_t split_stride, int splits, int K, int C, const float *dz, int64_t B, float *gw,
                         float *gb, cudaStream_t st);
 
@@ -208,6 +210,7 @@ struct FusedMlpArgs {
     HeadPartial *partials;
     unsigned int *ticket;
     ts_batch_record *record;
+    uint32_t *bad_target;       // optional host-visible word, as in HeadArgs
 };
 // ---------------------------------------------------------------- single-kernel fit step for small batches (step_kernel.cu)
 struct FitStepArgs {
@@ -224,6 +227,7 @@ struct FitStepArgs {
     ts_batch_record *record;
     int64_t off_w1, off_b1, off_w2, off_b2, sh_w1, sh_w2;
     OptArgs opt;                // flat buffers, tensor table (nsplit 0: gradients final in `grads`) and this update's hyper-parameters
+    uint32_t *bad_target;       // optional host-visible word, as in HeadArgs
     unsigned int *flag;         // device counter the compute cluster raises by `ns` per step; the updater CTAs wait for flag_target
     unsigned int flag_target;
     int n_chunks, sm_count;

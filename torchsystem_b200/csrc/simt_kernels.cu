@@ -191,7 +191,10 @@ __global__ void __launch_bounds__(256) head_kernel(HeadArgs p) {
         for (int c = 0; c < MAXC; ++c)
             if (c == yy) zy = z[c];
         float row_loss = lse - zy;
-        if (yy < 0 || yy >= C) row_loss = __int_as_float(0x7fc00000);  // target outside [0,C): poison the loss
+        if (yy < 0 || yy >= C) {                                       // target outside [0,C): poison the loss, tell the host
+            row_loss = __int_as_float(0x7fc00000);
+            if (lane == 0 && p.bad_target != nullptr) *reinterpret_cast<volatile uint32_t *>(p.bad_target) = (uint32_t)r + 1u;
+        }
         loss_acc += row_loss;
         corr_acc += (arg == yy);
         if (lane == 0) p.pred[r] = arg;
@@ -328,7 +331,8 @@ __device__ __forceinline__ uint32_t pack2_bf16(float a, float b) {
 __global__ void __launch_bounds__(256) logits_head_kernel(const float *__restrict__ Z, const float *__restrict__ bias,
                                                           const int64_t *__restrict__ y, int64_t B, int C, int64_t *__restrict__ pred,
                                                           float *__restrict__ dz, __nv_bfloat16 *__restrict__ dzb,
-                                                          HeadPartial *partials, unsigned int *ticket, ts_batch_record *record) {
+                                                          HeadPartial *partials, unsigned int *ticket, ts_batch_record *record,
+                                                          uint32_t *bad_target) {
     __shared__ float s_loss[8];
     __shared__ int s_corr[8];
     __shared__ bool s_last;
@@ -364,7 +368,10 @@ __global__ void __launch_bounds__(256) logits_head_kernel(const float *__restric
         for (int c = 0; c < 16; ++c)
             if (c == yy) zy = z[c];
         row_loss = lse - zy;
-        if (yy < 0 || yy >= C) row_loss = __int_as_float(0x7fc00000);   // target outside [0,C): poison the loss
+        if (yy < 0 || yy >= C) {                                        // target outside [0,C): poison the loss, tell the host
+            row_loss = __int_as_float(0x7fc00000);
+            if (bad_target != nullptr) *reinterpret_cast<volatile uint32_t *>(bad_target) = (uint32_t)r + 1u;
+        }
         corr = (arg == yy);
         pred[r] = arg;
         if (dz != nullptr) {
@@ -416,12 +423,13 @@ __global__ void __launch_bounds__(256) logits_head_kernel(const float *__restric
 }
 
 int launch_logits_head(const float *Z, const float *bias, const int64_t *y, int64_t B, int C, int64_t *pred, float *dz,
-                       __nv_bfloat16 *dzb, HeadPartial *partials, unsigned int *ticket, ts_batch_record *record, cudaStream_t st) {
+                       __nv_bfloat16 *dzb, HeadPartial *partials, unsigned int *ticket, ts_batch_record *record, uint32_t *bad_target,
+                       cudaStream_t st) {
     const int64_t blocks = (B + 255) / 256;
     TS_REQUIRE(blocks <= kMaxHeadBlocks, TS_E_TOO_LARGE, "batch %lld needs %lld head blocks, more than %d", (long long)B,
                (long long)blocks, kMaxHeadBlocks);
     TS_CUDA_CHECK(launch_pdl(logits_head_kernel, dim3((unsigned)blocks), dim3(256), 0, st, 1, Z, bias, y, B, C, pred, dz, dzb, partials,
-                             ticket, record));
+                             ticket, record, bad_target));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }

@@ -56,6 +56,7 @@ struct StepParams {
     int64_t off_w1, off_b1, off_w2, off_b2;       // element offsets in the flat buffers
     int64_t sh_w1, sh_w2;                         // element offsets in the bf16 shadow buffer
     OptArgs opt;                                  // flat buffers, tensor table (gradients final in `grads`) + hyper-parameters
+    uint32_t *bad_target;
     unsigned int *flag;                           // monotonic counter: += ns per step once the gradients are in `grads`
     unsigned int flag_target;
     int n_chunks;                                 // 1024-element chunks of the flat buffers
@@ -470,7 +471,10 @@ fit_step_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant
             for (int c = 0; c < CP; ++c)
                 if (c == yy) zy = z[c];
             float row_loss = lse - zy;
-            if (yy < 0 || yy >= p.C) row_loss = __int_as_float(0x7fc00000);
+            if (yy < 0 || yy >= p.C) {                       // target outside [0, C): poison the loss, tell the host
+                row_loss = __int_as_float(0x7fc00000);
+                if (row_ok && rank == 0 && p.bad_target != nullptr) *reinterpret_cast<volatile uint32_t *>(p.bad_target) = (uint32_t)row + 1u;
+            }
             loss_acc = row_ok ? row_loss : 0.0f;
             corr_acc = (row_ok && arg == yy) ? 1 : 0;
             if (row_ok && rank == 0) p.pred[row] = arg;
@@ -643,7 +647,7 @@ int launch_fit_step(const FitStepArgs &a, cudaStream_t st) {
     p.off_w1 = a.off_w1; p.off_b1 = a.off_b1; p.off_w2 = a.off_w2; p.off_b2 = a.off_b2; p.sh_w1 = a.sh_w1; p.sh_w2 = a.sh_w2;
     p.opt = a.opt;
     TS_REQUIRE(p.opt.params && p.opt.grads && p.opt.shadow && p.opt.chunk_tensor && a.flag, TS_E_INVALID, "single-kernel step: buffers missing");
-    p.flag = a.flag; p.flag_target = a.flag_target; p.n_chunks = a.n_chunks;
+    p.flag = a.flag; p.flag_target = a.flag_target; p.n_chunks = a.n_chunks; p.bad_target = a.bad_target;
     // updater CTAs: one per SM next to the compute cluster (every CTA of the launch reserves the same ~200 KB of shared
     // memory, so they land on distinct SMs and all of them are resident: the compute cluster never waits for an SM)
     int upd_clusters = (a.sm_count - 16) / p.ns - 1;

@@ -32,6 +32,7 @@ class B200Metrics:
         self.log_every = log_every
         self.state = torch.zeros(4, dtype=torch.int64, device=dev)    # ts_metrics_state (32 bytes)
         self._run = None        # (engine, first_slot, count) of records noted but not folded in yet
+        self._engines = []      # engines whose records were seen (their status word is checked in compute)
         self._dp = DataParallel(process_group)
 
     def _stream(self):
@@ -48,6 +49,8 @@ class B200Metrics:
         tag = getattr(loss, '_ts_record', None)
         if tag is not None:
             engine, slot = tag
+            if engine not in self._engines:
+                self._engines.append(engine)
             run = self._run
             if run is not None and run[0] is engine and (run[1] + run[2]) % RING == slot and run[2] < RING // 2:
                 self._run = (engine, run[1], run[2] + 1)
@@ -67,6 +70,8 @@ class B200Metrics:
         self._flush()
         out = _lib.MetricsState()
         check(lib.ts_metrics_read(self.state.data_ptr(), out, self._stream()), 'ts_metrics_read')
+        for engine in self._engines:       # the read above synchronised: a target outside [0, classes) is known by now
+            check(lib.ts_mlp_status(engine.handle), 'ts_mlp_status')
         return self._dp.reduce_metrics(out.loss_sum, out.n_batches, out.n_correct, out.n_total, self.device)
 
     def compute(self) -> dict[str, Tensor]:

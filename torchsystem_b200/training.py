@@ -1,7 +1,7 @@
 """The `iterate` / `train` / `validate` handlers and their events, for running where the reference is not
 installed (the GPU box). Same names, arguments and event flow as
 /root/reference/examples/tinysys/tinysys/services/training.py:15-63 -- which itself runs unmodified against this
-package's B200Classifier / B200Metrics / loaders (tests/test_dropin_reference.py)."""
+package's protocol classes (tests/test_host_logic.py::test_handlers_trace_equals_unmodified_reference_handlers)."""
 from __future__ import annotations
 
 from typing import Any, Sequence
