@@ -473,6 +473,10 @@ def main():
         'colsum': BATCH * H * esz,
         'dw_gemm': BATCH * H * esz + BATCH * D * esz + H * D * 4,
         'optimizer': sum(DIMS[i] * DIMS[i + 1] + DIMS[i + 1] for i in range(2)) * (12 if args.optimizer == 'sgd' else 28),
+        # dW1 GEMM + in-cluster reduce + update: dH + x (bf16) read once, W1 master read + written, grads + bf16 shadow written,
+        # optimizer moments read + written (Adam), the per-slab partials of the small tensors
+        'dw_gemm_update': BATCH * H * 2 + BATCH * D * 2 + H * D * ((8 if args.optimizer == 'sgd' else 24) + 4 + 2)
+                          + (BATCH // 128) * (DIMS[2] * H + H + DIMS[2]) * 4,
         # fused forward + head + dH: x (bf16 copy) + W1 + dH out + pred/target + per-slab gradient partials
         'fused_fwd_head': BATCH * D * 2 + H * D * 2 + BATCH * H * 2 + BATCH * 16 + (BATCH // 128) * (DIMS[2] * H + H + DIMS[2]) * 4,
     }

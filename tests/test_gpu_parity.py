@@ -310,3 +310,29 @@ def test_uint8_inputs_reproduce_the_host_transform(precision, tol):
         out_model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
                                    device='cuda:0', max_batch=B)
         out_model.fit(xu[:B].cuda(), y[:B].cuda())        # uint8 without a normalisation table: loud
+
+
+@pytest.mark.parametrize('precision,B', [('f32', 64), ('bf16', 64), ('bf16', 1024)])
+def test_ignore_index_targets_are_rejected_loudly(precision, B):
+    """CrossEntropyLoss() carries ignore_index = -100 (examples/tinysys/main.py:61); the engine does not implement it, and says
+    so: the batch's loss is NaN, metrics.compute() raises after its synchronisation, and so does the next fit / evaluate, until
+    the status is cleared. Covers the SIMT head, the single-kernel step (64 rows, bf16) and the fused kernel (1024 rows)."""
+    from torchsystem_b200 import B200Metrics, _lib
+    dims = [784, 256, 10]
+    x, y = synthetic(B, seed=3)
+    model, _ = build_model(dims, 0.0, 'relu', 'sgd', 0.05, seeded_init(dims, bf16=precision == 'bf16'), precision, max_batch=B)
+    metrics = B200Metrics(device='cuda:0', log_every=0)
+    yc = y.cuda().clone()
+    p, l = model.fit(x.cuda(), yc)
+    metrics.update(1, l, p, yc)
+    assert np.isfinite(metrics.compute()['loss'].item())
+    yc[B // 2] = -100
+    p, l = model.fit(x.cuda(), yc)
+    metrics.update(2, l, p, yc)
+    assert np.isnan(l.item())                              # .item() synchronises: the status word is written by now
+    with pytest.raises(_lib.TsError, match='ignore_index'):
+        metrics.compute()
+    with pytest.raises(_lib.TsError, match=f'row {B // 2}'):
+        model.evaluate(x.cuda(), y.cuda())
+    _lib.check(_lib.lib.ts_mlp_clear_status(model.engine.handle))
+    model.evaluate(x.cuda(), y.cuda())

@@ -52,6 +52,7 @@ PROTOTYPES = {
     'ts_mlp_shadow_elems': (C.c_int64, [C.c_void_p]),
     'ts_dp_bind_nvls': (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.POINTER(C.c_void_p)]),
+    'ts_dp_nvls_second_shadow': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p]),
     'ts_mlp_workspace_bytes': (C.c_int64, [C.c_void_p, C.c_int64]),
     'ts_mlp_set_workspace': (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),
     'ts_mlp_sync_weights': (C.c_int32, [C.c_void_p, C.c_void_p]),

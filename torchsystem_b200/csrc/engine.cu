@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <atomic>
 #include <cstring>
 #include <mutex>
@@ -28,9 +29,9 @@ void set_error(const char *fmt, ...) {
 static inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
 // ---- optional per-kernel timing: CUDA events recorded on the launching stream around each launch.
-enum { K_CAST = 0, K_FWD_GEMM, K_HEAD, K_HEAD_WGRAD, K_COLSUM, K_DW_GEMM, K_DX_GEMM, K_OPT, K_FUSED, K_STEP, K_COUNT };
-static const char *const kKindNames[K_COUNT] = {"cast_bf16", "fwd_gemm", "head", "head_wgrad", "colsum",
-                                                "dw_gemm",   "dx_gemm",  "optimizer", "fused_fwd_head", "fit_step_small"};
+enum { K_CAST = 0, K_FWD_GEMM, K_HEAD, K_HEAD_WGRAD, K_COLSUM, K_DW_GEMM, K_DX_GEMM, K_OPT, K_FUSED, K_STEP, K_WGRAD_UPD, K_COUNT };
+static const char *const kKindNames[K_COUNT] = {"cast_bf16", "fwd_gemm", "head", "head_wgrad", "colsum", "dw_gemm",
+                                                "dx_gemm",   "optimizer", "fused_fwd_head", "fit_step_small", "dw_gemm_update"};
 struct ProfPair { int kind; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfPair> g_prof;
@@ -65,6 +66,7 @@ struct ts_mlp {
     cudaEvent_t *ov_events = nullptr;   // per-call (ts_fit_backward_overlap): event of layer l recorded once its gradients are enqueued
     int32_t *ov_final = nullptr;        // per-call out: gradient tensor t is final in `grads` when its layer's event fires
     unsigned int step_flag = 0;   // value of the single-kernel step's gradient-ready counter after the launches so far
+    int wgrad_update = 1;         // fused path: dW1 GEMM, split-K reduce and optimizer update in one kernel (TSB200_WGRAD_UPDATE=0: off)
     int step_kernel = 1;          // batches of at most 64 rows: the whole fit step in one kernel (TSB200_STEP_KERNEL=0: off)
     int inkernel_cast = -1;       // fp32 batches converted inside the fused kernel: 1 always, 0 never (cast kernel in front), -1 by batch size
 
@@ -127,6 +129,8 @@ struct ts_mlp {
     const float *grads_mc = nullptr;
     float *params_mc = nullptr;
     __nv_bfloat16 *shadow_mc = nullptr, *shadow_ext = nullptr;
+    __nv_bfloat16 *shadow_alt = nullptr, *shadow_mc_alt = nullptr;   // second set of bf16 shadows (ts_dp_nvls_second_shadow): the update of
+                                                                      // step s writes the set step s+1 reads, so it never races with this step's dX
 
     int hidden_layers() const { return n_layers - 1; }
     int classes() const { return dims[n_layers]; }
@@ -176,8 +180,8 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
     if (m->prec == TS_PREC_BF16) {
         m->x_bf16 = (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2);
         m->x_bf16_alt = m->fused ? (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2) : nullptr;
-        m->shadow = (__nv_bfloat16 *)c.take(m->shadow_total * 2);
-        if (m->shadow_ext) m->shadow = m->shadow_ext;      // NVLS data parallel keeps the shadows in symmetric memory
+        __nv_bfloat16 *ws_shadow = (__nv_bfloat16 *)c.take(m->shadow_total * 2);
+        if (!m->shadow_ext) m->shadow = ws_shadow;         // NVLS data parallel keeps the shadows in symmetric memory (m->shadow set at bind)
     }
     if (m->tc_head) {
         m->zbuf = (float *)c.take(Bm * 16 * 4);
@@ -560,6 +564,7 @@ int exchange_layer(ts_mlp *m, int l, const int *nsplit, bool first_of_step, cuda
     fill_update(m, o, first_of_step);
     o.params_mc = m->params_mc;
     o.shadow_mc = m->prec == TS_PREC_BF16 ? m->shadow_mc : nullptr;
+    if (m->shadow_alt) { o.shadow = m->shadow_alt; o.shadow_mc = m->shadow_mc_alt; }   // the set the NEXT step reads
     o.partial_depth = 4;
     o.chunk_begin = (int)(m->off[2 * l] / kChunk);
     const int64_t chunk_end = (m->off[2 * l + 1] + round_up(m->cnt[2 * l + 1], kChunk)) / kChunk;
@@ -641,6 +646,24 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     const bool in_kernel = m->fused && fused_grads_supported(m->dims[1], m->dims[2], B);   // the fused kernel already left them
     if (in_kernel) {
         nsplit[2] = nsplit[3] = nsplit[1] = (int)row_blocks;
+        if (m->wgrad_update && update && !dp && m->ov_events == nullptr && row_blocks <= kReduceAbove &&
+            wgrad_update_supported(m->dims[0], m->dims[1], B)) {
+            // one kernel for the rest of the step: dW1 with the batch split over a cluster, reduced through distributed shared
+            // memory and applied by the CTA holding the sum; its last cluster folds and updates the small tensors
+            WgradUpdateArgs w{};
+            w.dH = (const __nv_bfloat16 *)m->dh[0]; w.X = (const __nv_bfloat16 *)a0;
+            w.B = B; w.D = m->dims[0]; w.H = m->dims[1];
+            w.off_w1 = m->off[0]; w.sh_w1 = m->shadow_off[0];
+            w.small_chunk_begin = (int)(m->off[1] / kChunk);
+            w.small_chunks = (int)(m->n_chunks - m->off[1] / kChunk);
+            bool any_partial = false;
+            rc = fill_tensor_table(m, nsplit, w.opt, &any_partial, st);
+            if (rc) return rc;
+            w.opt.update = 1; w.opt.grad_scale = 1.0f;
+            fill_update(m, w.opt);
+            ProfScope ps(K_WGRAD_UPD, st);
+            return launch_wgrad_update(w, st);
+        }
     } else if (tc_head) {
         // nothing to launch here
     } else if (small) {
@@ -714,6 +737,13 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         }
         rc = mark_layer_ready(m, l, nsplit, st);
         if (rc) return rc;
+        // nvls overlap with two shadow sets: layer l's exchange can start as soon as dW_l and db_l are enqueued -- the dX GEMM
+        // below still reads W_l, but from this step's set, which the update does not write
+        const bool ov_early = ov && m->shadow_alt != nullptr;
+        if (ov_early) {
+            rc = exchange_layer(m, l, nsplit, false, st);
+            if (rc) return rc;
+        }
         if (l > 0) {   // dH_{l-1} = (dH_l W_l) * act'(layer l-1) * keep/(1-p)
             const DropoutSpec ds = drop_spec(m, masks, seed, l - 1, true);
             ProfScope ps(K_DX_GEMM, st);
@@ -745,7 +775,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
             if (rc) return rc;
             cur ^= 1;
         }
-        if (ov) {   // layer l: dW_l and db_l are enqueued, and so is the dX GEMM above, the last reader of W_l in this step
+        if (ov && !ov_early) {   // one shadow set: wait until the dX GEMM above, the last reader of W_l in this step, is enqueued
             rc = exchange_layer(m, l, nsplit, false, st);
             if (rc) return rc;
         }
@@ -753,6 +783,10 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     if (ov) {       // the next forward pass reads every parameter: the compute stream waits for the last exchange
         TS_CUDA_CHECK(cudaEventRecord(m->dp_ev_done, m->dp_stream));
         TS_CUDA_CHECK(cudaStreamWaitEvent(st, m->dp_ev_done, 0));
+        if (m->shadow_alt) {   // the set just written becomes the one the next step reads
+            std::swap(m->shadow, m->shadow_alt);
+            std::swap(m->shadow_mc, m->shadow_mc_alt);
+        }
         return TS_OK;
     }
     if (!dp) return run_optimizer(m, nsplit, update, 1.0f, st);
@@ -802,6 +836,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     m->prec = precision; m->device = device; m->sm_count = sms; m->bwd_sms = sms;
     if (const char *e = getenv("TSB200_INKERNEL_CAST")) m->inkernel_cast = atoi(e) != 0 ? 1 : 0;
     if (const char *e = getenv("TSB200_STEP_KERNEL")) m->step_kernel = atoi(e) != 0 ? 1 : 0;
+    if (const char *e = getenv("TSB200_WGRAD_UPDATE")) m->wgrad_update = atoi(e) != 0 ? 1 : 0;
     m->n_tensors = 2 * m->n_layers;
     int64_t o = 0, so = 0;
     for (int l = 0; l < m->n_layers; ++l) {
@@ -975,6 +1010,15 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
     return ensure_dp_error_word(m);
 }
 
+int32_t ts_dp_nvls_second_shadow(ts_mlp *m, void *shadow2_local, void *shadow2_mc) {
+    TS_REQUIRE(m && shadow2_local && shadow2_mc, TS_E_INVALID, "null argument");
+    TS_REQUIRE(m->nvls && m->shadow_ext, TS_E_STATE, "call ts_dp_bind_nvls (bf16 mode) first");
+    TS_REQUIRE(((uintptr_t)shadow2_local % 256) == 0 && ((uintptr_t)shadow2_mc % 256) == 0, TS_E_INVALID, "buffers must be 256-byte aligned");
+    m->shadow_alt = (__nv_bfloat16 *)shadow2_local;
+    m->shadow_mc_alt = (__nv_bfloat16 *)shadow2_mc;
+    return TS_OK;
+}
+
 int64_t ts_mlp_workspace_bytes(const ts_mlp *m, int64_t max_batch) {
     if (!m || max_batch < 1) { set_error("ts_mlp_workspace_bytes: bad argument"); return TS_E_INVALID; }
     ts_mlp tmp = *m;   // carve() writes pointers; measure on a copy
@@ -1017,10 +1061,13 @@ int32_t ts_mlp_sync_weights(ts_mlp *m, void *stream) {
     if (m->prec != TS_PREC_BF16) return TS_OK;
     TS_REQUIRE(m->params && m->ws_set, TS_E_STATE, "bind parameters and workspace before ts_mlp_sync_weights");
     TS_CUDA_CHECK(cudaSetDevice(m->device));
-    TS_CUDA_CHECK(cudaMemsetAsync(m->shadow, 0, (size_t)m->shadow_total * 2, (cudaStream_t)stream));   // padded class rows stay zero
-    for (int l = 0; l < m->n_layers; ++l) {
-        int rc = launch_cast_bf16(m->params + m->off[2 * l], m->shadow + m->shadow_off[l], m->cnt[2 * l], (cudaStream_t)stream);
-        if (rc) return rc;
+    for (__nv_bfloat16 *set : {m->shadow, m->shadow_alt}) {
+        if (set == nullptr) continue;
+        TS_CUDA_CHECK(cudaMemsetAsync(set, 0, (size_t)m->shadow_total * 2, (cudaStream_t)stream));   // padded class rows stay zero
+        for (int l = 0; l < m->n_layers; ++l) {
+            int rc = launch_cast_bf16(m->params + m->off[2 * l], set + m->shadow_off[l], m->cnt[2 * l], (cudaStream_t)stream);
+            if (rc) return rc;
+        }
     }
     return TS_OK;
 }

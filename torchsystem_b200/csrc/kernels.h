@@ -236,6 +236,19 @@ bool fit_step_supported(int D, int H, int C, int64_t B);
 int launch_fit_step(const FitStepArgs &a, cudaStream_t st);
 int read_step_trace(unsigned long long *out_host);
 
+// ---------------------------------------------------------------- dW1 = dH^T X + optimizer update in one kernel (wgrad_update.cu)
+struct WgradUpdateArgs {
+    const __nv_bfloat16 *dH;    // [B, H] bf16, written by the fused kernel
+    const __nv_bfloat16 *X;     // [B, D] bf16 inputs
+    int64_t B;
+    int D, H;
+    int64_t off_w1, sh_w1;      // element offsets of W1 in the flat buffers / the bf16 shadow buffer
+    int small_chunk_begin, small_chunks;   // the 1024-element chunks of the remaining tensors (b1, W2, b2)
+    OptArgs opt;                // flat buffers, tensor table (row-block partials of the remaining tensors), hyper-parameters
+};
+bool wgrad_update_supported(int D, int H, int64_t B);
+int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st);
+
 bool fused_mlp_supported(int D, int H, int C);
 inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }
 int fused_cluster_size(int64_t B, int H, int sm_count);   // CTAs per 128-row slab the launcher will use

@@ -1,0 +1,322 @@
+// dW1 = dH^T X and the optimizer update of W1 in one kernel, for the one-hidden-layer fused path at training batches
+// (classifier.py:31-34: backward + optimizer.step). The batch is the contraction, so it is split over the CTAs of a
+// thread-block cluster; what used to be split-K partials in global memory, folded by a separate optimizer launch, is now
+//
+//   main loop   every CTA of the cluster (rank z) contracts its batch rows [z * k_chunk, ...) of one 128 x 128 tile of dW1:
+//               tcgen05.mma, dH and X tiles by TMA as MN-major operands (no transposed copy), accumulator in TMEM
+//   reduce      the accumulators go to shared memory, one cluster barrier, then rank z sums rows [z * 128/S, ...) of the tile over
+//               all S CTAs through distributed shared memory, in rank order (bit-reproducible)
+//   update      SGD / Adam (opt_math.cuh) on those elements: parameters and moments were fetched into registers while the
+//               main loop ran; the new master weights, moments, `grads` and the bf16 shadow go straight out
+//
+// One more cluster of the same launch does what is left of the optimizer kernel: it folds the per-slab partials of W2, b1 and
+// b2 that fused_mlp.cu produced and updates them. No gradient of W1 ever reaches global memory except as `param.grad`.
+#include <cstdlib>
+
+#include "opt_math.cuh"
+#include "tc_common.cuh"
+
+namespace tsb {
+
+using namespace tc;
+
+namespace {
+
+constexpr int kThreads = 352;     // warp 0: dH producer, 1: MMA issuer + TMEM owner, 2: X producer, 3..10: epilogue / reduce / update
+constexpr int kEpiThreads = 256;
+constexpr int kStages = 5;        // 32 KiB each
+constexpr int TN = 128;           // features per tile
+constexpr int BK = 64;            // batch rows per pipeline stage
+constexpr int kMaxOwn = 4;        // float4 quads of the tile one epilogue thread reduces and updates (cluster of 4: 4, of 8: 2)
+
+struct WgParams {
+    int H, D;
+    int64_t B;
+    int S;                        // cluster size = number of batch splits
+    int tiles_n, n_tiles;         // feature tiles per hidden-row tile; tiles in all
+    int kblocks, kblocks_per_split;
+    uint32_t idesc;
+    int64_t off_w1, sh_w1;
+    int small_chunk_begin, small_chunks;   // 1024-element chunks of the other tensors (b1, W2, b2), folded by the last cluster
+    OptArgs opt;
+};
+
+__device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;" ::: "memory"); }
+__device__ __forceinline__ float4 ld_cluster_v4(uint32_t local_saddr, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_saddr), "r"(rank));
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(remote) : "memory");
+    return v;
+}
+
+// staging of one accumulator tile: [128 rows][32 chunks of 16 B], chunk index XOR-swizzled by the row so that both the
+// row-per-lane writes and the row-contiguous reads are free of bank conflicts
+__device__ __forceinline__ uint32_t acc_off(int row, int chunk) { return (uint32_t)row * 512u + ((uint32_t)(chunk ^ (row & 7)) << 4); }
+
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const WgParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages];
+    __shared__ __align__(8) uint64_t acc_full_bar;
+    __shared__ uint32_t tmem_base_slot;
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+    const int S = p.S;
+    const int cluster_id = (int)blockIdx.x / S;
+    const uint32_t rank = S > 1 ? cluster_rank() : 0u;
+    const OptArgs &o = p.opt;
+
+    if (cluster_id >= p.n_tiles) {
+        // ===================== the other tensors: per-slab partials from the fused kernel -> sum -> update =====================
+        float4 *slots = reinterpret_cast<float4 *>((reinterpret_cast<uintptr_t>(smem_raw) + 15) & ~(uintptr_t)15);
+        pdl_launch_dependents();
+        pdl_wait();
+        if (threadIdx.x >= 256) return;
+        for (int c = (int)rank; c < p.small_chunks; c += S) {
+            const int chunk = p.small_chunk_begin + c;
+            const int tix = o.chunk_tensor[chunk];
+            if (tix < 0) continue;
+            const TensorDesc d = o.t[tix];
+            const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+            const int64_t j0 = i0 - d.offset;
+            if (j0 >= d.count) continue;
+            const int n = (int)min((int64_t)4, d.count - j0);
+            float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            if (d.nsplit > 0) {
+                sum_partials(o.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, o.partial_depth);
+                if (n == 4) *reinterpret_cast<float4 *>(o.grads + i0) = make_float4(g[0], g[1], g[2], g[3]);
+                else for (int e = 0; e < n; ++e) o.grads[i0 + e] = g[e];
+            } else {
+                const float4 t = *reinterpret_cast<const float4 *>(o.grads + i0);
+                g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
+            }
+            apply_update(o, d, i0, j0, n, g);
+        }
+        return;
+    }
+
+    uint8_t *tiles = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t a_bytes = BM * BK * 2, b_bytes = TN * BK * 2, stage_bytes = a_bytes + b_bytes;
+    const int tm = cluster_id / p.tiles_n, tn = cluster_id - tm * p.tiles_n;
+    const int m0 = tm * BM, n0 = tn * TN;
+    const int kb_begin = (int)rank * p.kblocks_per_split;
+    const int kb_end = min(p.kblocks, kb_begin + p.kblocks_per_split);
+    const bool has_k = kb_begin < kb_end;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&acc_full_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_b)) : "memory");
+    }
+    if (warp == 1) tmem_alloc(&tmem_base_slot, TN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+    pdl_launch_dependents();
+    pdl_wait();          // dH and the bf16 inputs were written by the kernel in front
+
+    if (warp == 0) {
+        // ===================== TMA producer: dH tile [BK batch rows][128 hidden units], two 64-unit boxes =====================
+        int s = 0;
+        uint32_t phase = 0;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+            if (elect_one()) {
+                mbar_wait(&empty_bar[s], phase ^ 1);
+                uint8_t *sa = tiles + (size_t)s * stage_bytes;
+                mbar_expect_tx(&full_bar[s], a_bytes);
+                tma_load_2d(&tma_a, &full_bar[s], sa, m0, kb * BK);
+                tma_load_2d(&tma_a, &full_bar[s], sa + (size_t)BK * 128, m0 + 64, kb * BK);
+            }
+            __syncwarp();
+            if (++s == kStages) { s = 0; phase ^= 1; }
+        }
+    } else if (warp == 2) {
+        // ===================== TMA producer: X tile [BK batch rows][128 features] =====================
+        int s = 0;
+        uint32_t phase = 0;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+            if (elect_one()) {
+                mbar_wait(&empty_bar[s], phase ^ 1);
+                uint8_t *sb = tiles + (size_t)s * stage_bytes + a_bytes;
+                mbar_expect_tx(&full_bar[s], b_bytes);
+                tma_load_2d(&tma_b, &full_bar[s], sb, n0, kb * BK);
+                tma_load_2d(&tma_b, &full_bar[s], sb + (size_t)BK * 128, n0 + 64, kb * BK);
+            }
+            __syncwarp();
+            if (++s == kStages) { s = 0; phase ^= 1; }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        int s = 0;
+        uint32_t phase = 0;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+            if (elect_one()) {
+                mbar_wait(&full_bar[s], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(tiles + (size_t)s * stage_bytes), sb = sa + a_bytes;
+                const uint64_t adesc = make_desc(sa, TC_MAJOR_MN, BK), bdesc = make_desc(sb, TC_MAJOR_MN, BK);
+#pragma unroll
+                for (int k = 0; k < BK / UMMA_K; ++k)
+                    umma_bf16(tmem_base, adesc + (uint64_t)(k * ((UMMA_K * 128) >> 4)), bdesc + (uint64_t)(k * ((UMMA_K * 128) >> 4)), p.idesc,
+                              (kb > kb_begin || k > 0) ? 1u : 0u);
+                umma_commit(&empty_bar[s]);
+                if (kb == kb_end - 1) umma_commit(&acc_full_bar);
+            }
+            __syncwarp();
+            if (++s == kStages) { s = 0; phase ^= 1; }
+        }
+    } else {
+        // ===================== epilogue warps: state prefetch, accumulator -> shared memory, cluster reduce, update =====================
+        const int et = threadIdx.x - 96;                 // 0..255
+        const int q = warp & 3, half = (warp - 3) >> 2;  // TMEM lane quarter, which 64 of the tile's 128 feature columns
+        const int rows_own = BM / S;                     // tile rows this CTA reduces: [rank * rows_own, ...)
+        const int n_own = rows_own * (TN / 4) / kEpiThreads;   // quads per thread: 2 (S = 8) or 4 (S = 4)
+        const bool adam = o.kind != TS_OPT_SGD;
+        const bool use_m = adam || o.momentum != 0.0f;
+        const bool use_x = adam && o.amsgrad;
+        float4 w[kMaxOwn], m[kMaxOwn], v[kMaxOwn], x[kMaxOwn];
+        int64_t idx[kMaxOwn];
+#pragma unroll
+        for (int i = 0; i < kMaxOwn; ++i) {
+            idx[i] = -1;
+            w[i] = m[i] = v[i] = x[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (i < n_own) {
+                const int f = et + i * kEpiThreads;
+                const int row = m0 + (int)rank * rows_own + f / (TN / 4), col = n0 + (f % (TN / 4)) * 4;
+                if (row < p.H && col < p.D) {             // D is a multiple of 4: a quad is inside or outside as a whole
+                    idx[i] = (int64_t)row * p.D + col;
+                    w[i] = *reinterpret_cast<const float4 *>(o.params + p.off_w1 + idx[i]);
+                    if (use_m) m[i] = *reinterpret_cast<const float4 *>(o.exp_avg + p.off_w1 + idx[i]);
+                    if (adam) v[i] = *reinterpret_cast<const float4 *>(o.exp_avg_sq + p.off_w1 + idx[i]);
+                    if (use_x) x[i] = *reinterpret_cast<const float4 *>(o.max_exp_avg_sq + p.off_w1 + idx[i]);
+                }
+            }
+        }
+        // keep the loads on this side of the wait (the compiler would otherwise sink them next to their use)
+#pragma unroll
+        for (int i = 0; i < kMaxOwn; ++i) asm volatile("" ::"f"(w[i].x), "f"(m[i].x), "f"(v[i].x), "f"(x[i].x) : "memory");
+
+        // ---- this CTA's partial tile: TMEM -> shared memory (the pipeline stages are idle by now)
+        if (has_k) {
+            if (elect_one()) mbar_wait(&acc_full_bar, 0);
+            __syncwarp();
+            tc_fence_after();
+        }
+        const int r_local = q * 32 + lane;
+        const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t acc_s = smem_u32(tiles);
+#pragma unroll 1
+        for (int c0 = half * 64; c0 < half * 64 + 64; c0 += 32) {
+            float vv[32];
+            if (has_k) {
+                tmem_ld16(t_lane + (uint32_t)c0, *reinterpret_cast<float(*)[16]>(&vv[0]));
+                tmem_ld16(t_lane + (uint32_t)(c0 + 16), *reinterpret_cast<float(*)[16]>(&vv[16]));
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) vv[j] = 0.0f;       // no batch rows in this split: it contributes zeros
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(acc_s + acc_off(r_local, (c0 >> 2) + j)), "f"(vv[4 * j]),
+                             "f"(vv[4 * j + 1]), "f"(vv[4 * j + 2]), "f"(vv[4 * j + 3]) : "memory");
+        }
+        tc_fence_before();
+        if (S > 1) { cluster_arrive(); cluster_wait(); }      // every CTA's tile is in its shared memory
+        else named_bar_sync(1, kEpiThreads);
+
+        // ---- sum over the cluster in rank order, update, store
+#pragma unroll
+        for (int i = 0; i < kMaxOwn; ++i) {
+            if (i >= n_own) continue;
+            const int f = et + i * kEpiThreads;
+            const int row_t = (int)rank * rows_own + f / (TN / 4), chunk = f % (TN / 4);
+            const uint32_t addr = acc_s + acc_off(row_t, chunk);
+            float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            for (int r = 0; r < S; ++r) {
+                float4 t;
+                if (S > 1) t = ld_cluster_v4(addr, (uint32_t)r);
+                else asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(addr) : "memory");
+                g[0] += t.x; g[1] += t.y; g[2] += t.z; g[3] += t.w;
+            }
+            if (idx[i] < 0) continue;
+            float ww[4] = {w[i].x, w[i].y, w[i].z, w[i].w}, mm[4] = {m[i].x, m[i].y, m[i].z, m[i].w};
+            float vq[4] = {v[i].x, v[i].y, v[i].z, v[i].w}, xx[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) opt_update_element(o, g[e], ww[e], mm[e], vq[e], xx[e]);
+            const int64_t gi = p.off_w1 + idx[i];
+            *reinterpret_cast<float4 *>(o.params + gi) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+            *reinterpret_cast<float4 *>(o.grads + gi) = make_float4(g[0], g[1], g[2], g[3]);
+            if (use_m) *reinterpret_cast<float4 *>(o.exp_avg + gi) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+            if (adam) *reinterpret_cast<float4 *>(o.exp_avg_sq + gi) = make_float4(vq[0], vq[1], vq[2], vq[3]);
+            if (use_x) *reinterpret_cast<float4 *>(o.max_exp_avg_sq + gi) = make_float4(xx[0], xx[1], xx[2], xx[3]);
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(ww[0], ww[1]), hi = __floats2bfloat162_rn(ww[2], ww[3]);
+            uint2 pk;
+            pk.x = *reinterpret_cast<const uint32_t *>(&lo);
+            pk.y = *reinterpret_cast<const uint32_t *>(&hi);
+            *reinterpret_cast<uint2 *>(o.shadow + p.sh_w1 + idx[i]) = pk;
+        }
+    }
+    // the cluster barriers are cluster-wide: the producer / issuer warps take part too. Second barrier: nobody leaves while a
+    // peer may still be reading its tile.
+    __syncwarp();
+    if (S > 1) {
+        if (warp < 3) { cluster_arrive(); cluster_wait(); }
+        cluster_arrive();
+        cluster_wait();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TN);
+    }
+}
+
+}  // namespace
+
+bool wgrad_update_supported(int D, int H, int64_t B) { return (H == 128 || H == 256) && D % 8 == 0 && B >= 512; }
+
+int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st) {
+    TS_REQUIRE(wgrad_update_supported(a.D, a.H, a.B), TS_E_UNSUPPORTED, "dW1 + update kernel: unsupported shape D=%d H=%d B=%lld", a.D, a.H,
+               (long long)a.B);
+    WgParams p{};
+    p.H = a.H; p.D = a.D; p.B = a.B;
+    p.S = a.B >= 2048 ? 8 : 4;
+    p.tiles_n = (a.D + TN - 1) / TN;
+    p.n_tiles = (a.H / BM) * p.tiles_n;
+    p.kblocks = (int)((a.B + BK - 1) / BK);
+    p.kblocks_per_split = (p.kblocks + p.S - 1) / p.S;
+    p.idesc = make_idesc(BM, TN, TC_MAJOR_MN, TC_MAJOR_MN);
+    p.off_w1 = a.off_w1; p.sh_w1 = a.sh_w1;
+    p.small_chunk_begin = a.small_chunk_begin; p.small_chunks = a.small_chunks;
+    p.opt = a.opt;
+    TS_REQUIRE(p.opt.params && p.opt.grads && p.opt.shadow && p.opt.chunk_tensor, TS_E_INVALID, "dW1 + update kernel: buffers missing");
+    TS_REQUIRE(p.opt.params_mc == nullptr, TS_E_INVALID, "dW1 + update kernel: single-GPU path only");
+
+    CUtensorMap ma, mb;
+    int rc = get_map(a.dH, (uint64_t)a.H, (uint64_t)a.B, (uint64_t)a.H, 64, BK, &ma);
+    if (rc) return rc;
+    rc = get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, 64, BK, &mb);
+    if (rc) return rc;
+
+    const size_t smem = (size_t)kStages * (BM * BK * 2 + TN * BK * 2) + 1024;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    TS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!attr_set[dev & 63]) {
+        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        attr_set[dev & 63] = true;
+    }
+    const unsigned grid = (unsigned)((p.n_tiles + 1) * p.S);
+    TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel, dim3(grid), dim3(kThreads), smem, st, (unsigned)p.S, ma, mb, p));
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+}  // namespace tsb

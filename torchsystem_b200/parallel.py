@@ -124,6 +124,18 @@ def bind_nvls(engine, params, dp: DataParallel):
     fptrs = (C.c_void_p * world)(*[hf.buffer_ptrs[r] for r in range(world)])
     check(lib.ts_dp_bind_nvls(engine.handle, rank, world, gbuf.data_ptr(), hg.multicast_ptr, pbuf.data_ptr(), hp.multicast_ptr,
                               sbuf.data_ptr() if n_shadow else None, hs.multicast_ptr if n_shadow else None, fptrs), 'ts_dp_bind_nvls')
+    keep = []
+    if n_shadow and len(engine.spec.dims) > 3:
+        # nets on the layer-by-layer path: a second shadow set lets each layer's exchange start under its own dX GEMM
+        # (ts_dp_nvls_second_shadow; used when TSB200_NVLS_OVERLAP_SMS is set)
+        with torch.cuda.device(engine.index):
+            sbuf2 = symm.empty(n_shadow, dtype=torch.bfloat16, device=dev)
+            sbuf2.zero_()
+            hs2 = symm.rendezvous(sbuf2, group)
+            torch.cuda.synchronize(engine.index)
+        if hs2.multicast_ptr:
+            check(lib.ts_dp_nvls_second_shadow(engine.handle, sbuf2.data_ptr(), hs2.multicast_ptr), 'ts_dp_nvls_second_shadow')
+            keep = [sbuf2, hs2]
     engine.params, engine.grads = pbuf, gbuf
     for i, p in enumerate(params):
         o, n = engine.offsets[i], p.numel()
@@ -132,4 +144,4 @@ def bind_nvls(engine, params, dp: DataParallel):
     engine.sync_weights()
     torch.cuda.synchronize(engine.index)
     dist.barrier(group=dp.group)
-    return gbuf, pbuf, sbuf, flags, handles
+    return gbuf, pbuf, sbuf, flags, handles, keep
