@@ -273,6 +273,8 @@ int32_t ts_test_gemm_bf16(const void *A, int32_t a_major, int64_t lda, const voi
 int32_t ts_test_fused_trace(uint64_t *out /*HOST, 32 entries*/);
 /* The same for the single-kernel small-batch step (ts_fit_step on at most 64 rows, one hidden layer, bf16 mode). */
 int32_t ts_test_step_trace(uint64_t *out /*HOST, 32 entries*/);
+/* The same for the dW1 + update kernel of the fused training path (16 samples). */
+int32_t ts_test_wgrad_trace(uint64_t *out /*HOST, 16 entries*/);
 
 /* number of kernels this library has launched on the calling process so far (bench.py's gpu_launches) */
 int64_t ts_launch_count(void);

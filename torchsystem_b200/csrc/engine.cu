@@ -1199,6 +1199,12 @@ int32_t ts_test_fused_trace(uint64_t *out) {
     return read_fused_trace((unsigned long long *)out);
 }
 
+int32_t ts_test_wgrad_trace(uint64_t *out) {
+    TS_REQUIRE(out, TS_E_INVALID, "null argument");
+    TS_CUDA_CHECK(cudaDeviceSynchronize());
+    return read_wgrad_trace((unsigned long long *)out);
+}
+
 int32_t ts_test_step_trace(uint64_t *out) {
     TS_REQUIRE(out, TS_E_INVALID, "null argument");
     TS_CUDA_CHECK(cudaDeviceSynchronize());

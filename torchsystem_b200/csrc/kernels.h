@@ -248,6 +248,7 @@ struct WgradUpdateArgs {
 };
 bool wgrad_update_supported(int D, int H, int64_t B);
 int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st);
+int read_wgrad_trace(unsigned long long *out_host);   // 16 clock64 samples of CTA 0 of the last launch
 
 bool fused_mlp_supported(int D, int H, int C);
 inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }

@@ -27,7 +27,6 @@ constexpr int kEpiThreads = 256;
 constexpr int kStages = 5;        // 32 KiB each
 constexpr int TN = 128;           // features per tile
 constexpr int BK = 64;            // batch rows per pipeline stage
-constexpr int kMaxOwn = 4;        // float4 quads of the tile one epilogue thread reduces and updates (cluster of 4: 4, of 8: 2)
 
 struct WgParams {
     int H, D;
@@ -40,6 +39,10 @@ struct WgParams {
     int small_chunk_begin, small_chunks;   // 1024-element chunks of the other tensors (b1, W2, b2), folded by the last cluster
     OptArgs opt;
 };
+
+// clock64 trace of CTA 0 of the most recent launch (read back by the ts_test_wgrad_trace hook)
+__device__ unsigned long long g_wgrad_trace[16];
+#define WTRACE(i) do { if (blockIdx.x == 0) g_wgrad_trace[(i)] = clock64(); } while (0)
 
 __device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;" ::: "memory"); }
@@ -56,6 +59,7 @@ __device__ __forceinline__ float4 ld_cluster_v4(uint32_t local_saddr, uint32_t r
 // row-per-lane writes and the row-contiguous reads are free of bank conflicts
 __device__ __forceinline__ uint32_t acc_off(int row, int chunk) { return (uint32_t)row * 512u + ((uint32_t)(chunk ^ (row & 7)) << 4); }
 
+template <int S>      // cluster size = number of batch splits: 4 or 8
 __global__ void __launch_bounds__(kThreads, 1)
 wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const WgParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -64,9 +68,8 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     __shared__ uint32_t tmem_base_slot;
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
-    const int S = p.S;
     const int cluster_id = (int)blockIdx.x / S;
-    const uint32_t rank = S > 1 ? cluster_rank() : 0u;
+    const uint32_t rank = cluster_rank();
     const OptArgs &o = p.opt;
 
     if (cluster_id >= p.n_tiles) {
@@ -106,6 +109,7 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     const int kb_end = min(p.kblocks, kb_begin + p.kblocks_per_split);
     const bool has_k = kb_begin < kb_end;
 
+    if (threadIdx.x == 0) WTRACE(0);
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
         mbar_init(&acc_full_bar, 1);
@@ -120,6 +124,7 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     const uint32_t tmem_base = tmem_base_slot;
     pdl_launch_dependents();
     pdl_wait();          // dH and the bf16 inputs were written by the kernel in front
+    if (threadIdx.x == 0) WTRACE(1);
 
     if (warp == 0) {
         // ===================== TMA producer: dH tile [BK batch rows][128 hidden units], two 64-unit boxes =====================
@@ -167,6 +172,8 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                               (kb > kb_begin || k > 0) ? 1u : 0u);
                 umma_commit(&empty_bar[s]);
                 if (kb == kb_end - 1) umma_commit(&acc_full_bar);
+                if (kb == kb_begin) WTRACE(2);
+                if (kb == kb_end - 1) WTRACE(3);
             }
             __syncwarp();
             if (++s == kStages) { s = 0; phase ^= 1; }
@@ -175,18 +182,18 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         // ===================== epilogue warps: state prefetch, accumulator -> shared memory, cluster reduce, update =====================
         const int et = threadIdx.x - 96;                 // 0..255
         const int q = warp & 3, half = (warp - 3) >> 2;  // TMEM lane quarter, which 64 of the tile's 128 feature columns
-        const int rows_own = BM / S;                     // tile rows this CTA reduces: [rank * rows_own, ...)
-        const int n_own = rows_own * (TN / 4) / kEpiThreads;   // quads per thread: 2 (S = 8) or 4 (S = 4)
+        constexpr int rows_own = BM / S;                 // tile rows this CTA reduces: [rank * rows_own, ...)
+        constexpr int n_own = rows_own * (TN / 4) / kEpiThreads;   // quads per thread: 2 (S = 8) or 4 (S = 4)
         const bool adam = o.kind != TS_OPT_SGD;
         const bool use_m = adam || o.momentum != 0.0f;
         const bool use_x = adam && o.amsgrad;
-        float4 w[kMaxOwn], m[kMaxOwn], v[kMaxOwn], x[kMaxOwn];
-        int64_t idx[kMaxOwn];
+        float4 w[n_own], m[n_own], v[n_own], x[n_own];
+        int64_t idx[n_own];
 #pragma unroll
-        for (int i = 0; i < kMaxOwn; ++i) {
+        for (int i = 0; i < n_own; ++i) {
             idx[i] = -1;
             w[i] = m[i] = v[i] = x[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            if (i < n_own) {
+            {
                 const int f = et + i * kEpiThreads;
                 const int row = m0 + (int)rank * rows_own + f / (TN / 4), col = n0 + (f % (TN / 4)) * 4;
                 if (row < p.H && col < p.D) {             // D is a multiple of 4: a quad is inside or outside as a whole
@@ -200,7 +207,7 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         }
         // keep the loads on this side of the wait (the compiler would otherwise sink them next to their use)
 #pragma unroll
-        for (int i = 0; i < kMaxOwn; ++i) asm volatile("" ::"f"(w[i].x), "f"(m[i].x), "f"(v[i].x), "f"(x[i].x) : "memory");
+        for (int i = 0; i < n_own; ++i) asm volatile("" ::"f"(w[i].x), "f"(m[i].x), "f"(v[i].x), "f"(x[i].x) : "memory");
 
         // ---- this CTA's partial tile: TMEM -> shared memory (the pipeline stages are idle by now)
         if (has_k) {
@@ -208,6 +215,7 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             __syncwarp();
             tc_fence_after();
         }
+        if (et == 0) WTRACE(4);
         const int r_local = q * 32 + lane;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         const uint32_t acc_s = smem_u32(tiles);
@@ -227,23 +235,28 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                              "f"(vv[4 * j + 1]), "f"(vv[4 * j + 2]), "f"(vv[4 * j + 3]) : "memory");
         }
         tc_fence_before();
-        if (S > 1) { cluster_arrive(); cluster_wait(); }      // every CTA's tile is in its shared memory
-        else named_bar_sync(1, kEpiThreads);
+        if (et == 0) WTRACE(5);
+        cluster_arrive();                                     // every CTA's tile is in its shared memory
+        cluster_wait();
+        if (et == 0) WTRACE(6);
 
-        // ---- sum over the cluster in rank order, update, store
+        // ---- sum over the cluster in rank order, update, store. All remote loads of a thread are issued before the first
+        //      add: a distributed-shared-memory load takes a few hundred nanoseconds, and S of them in a dependent chain
+        //      were the longest phase of the kernel.
+        float4 part[n_own][S];
 #pragma unroll
-        for (int i = 0; i < kMaxOwn; ++i) {
-            if (i >= n_own) continue;
+        for (int i = 0; i < n_own; ++i) {
             const int f = et + i * kEpiThreads;
-            const int row_t = (int)rank * rows_own + f / (TN / 4), chunk = f % (TN / 4);
-            const uint32_t addr = acc_s + acc_off(row_t, chunk);
+            const uint32_t addr = acc_s + acc_off((int)rank * rows_own + f / (TN / 4), f % (TN / 4));
+#pragma unroll
+            for (int r = 0; r < S; ++r) part[i][r] = ld_cluster_v4(addr, (uint32_t)r);
+        }
+        if (et == 0) WTRACE(7);
+#pragma unroll
+        for (int i = 0; i < n_own; ++i) {
             float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-            for (int r = 0; r < S; ++r) {
-                float4 t;
-                if (S > 1) t = ld_cluster_v4(addr, (uint32_t)r);
-                else asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(addr) : "memory");
-                g[0] += t.x; g[1] += t.y; g[2] += t.z; g[3] += t.w;
-            }
+#pragma unroll
+            for (int r = 0; r < S; ++r) { g[0] += part[i][r].x; g[1] += part[i][r].y; g[2] += part[i][r].z; g[3] += part[i][r].w; }
             if (idx[i] < 0) continue;
             float ww[4] = {w[i].x, w[i].y, w[i].z, w[i].w}, mm[4] = {m[i].x, m[i].y, m[i].z, m[i].w};
             float vq[4] = {v[i].x, v[i].y, v[i].z, v[i].w}, xx[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
@@ -262,23 +275,28 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             *reinterpret_cast<uint2 *>(o.shadow + p.sh_w1 + idx[i]) = pk;
         }
     }
+    if (threadIdx.x == 96) WTRACE(8);
     // the cluster barriers are cluster-wide: the producer / issuer warps take part too. Second barrier: nobody leaves while a
     // peer may still be reading its tile.
     __syncwarp();
-    if (S > 1) {
-        if (warp < 3) { cluster_arrive(); cluster_wait(); }
-        cluster_arrive();
-        cluster_wait();
-    }
+    if (warp < 3) { cluster_arrive(); cluster_wait(); }
+    cluster_arrive();
+    cluster_wait();
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, TN);
     }
+    if (threadIdx.x == 0) WTRACE(9);
 }
 
 }  // namespace
+
+int read_wgrad_trace(unsigned long long *out_host) {
+    TS_CUDA_CHECK(cudaMemcpyFromSymbol(out_host, g_wgrad_trace, sizeof(unsigned long long) * 16));
+    return TS_OK;
+}
 
 bool wgrad_update_supported(int D, int H, int64_t B) { return (H == 128 || H == 256) && D % 8 == 0 && B >= 512; }
 
@@ -310,11 +328,13 @@ int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st) {
     int dev = 0;
     TS_CUDA_CHECK(cudaGetDevice(&dev));
     if (!attr_set[dev & 63]) {
-        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_set[dev & 63] = true;
     }
     const unsigned grid = (unsigned)((p.n_tiles + 1) * p.S);
-    TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel, dim3(grid), dim3(kThreads), smem, st, (unsigned)p.S, ma, mb, p));
+    if (p.S == 8) TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<8>, dim3(grid), dim3(kThreads), smem, st, 8u, ma, mb, p));
+    else TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<4>, dim3(grid), dim3(kThreads), smem, st, 4u, ma, mb, p));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
