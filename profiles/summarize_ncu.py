@@ -14,7 +14,7 @@ import sys
 from collections import OrderedDict
 
 KINDS = {'fused_mlp_kernel': 'fused_fwd_head', 'tc_gemm_kernel': 'dw_gemm', 'optimizer_kernel': 'optimizer',
-         'cast_bf16_kernel': 'cast_bf16'}
+         'cast_bf16_kernel': 'cast_bf16', 'wgrad_update_kernel': 'dw_gemm_update', 'fit_step_kernel': 'fit_step_small'}
 
 
 def rows(path):

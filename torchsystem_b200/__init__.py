@@ -7,5 +7,6 @@ from .metrics import B200Metrics
 from .loader import DeviceLoader, PinnedLoader
 from .lowering import lower_classifier
 from .modules import MLP
+from . import training
 
-__all__ = ['B200Classifier', 'B200Metrics', 'DeviceLoader', 'PinnedLoader', 'lower_classifier', 'MLP', 'TsError']
+__all__ = ['B200Classifier', 'B200Metrics', 'DeviceLoader', 'PinnedLoader', 'lower_classifier', 'MLP', 'TsError', 'training']
