@@ -410,3 +410,29 @@ def test_single_kernel_step_equals_multi_kernel_path(monkeypatch, kind):
         assert np.array_equal(pa, pb)
         assert la == pytest.approx(lb, rel=1e-5)
     assert_params_close(wa, wb, 1e-4, lr=1e-3, steps=steps, adam=kind != 'sgd_momentum_nesterov')
+
+
+@pytest.mark.parametrize('B,optimizer', [(32, 'adam'), (4096, 'sgd'), (4096, 'adam'), (12000, 'sgd')])
+def test_training_is_bit_reproducible(B, optimizer):
+    """Two runs from the same state give the same bits -- predictions, loss records, weights, optimizer moments -- for the
+    single-kernel step (32 rows), the fused kernel + cluster-reduced dW1 update (4096 rows) and the round-1 kernel pair behind
+    the on-chip input conversion (12000 rows). No floating-point atomics and fixed summation orders make this hold by design;
+    it is also the race check this pool allows (compute-sanitizer is closed here, profiles/r2_compute_sanitizer_closed.log):
+    an unsynchronised read of a tile, a stage or a peer CTA's shared memory would show up as run-to-run differences."""
+    dims, steps = [784, 256, 10], 6
+    x, y = synthetic(B * 2, seed=41)
+    init = seeded_init(dims, bf16=True)
+    outs = []
+    for _ in range(2):
+        model, net = build_model(dims, 0.1, 'relu', optimizer, 1e-3 if optimizer == 'adam' else 0.05, init, 'bf16', max_batch=B, seed=9)
+        got = []
+        for s in range(steps):
+            pr, l = model.fit(x[(s % 2) * B:(s % 2 + 1) * B].cuda(), y[(s % 2) * B:(s % 2 + 1) * B].cuda())
+            got += [pr.cpu(), l.cpu().clone()]
+        got += [q.detach().cpu().clone() for q in net.parameters()]
+        if optimizer == 'adam':
+            st = model.optimizer.state_dict()['state']
+            got += [st[0]['exp_avg'].cpu().clone(), st[0]['exp_avg_sq'].cpu().clone()]
+        outs.append(got)
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
