@@ -150,6 +150,11 @@ int32_t ts_mlp_sync_weights(ts_mlp *m, void *stream);
  *   predictions  [B] int64 out
  *   record       one ts_batch_record out (its .loss is the returned loss tensor)
  */
+/* Precondition on `inputs` in TS_PREC_BF16 mode: fp32 / uint8 batches are converted by a kernel that reads `inputs` BEFORE it
+ * waits for the kernel in front of it on `stream` (it overlaps that kernel, normally this library's previous update). The
+ * kernel that PRODUCED `inputs` must therefore not be the one immediately in front of this call on `stream`: have at least
+ * one other kernel or an event / stream synchronisation in between (loaders that prepare an epoch up front, or copy on
+ * another stream and hand over with an event, satisfy this). */
 int32_t ts_fit_step(ts_mlp *m, const void *inputs, int32_t inputs_dtype, const int64_t *targets, int64_t batch,
                     const uint8_t *const *masks /*HOST*/, uint64_t seed, int64_t *predictions,
                     ts_batch_record *record, void *stream);
