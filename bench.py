@@ -275,7 +275,7 @@ def dp_parity(torch, dist, dev, world, rank, precision, dp_mode):
     from torchsystem_b200 import B200Classifier, MLP
     tol = 1e-2 if precision == 'bf16' else 1e-5
     solo_group = dist.new_group([0])
-    per = 1024
+    per = 2048          # rows per rank: the size class of the headline (dW1 + update kernel on clusters of 8)
     g = torch.Generator(device=dev).manual_seed(4242)            # same data on every rank
     xg = torch.randn(3 * per * world, 1, 28, 28, generator=g, device=dev).bfloat16().float()
     teacher = torch.randn(784, 10, generator=g, device=dev)

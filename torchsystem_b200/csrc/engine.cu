@@ -646,7 +646,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     const bool in_kernel = m->fused && fused_grads_supported(m->dims[1], m->dims[2], B);   // the fused kernel already left them
     if (in_kernel) {
         nsplit[2] = nsplit[3] = nsplit[1] = (int)row_blocks;
-        if (m->wgrad_update && update && !dp && m->ov_events == nullptr && row_blocks <= kReduceAbove &&
+        if (m->wgrad_update && update && (!dp || !m->nvls) && m->ov_events == nullptr && row_blocks <= kReduceAbove &&
             wgrad_update_supported(m->dims[0], m->dims[1], B)) {
             // one kernel for the rest of the step: dW1 with the batch split over a cluster, reduced through distributed shared
             // memory and applied by the CTA holding the sum; its last cluster folds and updates the small tensors
@@ -659,8 +659,17 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
             bool any_partial = false;
             rc = fill_tensor_table(m, nsplit, w.opt, &any_partial, st);
             if (rc) return rc;
-            w.opt.update = 1; w.opt.grad_scale = 1.0f;
+            w.opt.update = 1; w.opt.grad_scale = dp ? 1.0f / (float)m->dp_world : 1.0f;
+            const int parity = (int)(m->step & 1);     // which of the two peer-visible gradient buffers this step uses
             fill_update(m, w.opt);
+            w.sm_count = m->sm_count;
+            w.dp.world = 1;
+            if (dp) {   // 'p2p' data parallel: the cross-rank gradient sum happens inside this kernel
+                w.dp.world = m->dp_world; w.dp.rank = m->dp_rank; w.dp.step = (uint32_t)m->step;
+                w.dp.timeout_ns = (unsigned long long)(m->dp_timeout_s * 1e9);
+                w.dp.err = m->dp_err_dev;
+                for (int r = 0; r < m->dp_world; ++r) { w.dp.grads[r] = m->dp_grads[parity][r]; w.dp.flags[r] = m->dp_flags[r]; }
+            }
             ProfScope ps(K_WGRAD_UPD, st);
             return launch_wgrad_update(w, st);
         }

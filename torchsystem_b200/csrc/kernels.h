@@ -154,6 +154,22 @@ int launch_metrics_accumulate(ts_metrics_state *state, const ts_batch_record *ri
 int launch_metrics_update_raw(ts_metrics_state *state, const float *loss, const int64_t *pred, const int64_t *tgt,
                               int64_t B, cudaStream_t st);
 
+// ---------------------------------------------------------------- dW1 = dH^T X + optimizer update in one kernel (wgrad_update.cu)
+struct WgradUpdateArgs {
+    const __nv_bfloat16 *dH;    // [B, H] bf16, written by the fused kernel
+    const __nv_bfloat16 *X;     // [B, D] bf16 inputs
+    int64_t B;
+    int D, H;
+    int64_t off_w1, sh_w1;      // element offsets of W1 in the flat buffers / the bf16 shadow buffer
+    int small_chunk_begin, small_chunks;   // the 1024-element chunks of the remaining tensors (b1, W2, b2)
+    OptArgs opt;                // flat buffers, tensor table (row-block partials of the remaining tensors), hyper-parameters
+    DpArgs dp;                  // world > 1: data parallel over peer mappings ('p2p'), gradient sum inside this kernel
+    int sm_count;
+};
+bool wgrad_update_supported(int D, int H, int64_t B);
+int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st);
+int read_wgrad_trace(unsigned long long *out_host);   // 16 clock64 samples of CTA 0 of the last launch
+
 }  // namespace tsb
 
 // ---------------------------------------------------------------- tcgen05 bf16 GEMM (precision mode BF16), tc_gemm.cu
@@ -235,20 +251,6 @@ struct FitStepArgs {
 bool fit_step_supported(int D, int H, int C, int64_t B);
 int launch_fit_step(const FitStepArgs &a, cudaStream_t st);
 int read_step_trace(unsigned long long *out_host);
-
-// ---------------------------------------------------------------- dW1 = dH^T X + optimizer update in one kernel (wgrad_update.cu)
-struct WgradUpdateArgs {
-    const __nv_bfloat16 *dH;    // [B, H] bf16, written by the fused kernel
-    const __nv_bfloat16 *X;     // [B, D] bf16 inputs
-    int64_t B;
-    int D, H;
-    int64_t off_w1, sh_w1;      // element offsets of W1 in the flat buffers / the bf16 shadow buffer
-    int small_chunk_begin, small_chunks;   // the 1024-element chunks of the remaining tensors (b1, W2, b2)
-    OptArgs opt;                // flat buffers, tensor table (row-block partials of the remaining tensors), hyper-parameters
-};
-bool wgrad_update_supported(int D, int H, int64_t B);
-int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st);
-int read_wgrad_trace(unsigned long long *out_host);   // 16 clock64 samples of CTA 0 of the last launch
 
 bool fused_mlp_supported(int D, int H, int C);
 inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }

@@ -106,4 +106,28 @@ __device__ __forceinline__ void sum_partials(const float *q, int64_t stride, int
 }
 
 
+
+// Wait until *flag has reached `value` (release/acquire at system scope: the flag is written by a peer GPU). The wait is
+// bounded by wall-clock time (dp.timeout_ns on %globaltimer, minutes by default like a collective library's watchdog, not
+// by a poll count: a peer may legitimately be seconds late, e.g. while rank 0 writes a checkpoint). On expiry the step
+// number goes into the host-visible error word and the caller skips its update; nothing traps, the context stays usable.
+__device__ __forceinline__ bool wait_for_flag(const uint32_t *flag, uint32_t value, const DpArgs &dp) {
+    unsigned long long t0 = 0;
+    for (uint32_t spins = 0;; ++spins) {
+        uint32_t seen;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
+        if ((int32_t)(seen - value) >= 0) return true;
+        __nanosleep(32);
+        if ((spins & 1023u) == 1023u) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > dp.timeout_ns) {
+                if (dp.err != nullptr) *reinterpret_cast<volatile uint32_t *>(dp.err) = dp.step ? dp.step : 1u;
+                return false;
+            }
+        }
+    }
+}
+
 }  // namespace tsb

@@ -11,6 +11,14 @@
 //
 // One more cluster of the same launch does what is left of the optimizer kernel: it folds the per-slab partials of W2, b1 and
 // b2 that fused_mlp.cu produced and updates them. No gradient of W1 ever reaches global memory except as `param.grad`.
+//
+// Data parallel (DP = true, dp_mode 'p2p'): the cross-rank gradient sum happens in the same launch. After the cluster reduce
+// every CTA stores its share of this rank's gradient into the rank's peer-visible buffer (NVLink / NVSwitch mappings of every
+// rank's buffer are in DpArgs); the last CTA of the grid to do so publishes "step s complete" into every rank's flag array
+// (st.release.sys), everybody waits until the local flag array shows step s for every rank (ld.acquire.sys, bounded by
+// wall-clock time), then re-reads ITS OWN quads from all ranks' buffers, sums them in rank order (bit-identical replicas),
+// scales by 1/world and updates. What the separate dp_optimizer_kernel launch cost (a kernel boundary, a fold of eight split
+// partials, a second pass over the optimizer state) is gone; what remains is the handshake and the remote reads.
 #include <cstdlib>
 
 #include "opt_math.cuh"
@@ -38,7 +46,30 @@ struct WgParams {
     int64_t off_w1, sh_w1;
     int small_chunk_begin, small_chunks;   // 1024-element chunks of the other tensors (b1, W2, b2), folded by the last cluster
     OptArgs opt;
+    DpArgs dp;                    // DP = true: peer mappings of every rank's gradient buffer (this step's parity) and flag array
 };
+
+// Data parallel handshake of one 256-thread group (tid 0..255, named barrier `bar`): every thread has stored its share of
+// this rank's gradient. The last CTA of the grid to get here publishes the step into every rank's flag array; then the
+// group waits until its own rank's flag array shows the step for every rank. Returns false if a peer never arrived within
+// dp.timeout_ns (the error word is set; the caller skips its update).
+__device__ __forceinline__ bool dp_publish_and_wait(const DpArgs &dp, int tid, int bar, bool *s_last, bool *s_timed_out) {
+    uint32_t *own = dp.flags[dp.rank];
+    __threadfence();                                               // this thread's gradient stores, device-wide, before the ticket
+    named_bar_sync(bar, 256);
+    if (tid == 0) {
+        *s_timed_out = false;
+        const uint32_t arrived = atomicAdd(own + 8, 1u);
+        *s_last = arrived == gridDim.x - 1;
+        if (*s_last) own[8] = 0u;                                  // the next step's kernel starts from zero
+    }
+    named_bar_sync(bar, 256);
+    if (*s_last && tid < dp.world)    // one thread per destination rank: the system-scope releases run side by side
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dp.flags[tid] + dp.rank), "r"(dp.step) : "memory");
+    if (tid < dp.world && !wait_for_flag(own + tid, dp.step, dp)) *s_timed_out = true;
+    named_bar_sync(bar, 256);
+    return !*s_timed_out;
+}
 
 // clock64 trace of CTA 0 of the most recent launch (read back by the ts_test_wgrad_trace hook)
 __device__ unsigned long long g_wgrad_trace[16];
@@ -59,13 +90,14 @@ __device__ __forceinline__ float4 ld_cluster_v4(uint32_t local_saddr, uint32_t r
 // row-per-lane writes and the row-contiguous reads are free of bank conflicts
 __device__ __forceinline__ uint32_t acc_off(int row, int chunk) { return (uint32_t)row * 512u + ((uint32_t)(chunk ^ (row & 7)) << 4); }
 
-template <int S>      // cluster size = number of batch splits: 4 or 8
+template <int S, bool DP>      // cluster size = number of batch splits: 4 or 8; DP: cross-rank gradient sum over peer mappings
 __global__ void __launch_bounds__(kThreads, 1)
 wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const WgParams p) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages];
     __shared__ __align__(8) uint64_t acc_full_bar;
     __shared__ uint32_t tmem_base_slot;
+    __shared__ bool s_last, s_timed_out;
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int cluster_id = (int)blockIdx.x / S;
@@ -78,25 +110,40 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         pdl_launch_dependents();
         pdl_wait();
         if (threadIdx.x >= 256) return;
-        for (int c = (int)rank; c < p.small_chunks; c += S) {
-            const int chunk = p.small_chunk_begin + c;
-            const int tix = o.chunk_tensor[chunk];
-            if (tix < 0) continue;
-            const TensorDesc d = o.t[tix];
-            const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
-            const int64_t j0 = i0 - d.offset;
-            if (j0 >= d.count) continue;
-            const int n = (int)min((int64_t)4, d.count - j0);
-            float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-            if (d.nsplit > 0) {
-                sum_partials(o.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, o.partial_depth);
-                if (n == 4) *reinterpret_cast<float4 *>(o.grads + i0) = make_float4(g[0], g[1], g[2], g[3]);
-                else for (int e = 0; e < n; ++e) o.grads[i0 + e] = g[e];
-            } else {
-                const float4 t = *reinterpret_cast<const float4 *>(o.grads + i0);
-                g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
+        for (int pass = 0; pass < (DP ? 2 : 1); ++pass) {
+            // DP: pass 0 folds the partials into this rank's peer-visible gradient buffer, then the handshake, pass 1 sums the
+            // ranks and updates; single GPU: one pass does both
+            for (int c = (int)rank; c < p.small_chunks; c += S) {
+                const int chunk = p.small_chunk_begin + c;
+                const int tix = o.chunk_tensor[chunk];
+                if (tix < 0) continue;
+                const TensorDesc d = o.t[tix];
+                const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+                const int64_t j0 = i0 - d.offset;
+                if (j0 >= d.count) continue;
+                const int n = (int)min((int64_t)4, d.count - j0);
+                float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                if (pass == 0) {
+                    if (d.nsplit > 0) {
+                        sum_partials(o.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, o.partial_depth);
+                        // padding lanes carry zeros: the flat buffers are padded to whole chunks
+                        *reinterpret_cast<float4 *>(o.grads + i0) = make_float4(g[0], n > 1 ? g[1] : 0.0f, n > 2 ? g[2] : 0.0f, n > 3 ? g[3] : 0.0f);
+                    } else {
+                        const float4 t = *reinterpret_cast<const float4 *>(o.grads + i0);
+                        g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
+                    }
+                    if (!DP) apply_update(o, d, i0, j0, n, g);
+                } else {
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if (r < p.dp.world) {
+                            const float4 t = __ldcv(reinterpret_cast<const float4 *>(p.dp.grads[r] + i0));
+                            g[0] += t.x; g[1] += t.y; g[2] += t.z; g[3] += t.w;
+                        }
+                    apply_update(o, d, i0, j0, n, g);
+                }
             }
-            apply_update(o, d, i0, j0, n, g);
+            if (DP && pass == 0 && !dp_publish_and_wait(p.dp, (int)threadIdx.x, 2, &s_last, &s_timed_out)) return;
         }
         return;
     }
@@ -252,19 +299,14 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             for (int r = 0; r < S; ++r) part[i][r] = ld_cluster_v4(addr, (uint32_t)r);
         }
         if (et == 0) WTRACE(7);
-#pragma unroll
-        for (int i = 0; i < n_own; ++i) {
-            float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-#pragma unroll
-            for (int r = 0; r < S; ++r) { g[0] += part[i][r].x; g[1] += part[i][r].y; g[2] += part[i][r].z; g[3] += part[i][r].w; }
-            if (idx[i] < 0) continue;
+        auto update_quad = [&](int i, const float (&g)[4]) {
             float ww[4] = {w[i].x, w[i].y, w[i].z, w[i].w}, mm[4] = {m[i].x, m[i].y, m[i].z, m[i].w};
             float vq[4] = {v[i].x, v[i].y, v[i].z, v[i].w}, xx[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) opt_update_element(o, g[e], ww[e], mm[e], vq[e], xx[e]);
             const int64_t gi = p.off_w1 + idx[i];
             *reinterpret_cast<float4 *>(o.params + gi) = make_float4(ww[0], ww[1], ww[2], ww[3]);
-            *reinterpret_cast<float4 *>(o.grads + gi) = make_float4(g[0], g[1], g[2], g[3]);
+            if (!DP) *reinterpret_cast<float4 *>(o.grads + gi) = make_float4(g[0], g[1], g[2], g[3]);   // DP: `grads` keeps this rank's own gradient
             if (use_m) *reinterpret_cast<float4 *>(o.exp_avg + gi) = make_float4(mm[0], mm[1], mm[2], mm[3]);
             if (adam) *reinterpret_cast<float4 *>(o.exp_avg_sq + gi) = make_float4(vq[0], vq[1], vq[2], vq[3]);
             if (use_x) *reinterpret_cast<float4 *>(o.max_exp_avg_sq + gi) = make_float4(xx[0], xx[1], xx[2], xx[3]);
@@ -273,6 +315,36 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             pk.x = *reinterpret_cast<const uint32_t *>(&lo);
             pk.y = *reinterpret_cast<const uint32_t *>(&hi);
             *reinterpret_cast<uint2 *>(o.shadow + p.sh_w1 + idx[i]) = pk;
+        };
+#pragma unroll
+        for (int i = 0; i < n_own; ++i) {
+            float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+            for (int r = 0; r < S; ++r) { g[0] += part[i][r].x; g[1] += part[i][r].y; g[2] += part[i][r].z; g[3] += part[i][r].w; }
+            if (idx[i] < 0) continue;
+            if (DP) *reinterpret_cast<float4 *>(o.grads + p.off_w1 + idx[i]) = make_float4(g[0], g[1], g[2], g[3]);   // peer-visible buffer
+            else update_quad(i, g);
+        }
+        if (DP) {
+            // ---- every rank's gradient is complete once the handshake returns: this thread's quads from all of them, rank order
+            if (dp_publish_and_wait(p.dp, et, 1, &s_last, &s_timed_out)) {
+                float4 rv[n_own][8];
+#pragma unroll
+                for (int i = 0; i < n_own; ++i)
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        rv[i][r] = (idx[i] >= 0 && r < p.dp.world) ? __ldcv(reinterpret_cast<const float4 *>(p.dp.grads[r] + p.off_w1 + idx[i]))
+                                                                   : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+                for (int i = 0; i < n_own; ++i) {
+                    if (idx[i] < 0) continue;
+                    float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if (r < p.dp.world) { g[0] += rv[i][r].x; g[1] += rv[i][r].y; g[2] += rv[i][r].z; g[3] += rv[i][r].w; }
+                    update_quad(i, g);
+                }
+            }
         }
     }
     if (threadIdx.x == 96) WTRACE(8);
@@ -315,7 +387,7 @@ int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st) {
     p.small_chunk_begin = a.small_chunk_begin; p.small_chunks = a.small_chunks;
     p.opt = a.opt;
     TS_REQUIRE(p.opt.params && p.opt.grads && p.opt.shadow && p.opt.chunk_tensor, TS_E_INVALID, "dW1 + update kernel: buffers missing");
-    TS_REQUIRE(p.opt.params_mc == nullptr, TS_E_INVALID, "dW1 + update kernel: single-GPU path only");
+    TS_REQUIRE(p.opt.params_mc == nullptr, TS_E_INVALID, "dW1 + update kernel: not for the nvls exchange");
 
     CUtensorMap ma, mb;
     int rc = get_map(a.dH, (uint64_t)a.H, (uint64_t)a.B, (uint64_t)a.H, 64, BK, &ma);
@@ -328,13 +400,21 @@ int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st) {
     int dev = 0;
     TS_CUDA_CHECK(cudaGetDevice(&dev));
     if (!attr_set[dev & 63]) {
-        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        TS_CUDA_CHECK(cudaFuncSetAttribute(wgrad_update_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_set[dev & 63] = true;
     }
     const unsigned grid = (unsigned)((p.n_tiles + 1) * p.S);
-    if (p.S == 8) TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<8>, dim3(grid), dim3(kThreads), smem, st, 8u, ma, mb, p));
-    else TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<4>, dim3(grid), dim3(kThreads), smem, st, 4u, ma, mb, p));
+    const bool dp = a.dp.world > 1;
+    p.dp = a.dp;
+    // DP: every CTA waits for the peers, so the whole grid must be resident: one CTA per SM (160 KiB of shared memory each)
+    TS_REQUIRE(!dp || (int)grid <= a.sm_count, TS_E_UNSUPPORTED, "dW1 + update kernel: %u CTAs do not fit on %d SMs at once", grid, a.sm_count);
+    if (p.S == 8 && dp) TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<8, true>, dim3(grid), dim3(kThreads), smem, st, 8u, ma, mb, p));
+    else if (p.S == 8) TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<8, false>, dim3(grid), dim3(kThreads), smem, st, 8u, ma, mb, p));
+    else if (dp) TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<4, true>, dim3(grid), dim3(kThreads), smem, st, 4u, ma, mb, p));
+    else TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<4, false>, dim3(grid), dim3(kThreads), smem, st, 4u, ma, mb, p));
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
