@@ -436,3 +436,33 @@ def test_training_is_bit_reproducible(B, optimizer):
         outs.append(got)
     for a, b in zip(*outs):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize('B,x_bf16,H', [(19000, False, 256), (40000, False, 256), (19000, True, 256), (30000, False, 128), (19000, False, 64)])
+def test_streaming_evaluate_against_oracle_and_single_slab_kernel(monkeypatch, B, x_bf16, H):
+    """evaluate() on more slabs than SMs runs the persistent pipelined kernel (eval_stream.cu): two TMEM accumulators, the next
+    slab's loads / conversion / MMAs under this slab's epilogue. 19000 rows = 148 full slabs + a ragged one (56 rows) on 148 SMs.
+    Against the emulating oracle (exact-or-explained predictions, loss within 1e-2 -- it is 1e-5 here, same weights), and against
+    the single-slab fused kernel (TSB200_EVAL_STREAM=0): identical predictions and counts, loss to fp32 round-off, twice in a row
+    (the second call finds the ticket and both accumulators as the first one left them)."""
+    dims = [784, H, 10]
+    x, y = synthetic(B, seed=51)
+    x = x.bfloat16().float()
+    init = seeded_init(dims, bf16=True)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD, lr=0.0, emulate_bf16=True)
+    xin = x.flatten(1).bfloat16() if x_bf16 else x
+    outs = []
+    for flag in ('1', '0'):
+        monkeypatch.setenv('TSB200_EVAL_STREAM', flag)
+        model, net = build_model(dims, 0.1, 'relu', 'sgd', 0.0, init, 'bf16', max_batch=B)
+        if flag == '1':
+            evaluate_checked(model, net, oracle, xin, y, f'streaming evaluate B={B} H={H}', tol=1e-4)
+        got = []
+        for _ in range(2):
+            pr, l = model.evaluate(xin.cuda(), y.cuda())
+            got.append((pr.cpu().numpy(), l.item(), record_counts(l)))
+        assert np.array_equal(got[0][0], got[1][0]) and got[0][1] == got[1][1] and got[0][2] == got[1][2]
+        outs.append(got[0])
+    assert np.array_equal(outs[0][0], outs[1][0])
+    assert outs[0][2] == outs[1][2] == (int((outs[0][0] == y.numpy()).sum()), B)
+    assert outs[0][1] == pytest.approx(outs[1][1], rel=1e-5)

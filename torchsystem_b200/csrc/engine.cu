@@ -66,6 +66,7 @@ struct ts_mlp {
     cudaEvent_t *ov_events = nullptr;   // per-call (ts_fit_backward_overlap): event of layer l recorded once its gradients are enqueued
     int32_t *ov_final = nullptr;        // per-call out: gradient tensor t is final in `grads` when its layer's event fires
     unsigned int step_flag = 0;   // value of the single-kernel step's gradient-ready counter after the launches so far
+    int eval_stream = 1;          // evaluate, large batches: persistent pipelined kernel (TSB200_EVAL_STREAM=0: the single-slab fused kernel)
     int wgrad_update = 1;         // fused path: dW1 GEMM, split-K reduce and optimizer update in one kernel (TSB200_WGRAD_UPDATE=0: off)
     int step_kernel = 1;          // batches of at most 64 rows: the whole fit step in one kernel (TSB200_STEP_KERNEL=0: off)
     int inkernel_cast = -1;       // fp32 batches converted inside the fused kernel: 1 always, 0 never (cast kernel in front), -1 by batch size
@@ -437,6 +438,11 @@ int fused_forward(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64
     f.training = train && m->p > 0.0f;
     f.partials = m->head_partials; f.ticket = m->ticket; f.record = rec; f.bad_target = m->status_dev;
     ProfScope ps(K_FUSED, st);
+    // evaluate on more slabs than half the SMs (a slab is then a single CTA): the persistent kernel overlaps a slab's epilogue
+    // with the next slab's loads, conversion and main loop
+    if (!train && m->eval_stream && fused_cluster_size(B, m->dims[1], m->sm_count) == 1 && (B + 127) / 128 >= m->sm_count &&
+        eval_stream_supported(m->dims[0], m->dims[1], m->dims[2]))
+        return launch_eval_stream(f, m->sm_count, st);
     return launch_fused_mlp(f, m->sm_count, st);
 }
 
@@ -846,6 +852,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     if (const char *e = getenv("TSB200_INKERNEL_CAST")) m->inkernel_cast = atoi(e) != 0 ? 1 : 0;
     if (const char *e = getenv("TSB200_STEP_KERNEL")) m->step_kernel = atoi(e) != 0 ? 1 : 0;
     if (const char *e = getenv("TSB200_WGRAD_UPDATE")) m->wgrad_update = atoi(e) != 0 ? 1 : 0;
+    if (const char *e = getenv("TSB200_EVAL_STREAM")) m->eval_stream = atoi(e) != 0 ? 1 : 0;
     m->n_tensors = 2 * m->n_layers;
     int64_t o = 0, so = 0;
     for (int l = 0; l < m->n_layers; ++l) {

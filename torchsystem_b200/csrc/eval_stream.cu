@@ -1,0 +1,429 @@
+// Streaming evaluate for large batches of the one-hidden-layer aggregate (classifier.py:37-39, mlp.py:14-17, metrics.py:14-15):
+// the `validate` handler at batch 65,536 is HBM-bound -- 3,152 bytes per sample for 0.4 MFLOP -- and the single-slab fused
+// kernel (fused_mlp.cu) spent as long outside its main loop as inside it, with nothing overlapping the two.
+//
+// Persistent: one CTA per SM walks the 128-row slabs (slab = blockIdx.x, + gridDim.x, ...). Everything about slab i+1 that
+// does not depend on slab i runs while slab i's epilogue drains:
+//
+//   warp 0        TMA producer: fp32 input tiles into a two-slot staging ring (or bf16 tiles straight into the operand ring)
+//   warps 8..15   converters: fp32 staging slot -> bf16 -> swizzled K-major operand tile (two stages)
+//   warp 2        TMA producer: W1 tiles (H x 64, three stages) and, once, W2
+//   warp 1        MMA issuer: H = X W1^T into one of TWO TMEM accumulators (256 columns each)
+//   warps 4..7    epilogue, one batch row per thread: accumulator -> + b1, ReLU -> bf16 -> one 64-column operand atom at a
+//                 time (single 16 KiB buffer), then logits -> softmax / NLL / first-max argmax -> predictions
+//   warp 3        second MMA issuer: Z += A_atom W2_atom^T as soon as an atom is written. The logits accumulate into columns
+//                 0..15 of the SAME accumulator the epilogue is draining (those columns were read first), so two 256-column
+//                 accumulators and the logits fit the 512 columns of tensor memory.
+//
+// Loss sum and correct count stay in registers across the slabs of a CTA and are folded warp -> CTA -> grid in a fixed order
+// (one partial per CTA, last CTA sums them by index): bit-reproducible for a given grid size.
+// Shared memory (H = 256, fp32 inputs): staging 64 KiB + X operand 32 KiB + W1 96 KiB + activation atom 16 KiB + W2 8 KiB.
+#include <cstdlib>
+
+#include "tc_common.cuh"
+
+namespace tsb {
+
+using namespace tc;
+
+namespace {
+
+constexpr int kThreads = 512;
+constexpr int kConvWarps = 8, kEpiWarps = 4;
+constexpr int CP = 16;
+constexpr int kXStages = 2, kFStages = 2, kMaxWStages = 4;
+constexpr uint32_t kFBytes = 128 * 64 * 4;     // one fp32 staging slot: 128 rows x 64 columns
+constexpr uint32_t kXBytes = 128 * 64 * 2;     // one bf16 operand tile
+constexpr int kAccStride = 256;                // TMEM columns between the two accumulators
+
+struct EvalParams {
+    int B, D, H, C;
+    int num_kblocks, wstages, atoms, slabs;
+    int x_f32;
+    uint32_t w_bytes;                          // one W1 stage: H x 128 B
+    uint32_t idesc_main, idesc_z;
+    const float *b1, *b2;
+    const int64_t *y;
+    int64_t *pred;
+    HeadPartial *partials;
+    unsigned int *ticket;
+    ts_batch_record *record;
+    uint32_t *bad_target;
+};
+
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w1,
+                   const __grid_constant__ CUtensorMap tma_w2, const EvalParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t xf_full[kFStages], xf_empty[kFStages];      // fp32 staging slots
+    __shared__ __align__(8) uint64_t x_full[kXStages], x_empty[kXStages];        // bf16 X operand stages
+    __shared__ __align__(8) uint64_t w_full[kMaxWStages], w_empty[kMaxWStages];  // W1 stages
+    __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2], z_full[2];
+    __shared__ __align__(8) uint64_t a_full, a_empty, w2_full;
+    __shared__ uint32_t tmem_base_slot;
+    __shared__ float s_loss[kEpiWarps];
+    __shared__ int s_corr[kEpiWarps];
+    __shared__ bool s_last;
+
+    uint8_t *base = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *x_stage = base;                                            // kXStages x 16 KiB
+    uint8_t *a_atom = x_stage + kXStages * kXBytes;                     // 16 KiB
+    uint8_t *w_stage = a_atom + kXBytes;                                // wstages x w_bytes
+    uint8_t *w2_tile = w_stage + (size_t)p.wstages * p.w_bytes;         // atoms x 2 KiB
+    float *b1s = reinterpret_cast<float *>(w2_tile + (size_t)p.atoms * 2048);
+    uint8_t *f_stage = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(b1s + p.H) + 1023) & ~(uintptr_t)1023);   // kFStages x 32 KiB
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+    const int my_slabs = (p.slabs - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kFStages; ++s) { mbar_init(&xf_full[s], 1); mbar_init(&xf_empty[s], kConvWarps); }
+        for (int s = 0; s < kXStages; ++s) { mbar_init(&x_full[s], p.x_f32 ? kConvWarps : 1); mbar_init(&x_empty[s], 1); }
+        for (int s = 0; s < p.wstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiWarps); mbar_init(&z_full[b], 1); }
+        mbar_init(&a_full, kEpiWarps);
+        mbar_init(&a_empty, 1);
+        mbar_init(&w2_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_x)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_w1)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_w2)) : "memory");
+    }
+    if (warp == 1) tmem_alloc(&tmem_base_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+    pdl_wait();
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        // ===================== TMA producer: input tiles =====================
+        int f = 0, sx = 0;
+        uint32_t fphase = 0, xphase = 0;
+        for (int it = 0; it < my_slabs; ++it) {
+            const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) * BM;
+            for (int kb = 0; kb < p.num_kblocks; ++kb) {
+                if (elect_one()) {
+                    if (p.x_f32) {       // fp32 tile = two boxes of 32 columns (128-byte rows) into the staging ring
+                        mbar_wait(&xf_empty[f], fphase ^ 1);
+                        mbar_expect_tx(&xf_full[f], kFBytes);
+                        uint8_t *dst = f_stage + (size_t)f * kFBytes;
+                        tma_load_2d(&tma_x, &xf_full[f], dst, kb * KATOM, m0);
+                        tma_load_2d(&tma_x, &xf_full[f], dst + kFBytes / 2, kb * KATOM + 32, m0);
+                    } else {
+                        mbar_wait(&x_empty[sx], xphase ^ 1);
+                        mbar_expect_tx(&x_full[sx], kXBytes);
+                        tma_load_2d(&tma_x, &x_full[sx], x_stage + (size_t)sx * kXBytes, kb * KATOM, m0);
+                    }
+                }
+                __syncwarp();
+                if (++f == kFStages) { f = 0; fphase ^= 1; }
+                if (++sx == kXStages) { sx = 0; xphase ^= 1; }
+            }
+        }
+    } else if (warp == 2) {
+        // ===================== TMA producer: W2 once, W1 tiles for every slab (re-read from L2) =====================
+        if (elect_one()) {
+            mbar_expect_tx(&w2_full, (uint32_t)p.atoms * 2048u);
+            for (int a = 0; a < p.atoms; ++a) tma_load_2d(&tma_w2, &w2_full, w2_tile + (size_t)a * 2048, a * KATOM, 0);
+        }
+        __syncwarp();
+        int s = 0;
+        uint32_t phase = 0;
+        for (int it = 0; it < my_slabs; ++it)
+            for (int kb = 0; kb < p.num_kblocks; ++kb) {
+                if (elect_one()) {
+                    mbar_wait(&w_empty[s], phase ^ 1);
+                    mbar_expect_tx(&w_full[s], p.w_bytes);
+                    tma_load_2d(&tma_w1, &w_full[s], w_stage + (size_t)s * p.w_bytes, kb * KATOM, 0);
+                }
+                __syncwarp();
+                if (++s == p.wstages) { s = 0; phase ^= 1; }
+            }
+    } else if (warp == 1) {
+        // ===================== MMA issuer: H = X W1^T, accumulators alternate =====================
+        int sx = 0, sw = 0;
+        uint32_t xphase = 0, wphase = 0;
+        for (int it = 0; it < my_slabs; ++it) {
+            const int b = it & 1;
+            const uint32_t tmem_d = tmem_base + (uint32_t)(b * kAccStride);
+            if (elect_one()) {
+                mbar_wait(&acc_empty[b], ((uint32_t)(it >> 1) & 1u) ^ 1u);      // the epilogue has drained this accumulator
+                tc_fence_after();
+            }
+            __syncwarp();
+            for (int kb = 0; kb < p.num_kblocks; ++kb) {
+                if (elect_one()) {
+                    mbar_wait(&x_full[sx], xphase);
+                    mbar_wait(&w_full[sw], wphase);
+                    tc_fence_after();
+                    const uint64_t adesc = make_desc(smem_u32(x_stage + (size_t)sx * kXBytes), TC_MAJOR_K, KATOM);
+                    const uint64_t bdesc = make_desc(smem_u32(w_stage + (size_t)sw * p.w_bytes), TC_MAJOR_K, KATOM);
+#pragma unroll
+                    for (int k = 0; k < KATOM / UMMA_K; ++k)
+                        umma_bf16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc_main, (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&x_empty[sx]);
+                    umma_commit(&w_empty[sw]);
+                    if (kb == p.num_kblocks - 1) umma_commit(&acc_full[b]);
+                }
+                __syncwarp();
+                if (++sx == kXStages) { sx = 0; xphase ^= 1; }
+                if (++sw == p.wstages) { sw = 0; wphase ^= 1; }
+            }
+        }
+    } else if (warp == 3) {
+        // ===================== second MMA issuer: Z += A_atom W2_atom^T, into columns 0..15 of the accumulator being drained =====================
+        if (elect_one()) mbar_wait(&w2_full, 0);
+        __syncwarp();
+        uint32_t use = 0;
+        for (int it = 0; it < my_slabs; ++it) {
+            const int b = it & 1;
+            const uint32_t tmem_z = tmem_base + (uint32_t)(b * kAccStride);
+            for (int a = 0; a < p.atoms; ++a, ++use) {
+                if (elect_one()) {
+                    mbar_wait(&a_full, use & 1u);
+                    tc_fence_after();
+                    const uint64_t adesc = make_desc(smem_u32(a_atom), TC_MAJOR_K, KATOM);
+                    const uint64_t bdesc = make_desc(smem_u32(w2_tile + (size_t)a * 2048), TC_MAJOR_K, KATOM);
+#pragma unroll
+                    for (int k = 0; k < KATOM / UMMA_K; ++k)
+                        umma_bf16(tmem_z, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc_z, (a > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&a_empty);
+                    if (a == p.atoms - 1) umma_commit(&z_full[b]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp < 4 + kEpiWarps) {
+        // ===================== epilogue warps: one batch row per thread =====================
+        const int q = warp & 3;
+        const int r_local = q * 32 + lane;
+        const int et = threadIdx.x - 128;                   // 0..127
+        for (int i = et; i < p.H; i += 32 * kEpiWarps) b1s[i] = p.b1[i];
+        named_bar_sync(1, 32 * kEpiWarps);
+        float b2v[CP];
+#pragma unroll
+        for (int c = 0; c < CP; ++c) b2v[c] = (c < p.C) ? p.b2[c] : 0.0f;
+        float loss_acc = 0.0f;
+        int corr_acc = 0;
+        uint32_t use = 0;
+        for (int it = 0; it < my_slabs; ++it) {
+            const int b = it & 1;
+            const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) * BM;
+            const int64_t row = (int64_t)m0 + r_local;
+            const bool row_ok = row < p.B;
+            const uint32_t t_acc = tmem_base + (uint32_t)(b * kAccStride) + ((uint32_t)(q * 32) << 16);
+            const int yy = row_ok ? (int)p.y[row] : 0;      // issued early: its latency hides behind the accumulator wait
+            if (elect_one()) mbar_wait(&acc_full[b], (uint32_t)(it >> 1) & 1u);
+            __syncwarp();
+            tc_fence_after();
+            // ---- A = relu(H + b1) -> bf16 -> K-major swizzled atom, 64 hidden columns at a time
+            for (int a = 0; a < p.atoms; ++a, ++use) {
+                const uint32_t rowp = smem_u32(a_atom) + (uint32_t)r_local * 128u;
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {             // 32 columns at a time keeps the thread under 128 registers
+                    float v[32];
+                    tmem_ld16(t_acc + (uint32_t)(a * 64 + hf * 32), *reinterpret_cast<float(*)[16]>(&v[0]));
+                    tmem_ld16(t_acc + (uint32_t)(a * 64 + hf * 32 + 16), *reinterpret_cast<float(*)[16]>(&v[16]));
+                    uint4 pk[4];
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        float r8[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) r8[j] = fmaxf(v[8 * t + j] + b1s[a * 64 + hf * 32 + 8 * t + j], 0.0f);
+                        pk[t].x = pack_bf16(r8[0], r8[1]); pk[t].y = pack_bf16(r8[2], r8[3]);
+                        pk[t].z = pack_bf16(r8[4], r8[5]); pk[t].w = pack_bf16(r8[6], r8[7]);
+                    }
+                    if (hf == 0) {
+                        if (elect_one()) mbar_wait(&a_empty, (use & 1u) ^ 1u);   // the logits MMAs of the previous atom have read the buffer
+                        __syncwarp();
+                    }
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) sts128(rowp + ((uint32_t)((hf * 4 + t) ^ (r_local & 7)) << 4), pk[t]);
+                }
+                fence_proxy_async_smem();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&a_full);
+            }
+            // ---- logits -> cross-entropy, argmax (classifier.py:27, 38-39); bf16 mode tolerates the fast exp / log
+            if (elect_one()) mbar_wait(&z_full[b], (uint32_t)(it >> 1) & 1u);
+            __syncwarp();
+            tc_fence_after();
+            float z[CP];
+            tmem_ld16(t_acc, z);
+            // this warp's reads of the accumulator are done: hand it back to the main MMA issuer
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[b]);
+#pragma unroll
+            for (int c = 0; c < CP; ++c) z[c] = (c < p.C) ? z[c] + b2v[c] : 0.0f;
+            float mx = z[0];
+            int arg = 0;
+#pragma unroll
+            for (int c = 1; c < CP; ++c)
+                if (c < p.C && z[c] > mx) { mx = z[c]; arg = c; }      // strict '>': first maximum wins (torch.argmax)
+            float ssum = 0.0f;
+#pragma unroll
+            for (int c = 0; c < CP; ++c) ssum += (c < p.C) ? __expf(z[c] - mx) : 0.0f;
+            const float lse = mx + __logf(ssum);
+            float zy = 0.0f;
+#pragma unroll
+            for (int c = 0; c < CP; ++c)
+                if (c == yy) zy = z[c];
+            float row_loss = lse - zy;
+            if (yy < 0 || yy >= p.C) {                       // target outside [0, C): poison the loss, tell the host
+                row_loss = __int_as_float(0x7fc00000);
+                if (row_ok && p.bad_target != nullptr) *reinterpret_cast<volatile uint32_t *>(p.bad_target) = (uint32_t)row + 1u;
+            }
+            if (row_ok) {
+                loss_acc += row_loss;
+                corr_acc += (arg == yy) ? 1 : 0;
+                p.pred[row] = arg;
+            }
+        }
+        // ---- loss sum / correct count: thread -> warp -> CTA -> grid (last CTA finalises in index order)
+        loss_acc = warp_sum(loss_acc);
+        corr_acc = warp_sum(corr_acc);
+        if (lane == 0) { s_loss[q] = loss_acc; s_corr[q] = corr_acc; }
+        named_bar_sync(1, 32 * kEpiWarps);
+        if (q == 3 && lane == 0) {
+            p.partials[blockIdx.x].loss_sum = (s_loss[0] + s_loss[1]) + (s_loss[2] + s_loss[3]);
+            p.partials[blockIdx.x].correct = s_corr[0] + s_corr[1] + s_corr[2] + s_corr[3];
+            __threadfence();
+            s_last = (atomicAdd(p.ticket, 1u) == gridDim.x - 1);
+        }
+        named_bar_sync(1, 32 * kEpiWarps);
+        if (s_last && q == 3) {
+            __threadfence();
+            float l = 0.0f;
+            int c = 0;
+            for (int i = lane; i < (int)gridDim.x; i += 32) {
+                const volatile HeadPartial *hp = p.partials + i;
+                l += hp->loss_sum;
+                c += hp->correct;
+            }
+            l = warp_sum(l);
+            c = warp_sum(c);
+            if (lane == 0) {
+                p.record->loss = l / (float)p.B;
+                p.record->n_correct = c;
+                p.record->n_rows = (int32_t)p.B;
+                p.record->reserved = 0;
+                *p.ticket = 0u;
+            }
+        }
+    } else if (p.x_f32) {
+        // ===================== converter warps: fp32 staging slot -> bf16 operand tile, thread = (row, 32-column half) =====================
+        const int ct = threadIdx.x - 256;                    // 0..255
+        const int cr = ct >> 1, ch = ct & 1;
+        const uint32_t src0 = smem_u32(f_stage) + (uint32_t)ch * (kFBytes / 2) + (uint32_t)cr * 128;
+        const uint32_t dst0 = smem_u32(x_stage) + (uint32_t)cr * 128;
+        const uint32_t sw = (uint32_t)(cr & 7);
+        int f = 0, sx = 0;
+        uint32_t fphase = 0, xphase = 0;
+        const int total = my_slabs * p.num_kblocks;
+        for (int i = 0; i < total; ++i) {
+            // every lane observes the TMA barrier itself: bytes written through the async proxy are only guaranteed visible
+            // to threads that waited on the mbarrier
+            mbar_wait(&xf_full[f], fphase);
+            const uint32_t src = src0 + (uint32_t)f * kFBytes;
+            float4 v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = lds128(src + (((uint32_t)j ^ sw) << 4));
+            uint4 pk[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                pk[t].x = pack_bf16(v[2 * t].x, v[2 * t].y);
+                pk[t].y = pack_bf16(v[2 * t].z, v[2 * t].w);
+                pk[t].z = pack_bf16(v[2 * t + 1].x, v[2 * t + 1].y);
+                pk[t].w = pack_bf16(v[2 * t + 1].z, v[2 * t + 1].w);
+            }
+            mbar_wait(&x_empty[sx], xphase ^ 1);             // operand stage free (its MMAs retired)
+            const uint32_t dst = dst0 + (uint32_t)sx * kXBytes;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) sts128(dst + ((((uint32_t)ch * 4 + t) ^ sw) << 4), pk[t]);
+            // the staging slot is released only after its values were consumed by the stores above (an arrive does not wait
+            // for loads still in flight; releasing right behind them lets the next TMA fill overtake them)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&xf_empty[f]);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&x_full[sx]);
+            if (++f == kFStages) { f = 0; fphase ^= 1; }
+            if (++sx == kXStages) { sx = 0; xphase ^= 1; }
+        }
+    }
+    __syncwarp();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace
+
+bool eval_stream_supported(int D, int H, int C) { return (H == 64 || H == 128 || H == 256) && C >= 1 && C <= CP && D % 8 == 0; }
+
+int launch_eval_stream(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
+    TS_REQUIRE(eval_stream_supported(a.D, a.H, a.C), TS_E_UNSUPPORTED, "streaming evaluate: unsupported shape D=%d H=%d C=%d", a.D, a.H, a.C);
+    TS_REQUIRE(a.B >= 1 && a.dH_out == nullptr, TS_E_INVALID, "streaming evaluate: batch %lld / not an evaluate call", (long long)a.B);
+    TS_REQUIRE((a.X != nullptr) != (a.X_f32 != nullptr), TS_E_INVALID, "streaming evaluate: exactly one of X (bf16) and X_f32");
+    EvalParams p{};
+    p.B = (int)a.B; p.D = a.D; p.H = a.H; p.C = a.C;
+    p.slabs = (int)((a.B + BM - 1) / BM);
+    p.num_kblocks = (a.D + KATOM - 1) / KATOM;
+    p.atoms = a.H / KATOM;
+    p.x_f32 = a.X_f32 != nullptr ? 1 : 0;
+    p.w_bytes = (uint32_t)a.H * 128u;
+    const size_t fixed = (size_t)kXStages * kXBytes + kXBytes + (size_t)p.atoms * 2048 + (size_t)a.H * 4 + 1024 + 1024 +
+                         (p.x_f32 ? (size_t)kFStages * kFBytes : 0) + 64;
+    p.wstages = (int)((226u * 1024u - fixed) / p.w_bytes);
+    if (p.wstages > kMaxWStages) p.wstages = kMaxWStages;
+    TS_REQUIRE(p.wstages >= 2, TS_E_UNSUPPORTED, "streaming evaluate: shared memory budget does not fit H=%d", a.H);
+    p.idesc_main = make_idesc(BM, a.H, TC_MAJOR_K, TC_MAJOR_K);
+    p.idesc_z = make_idesc(BM, CP, TC_MAJOR_K, TC_MAJOR_K);
+    p.b1 = a.b1; p.b2 = a.b2; p.y = a.y; p.pred = a.pred;
+    p.partials = a.partials; p.ticket = a.ticket; p.record = a.record; p.bad_target = a.bad_target;
+
+    CUtensorMap mx, mw1, mw2;
+    int rc = p.x_f32 ? get_map(a.X_f32, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, 32, (uint32_t)BM, &mx, 4)
+                     : get_map(a.X, (uint64_t)a.D, (uint64_t)a.B, (uint64_t)a.D, KATOM, (uint32_t)BM, &mx);
+    if (rc) return rc;
+    rc = get_map(a.W1, (uint64_t)a.D, (uint64_t)a.H, (uint64_t)a.D, KATOM, (uint32_t)a.H, &mw1);
+    if (rc) return rc;
+    rc = get_map(a.W2p, (uint64_t)a.H, (uint64_t)CP, (uint64_t)a.H, KATOM, CP, &mw2);
+    if (rc) return rc;
+
+    const size_t smem = fixed + (size_t)p.wstages * p.w_bytes;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    TS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!attr_set[dev & 63]) {
+        TS_CUDA_CHECK(cudaFuncSetAttribute(eval_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        attr_set[dev & 63] = true;
+    }
+    const int grid = p.slabs < sm_count ? p.slabs : sm_count;
+    TS_REQUIRE(grid <= kMaxHeadBlocks, TS_E_TOO_LARGE, "streaming evaluate: %d CTAs, more than the %d partial slots", grid, kMaxHeadBlocks);
+    TS_CUDA_CHECK(launch_pdl(eval_stream_kernel, dim3((unsigned)grid), dim3(kThreads), smem, st, 1, mx, mw1, mw2, p));
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
+}  // namespace tsb

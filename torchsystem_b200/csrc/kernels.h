@@ -256,6 +256,9 @@ bool fused_mlp_supported(int D, int H, int C);
 inline bool fused_grads_supported(int H, int C, int64_t B) { return H >= 128 && C <= 15 && (B + 127) / 128 <= kMaxRowBlocks; }
 int fused_cluster_size(int64_t B, int H, int sm_count);   // CTAs per 128-row slab the launcher will use
 int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st);
+// persistent, pipelined evaluate for batches whose slabs are single CTAs (eval_stream.cu); same arguments, evaluate only
+bool eval_stream_supported(int D, int H, int C);
+int launch_eval_stream(const FusedMlpArgs &a, int sm_count, cudaStream_t st);
 int read_fused_trace(unsigned long long *out_host);   // 32 clock64 samples of CTA 0 of the last launch
 
 }  // namespace tsb
