@@ -280,6 +280,8 @@ int32_t ts_test_fused_trace(uint64_t *out /*HOST, 32 entries*/);
 int32_t ts_test_step_trace(uint64_t *out /*HOST, 32 entries*/);
 /* The same for the dW1 + update kernel of the fused training path (16 samples). */
 int32_t ts_test_wgrad_trace(uint64_t *out /*HOST, 16 entries*/);
+/* The same for the streaming evaluate kernel (CTA 0, third slab; 32 samples). */
+int32_t ts_test_eval_trace(uint64_t *out /*HOST, 32 entries*/);
 
 /* number of kernels this library has launched on the calling process so far (bench.py's gpu_launches) */
 int64_t ts_launch_count(void);

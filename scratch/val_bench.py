@@ -1,5 +1,6 @@
 import sys, torch
-sys.path.insert(0, '/root/repo')
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from torch import nn
 from torchsystem_b200 import B200Classifier, MLP
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
@@ -18,3 +19,14 @@ def run(fn, iters):
 for name, fn in (('evaluate', model.evaluate), ('fit', model.fit)):
     us = run(fn, 40)
     print(f'{name} B={B}: {us:.1f} us/batch, {B / us:.1f} M samples/s, fp32-stream {B * 3152 / us / 1e3:.0f} GB/s')
+
+import ctypes as C
+from torchsystem_b200 import _lib
+model.evaluate(x[:B], y[:B])
+out = (C.c_uint64 * 32)()
+_lib.check(_lib.lib.ts_test_eval_trace(out), 'trace'); t = list(out)
+t0 = t[0]
+print('MMA issuer (slab 3): acc_empty wait', t[1] - t0, '| kb0 x_full', t[2] - t0, 'w_full', t[3] - t0, '| kb1', t[4] - t0, t[5] - t0, '| kb2', t[6] - t0, t[7] - t0,
+      '| kb3', t[8] - t0, t[9] - t0, '| last kb committed', t[10] - t0)
+print('epilogue: start', t[11] - t0, 'acc_full', t[12] - t0, 'atoms done', t[13] - t0, 'z_full', t[14] - t0, 'slab done', t[15] - t0)
+print('converter kb0..3 (start, xf_full, x_empty):', [(t[16 + 3 * i] - t0, t[17 + 3 * i] - t0, t[18 + 3 * i] - t0) for i in range(4)])

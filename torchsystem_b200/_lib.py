@@ -79,6 +79,7 @@ PROTOTYPES = {
     'ts_test_fused_trace': (C.c_int32, [C.POINTER(C.c_uint64)]),
     'ts_test_step_trace': (C.c_int32, [C.POINTER(C.c_uint64)]),
     'ts_test_wgrad_trace': (C.c_int32, [C.POINTER(C.c_uint64)]),
+    'ts_test_eval_trace': (C.c_int32, [C.POINTER(C.c_uint64)]),
     'ts_launch_count': (C.c_int64, []),
     'ts_profile_begin': (C.c_int32, []),
     'ts_profile_end': (C.c_int32, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]),

@@ -1215,6 +1215,12 @@ int32_t ts_test_fused_trace(uint64_t *out) {
     return read_fused_trace((unsigned long long *)out);
 }
 
+int32_t ts_test_eval_trace(uint64_t *out) {
+    TS_REQUIRE(out, TS_E_INVALID, "null argument");
+    TS_CUDA_CHECK(cudaDeviceSynchronize());
+    return read_eval_trace((unsigned long long *)out);
+}
+
 int32_t ts_test_wgrad_trace(uint64_t *out) {
     TS_REQUIRE(out, TS_E_INVALID, "null argument");
     TS_CUDA_CHECK(cudaDeviceSynchronize());

@@ -31,14 +31,14 @@ namespace {
 constexpr int kThreads = 512;
 constexpr int kConvWarps = 8, kEpiWarps = 4;
 constexpr int CP = 16;
-constexpr int kXStages = 2, kFStages = 2, kMaxWStages = 4;
+constexpr int kMaxXStages = 4, kMaxFStages = 4, kMaxWStages = 4;
 constexpr uint32_t kFBytes = 128 * 64 * 4;     // one fp32 staging slot: 128 rows x 64 columns
 constexpr uint32_t kXBytes = 128 * 64 * 2;     // one bf16 operand tile
 constexpr int kAccStride = 256;                // TMEM columns between the two accumulators
 
 struct EvalParams {
     int B, D, H, C;
-    int num_kblocks, wstages, atoms, slabs;
+    int num_kblocks, wstages, xstages, fstages, atoms, slabs;
     int x_f32;
     uint32_t w_bytes;                          // one W1 stage: H x 128 B
     uint32_t idesc_main, idesc_z;
@@ -50,6 +50,10 @@ struct EvalParams {
     ts_batch_record *record;
     uint32_t *bad_target;
 };
+
+// clock64 trace of CTA 0, second slab (steady state), read back by the ts_test_eval_trace hook
+__device__ unsigned long long g_eval_trace[32];
+#define ETRACE(i) do { if (blockIdx.x == 0) g_eval_trace[(i)] = clock64(); } while (0)
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
     float4 v;
@@ -68,8 +72,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w1,
                    const __grid_constant__ CUtensorMap tma_w2, const EvalParams p) {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t xf_full[kFStages], xf_empty[kFStages];      // fp32 staging slots
-    __shared__ __align__(8) uint64_t x_full[kXStages], x_empty[kXStages];        // bf16 X operand stages
+    __shared__ __align__(8) uint64_t xf_full[kMaxFStages], xf_empty[kMaxFStages];  // fp32 staging slots
+    __shared__ __align__(8) uint64_t x_full[kMaxXStages], x_empty[kMaxXStages];    // bf16 X operand stages
     __shared__ __align__(8) uint64_t w_full[kMaxWStages], w_empty[kMaxWStages];  // W1 stages
     __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2], z_full[2];
     __shared__ __align__(8) uint64_t a_full, a_empty, w2_full;
@@ -79,19 +83,19 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
     __shared__ bool s_last;
 
     uint8_t *base = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint8_t *x_stage = base;                                            // kXStages x 16 KiB
-    uint8_t *a_atom = x_stage + kXStages * kXBytes;                     // 16 KiB
+    uint8_t *x_stage = base;                                            // xstages x 16 KiB
+    uint8_t *a_atom = x_stage + (size_t)p.xstages * kXBytes;            // 16 KiB
     uint8_t *w_stage = a_atom + kXBytes;                                // wstages x w_bytes
     uint8_t *w2_tile = w_stage + (size_t)p.wstages * p.w_bytes;         // atoms x 2 KiB
     float *b1s = reinterpret_cast<float *>(w2_tile + (size_t)p.atoms * 2048);
-    uint8_t *f_stage = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(b1s + p.H) + 1023) & ~(uintptr_t)1023);   // kFStages x 32 KiB
+    uint8_t *f_stage = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(b1s + p.H) + 1023) & ~(uintptr_t)1023);   // fstages x 32 KiB
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int my_slabs = (p.slabs - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kFStages; ++s) { mbar_init(&xf_full[s], 1); mbar_init(&xf_empty[s], kConvWarps); }
-        for (int s = 0; s < kXStages; ++s) { mbar_init(&x_full[s], p.x_f32 ? kConvWarps : 1); mbar_init(&x_empty[s], 1); }
+        for (int s = 0; s < p.fstages; ++s) { mbar_init(&xf_full[s], 1); mbar_init(&xf_empty[s], kConvWarps); }
+        for (int s = 0; s < p.xstages; ++s) { mbar_init(&x_full[s], p.x_f32 ? kConvWarps : 1); mbar_init(&x_empty[s], 1); }
         for (int s = 0; s < p.wstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiWarps); mbar_init(&z_full[b], 1); }
         mbar_init(&a_full, kEpiWarps);
@@ -131,8 +135,8 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
                     }
                 }
                 __syncwarp();
-                if (++f == kFStages) { f = 0; fphase ^= 1; }
-                if (++sx == kXStages) { sx = 0; xphase ^= 1; }
+                if (++f == p.fstages) { f = 0; fphase ^= 1; }
+                if (++sx == p.xstages) { sx = 0; xphase ^= 1; }
             }
         }
     } else if (warp == 2) {
@@ -162,14 +166,18 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
             const int b = it & 1;
             const uint32_t tmem_d = tmem_base + (uint32_t)(b * kAccStride);
             if (elect_one()) {
+                if (it == 2) ETRACE(0);
                 mbar_wait(&acc_empty[b], ((uint32_t)(it >> 1) & 1u) ^ 1u);      // the epilogue has drained this accumulator
                 tc_fence_after();
+                if (it == 2) ETRACE(1);
             }
             __syncwarp();
             for (int kb = 0; kb < p.num_kblocks; ++kb) {
                 if (elect_one()) {
                     mbar_wait(&x_full[sx], xphase);
+                    if (it == 2 && kb < 4) ETRACE(2 + 2 * kb);
                     mbar_wait(&w_full[sw], wphase);
+                    if (it == 2 && kb < 4) ETRACE(3 + 2 * kb);
                     tc_fence_after();
                     const uint64_t adesc = make_desc(smem_u32(x_stage + (size_t)sx * kXBytes), TC_MAJOR_K, KATOM);
                     const uint64_t bdesc = make_desc(smem_u32(w_stage + (size_t)sw * p.w_bytes), TC_MAJOR_K, KATOM);
@@ -179,9 +187,10 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
                     umma_commit(&x_empty[sx]);
                     umma_commit(&w_empty[sw]);
                     if (kb == p.num_kblocks - 1) umma_commit(&acc_full[b]);
+                    if (it == 2 && kb == p.num_kblocks - 1) ETRACE(10);
                 }
                 __syncwarp();
-                if (++sx == kXStages) { sx = 0; xphase ^= 1; }
+                if (++sx == p.xstages) { sx = 0; xphase ^= 1; }
                 if (++sw == p.wstages) { sw = 0; wphase ^= 1; }
             }
         }
@@ -228,9 +237,11 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
             const bool row_ok = row < p.B;
             const uint32_t t_acc = tmem_base + (uint32_t)(b * kAccStride) + ((uint32_t)(q * 32) << 16);
             const int yy = row_ok ? (int)p.y[row] : 0;      // issued early: its latency hides behind the accumulator wait
+            if (it == 2 && et == 0) ETRACE(11);
             if (elect_one()) mbar_wait(&acc_full[b], (uint32_t)(it >> 1) & 1u);
             __syncwarp();
             tc_fence_after();
+            if (it == 2 && et == 0) ETRACE(12);
             // ---- A = relu(H + b1) -> bf16 -> K-major swizzled atom, 64 hidden columns at a time
             for (int a = 0; a < p.atoms; ++a, ++use) {
                 const uint32_t rowp = smem_u32(a_atom) + (uint32_t)r_local * 128u;
@@ -261,9 +272,11 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
                 if (lane == 0) mbar_arrive(&a_full);
             }
             // ---- logits -> cross-entropy, argmax (classifier.py:27, 38-39); bf16 mode tolerates the fast exp / log
+            if (it == 2 && et == 0) ETRACE(13);
             if (elect_one()) mbar_wait(&z_full[b], (uint32_t)(it >> 1) & 1u);
             __syncwarp();
             tc_fence_after();
+            if (it == 2 && et == 0) ETRACE(14);
             float z[CP];
             tmem_ld16(t_acc, z);
             // this warp's reads of the accumulator are done: hand it back to the main MMA issuer
@@ -295,6 +308,7 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
                 corr_acc += (arg == yy) ? 1 : 0;
                 p.pred[row] = arg;
             }
+            if (it == 2 && et == 0) ETRACE(15);
         }
         // ---- loss sum / correct count: thread -> warp -> CTA -> grid (last CTA finalises in index order)
         loss_acc = warp_sum(loss_acc);
@@ -340,7 +354,10 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
         for (int i = 0; i < total; ++i) {
             // every lane observes the TMA barrier itself: bytes written through the async proxy are only guaranteed visible
             // to threads that waited on the mbarrier
+            const bool tr = ct == 0 && i >= 2 * p.num_kblocks && i < 2 * p.num_kblocks + 4;
+            if (tr) ETRACE(16 + 3 * (i - 2 * p.num_kblocks));
             mbar_wait(&xf_full[f], fphase);
+            if (tr) ETRACE(17 + 3 * (i - 2 * p.num_kblocks));
             const uint32_t src = src0 + (uint32_t)f * kFBytes;
             float4 v[8];
 #pragma unroll
@@ -354,6 +371,7 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
                 pk[t].w = pack_bf16(v[2 * t + 1].z, v[2 * t + 1].w);
             }
             mbar_wait(&x_empty[sx], xphase ^ 1);             // operand stage free (its MMAs retired)
+            if (tr) ETRACE(18 + 3 * (i - 2 * p.num_kblocks));
             const uint32_t dst = dst0 + (uint32_t)sx * kXBytes;
 #pragma unroll
             for (int t = 0; t < 4; ++t) sts128(dst + ((((uint32_t)ch * 4 + t) ^ sw) << 4), pk[t]);
@@ -364,8 +382,8 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(&x_full[sx]);
-            if (++f == kFStages) { f = 0; fphase ^= 1; }
-            if (++sx == kXStages) { sx = 0; xphase ^= 1; }
+            if (++f == p.fstages) { f = 0; fphase ^= 1; }
+            if (++sx == p.xstages) { sx = 0; xphase ^= 1; }
         }
     }
     __syncwarp();
@@ -378,6 +396,11 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
 }
 
 }  // namespace
+
+int read_eval_trace(unsigned long long *out_host) {
+    TS_CUDA_CHECK(cudaMemcpyFromSymbol(out_host, g_eval_trace, sizeof(unsigned long long) * 32));
+    return TS_OK;
+}
 
 bool eval_stream_supported(int D, int H, int C) { return (H == 64 || H == 128 || H == 256) && C >= 1 && C <= CP && D % 8 == 0; }
 
@@ -392,8 +415,17 @@ int launch_eval_stream(const FusedMlpArgs &a, int sm_count, cudaStream_t st) {
     p.atoms = a.H / KATOM;
     p.x_f32 = a.X_f32 != nullptr ? 1 : 0;
     p.w_bytes = (uint32_t)a.H * 128u;
-    const size_t fixed = (size_t)kXStages * kXBytes + kXBytes + (size_t)p.atoms * 2048 + (size_t)a.H * 4 + 1024 + 1024 +
-                         (p.x_f32 ? (size_t)kFStages * kFBytes : 0) + 64;
+    // stage counts: the fp32 staging slots are what is in flight from HBM (Little's law: 6.5 TB/s x ~2 us of loaded latency =
+    // ~90 KB per SM), the W1 stages only have to cover an L2 hit
+    p.fstages = p.x_f32 ? 3 : 0;
+    p.xstages = p.x_f32 ? 2 : 4;
+    if (const char *e = getenv("TSB_EVAL_F")) p.fstages = p.x_f32 ? atoi(e) : 0;
+    if (const char *e = getenv("TSB_EVAL_X")) p.xstages = atoi(e);
+    TS_REQUIRE(p.fstages <= kMaxFStages && p.xstages >= 2 && p.xstages <= kMaxXStages && (!p.x_f32 || p.fstages >= 2), TS_E_INVALID,
+               "streaming evaluate: stage counts %d / %d", p.fstages, p.xstages);
+    const size_t fixed = (size_t)p.xstages * kXBytes + kXBytes + (size_t)p.atoms * 2048 + (size_t)a.H * 4 + 1024 + 1024 +
+                         (size_t)p.fstages * kFBytes + 64;
+    TS_REQUIRE(fixed + 2 * (size_t)p.w_bytes <= 226u * 1024u, TS_E_UNSUPPORTED, "streaming evaluate: shared memory budget does not fit H=%d", a.H);
     p.wstages = (int)((226u * 1024u - fixed) / p.w_bytes);
     if (p.wstages > kMaxWStages) p.wstages = kMaxWStages;
     TS_REQUIRE(p.wstages >= 2, TS_E_UNSUPPORTED, "streaming evaluate: shared memory budget does not fit H=%d", a.H);

@@ -259,6 +259,7 @@ int launch_fused_mlp(const FusedMlpArgs &a, int sm_count, cudaStream_t st);
 // persistent, pipelined evaluate for batches whose slabs are single CTAs (eval_stream.cu); same arguments, evaluate only
 bool eval_stream_supported(int D, int H, int C);
 int launch_eval_stream(const FusedMlpArgs &a, int sm_count, cudaStream_t st);
+int read_eval_trace(unsigned long long *out_host);    // 32 clock64 samples of CTA 0's third slab
 int read_fused_trace(unsigned long long *out_host);   // 32 clock64 samples of CTA 0 of the last launch
 
 }  // namespace tsb
