@@ -535,7 +535,8 @@ def main():
         v_rate = n * args.steps / (v_ms * 1e-3)
         extras['validate_batch65536'] = {'value': world * v_rate, 'unit': 'samples/s', 'per_gpu_streaming_gbs': v_rate * 3152 / 1e9,
                                          'frac_of_hbm_peak': v_rate * 3152 / 1e9 / peak,
-                                         'note': 'validate handler (inference_mode, evaluate + fused metrics), fp32 inputs resident in HBM'}
+                                         'note': 'validate handler (inference_mode, evaluate + fused metrics), fp32 inputs resident in HBM; persistent pipelined '
+                                                 'evaluate kernel (eval_stream.cu) from 148 slabs up'}
 
     # ---- the GPU incumbent: stock PyTorch eager on the same B200, same model / batch / optimizer,
     #      fp32 and under autocast(bf16); plain library code, not part of the product

@@ -344,7 +344,9 @@ eval_stream_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
     } else if (p.x_f32) {
         // ===================== converter warps: fp32 staging slot -> bf16 operand tile, thread = (row, 32-column half) =====================
         const int ct = threadIdx.x - 256;                    // 0..255
-        const int cr = ct >> 1, ch = ct & 1;
+        // 8 consecutive threads = 8 consecutive rows: their 16-byte accesses fall into 8 different bank groups of the swizzled
+        // tiles (row pairs sharing a chunk index made every load and store a 2-way bank conflict: ncu, round 2)
+        const int cr = ct & 127, ch = ct >> 7;
         const uint32_t src0 = smem_u32(f_stage) + (uint32_t)ch * (kFBytes / 2) + (uint32_t)cr * 128;
         const uint32_t dst0 = smem_u32(x_stage) + (uint32_t)cr * 128;
         const uint32_t sw = (uint32_t)(cr & 7);

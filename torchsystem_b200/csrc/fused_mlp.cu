@@ -281,7 +281,9 @@ fused_mlp_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 
         if (p.x_f32) {
             // ---- during the main loop these warps are the fp32 -> bf16 converters: thread = (row, 32-column half)
-            const int cr = et >> 1, ch = et & 1;             // tile row 0..127, which fp32 box
+            // tile row 0..127, which fp32 box. 8 consecutive threads = 8 consecutive rows, so their 16-byte accesses fall into 8
+            // different bank groups of the swizzled tiles (row pairs sharing a chunk index were 2-way bank conflicts)
+            const int cr = et & 127, ch = et >> 7;
             const uint32_t xsrc0 = smem_u32(xstage) + (uint32_t)ch * (kXBytes / 2) + (uint32_t)cr * 128;
             const uint32_t dst0 = smem_u32(tiles) + (uint32_t)cr * 128;
             const uint32_t sw = (uint32_t)(cr & 7);
