@@ -224,10 +224,11 @@ def config4_dp(torch, dist, dev, world, rank, x, y, precision, peaks, steps=6, w
     out = {'model': 'MLP 784-4096x4-10, Adam lr 1e-3, dropout 0.1', 'global_batch': GLOBAL_BATCH_CFG4, 'rows_per_gpu': per,
            'unit': 'samples/s', 'modes': {}}
     n_sets = max(1, min(4, x.shape[0] // per))
-    for mode in (['single'] if world == 1 else ['nvls', 'nvls_overlap', 'nccl']):
+    for mode in (['single'] if world == 1 else ['nvls', 'nvls_overlap', 'nvls_overlap_20sm', 'nccl']):
         try:
-            # 'nvls_overlap': each layer's in-switch reduce + update on a side stream (20 SMs) under the rest of the backward pass
-            os.environ['TSB200_NVLS_OVERLAP_SMS'] = '20' if mode == 'nvls_overlap' else '0'
+            # 'nvls_overlap': each layer's in-switch reduce + update on a side stream under the rest of the backward pass, its CTAs
+            # co-resident with the GEMM CTAs; '_20sm': on 20 SMs taken from the GEMMs instead; 'nvls': one kernel after the backward pass
+            os.environ['TSB200_NVLS_OVERLAP_SMS'] = {'nvls_overlap': '-1', 'nvls_overlap_20sm': '20'}.get(mode, '0')
             torch.manual_seed(0)
             net = MLP(L_DIMS[0], L_DIMS[1:-1], L_DIMS[-1], dropout=DROPOUT, activation=nn.ReLU())
             model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.Adam(net.parameters(), lr=1e-3), precision=precision,

@@ -109,7 +109,7 @@ def test_two_gpu_data_parallel_matches_full_batch_oracle(tmp_path, precision, to
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
-@pytest.mark.parametrize('overlap', ['buckets', 'backward', 'nvls', 'nvls_one_kernel'])
+@pytest.mark.parametrize('overlap', ['buckets', 'backward', 'nvls', 'nvls_reserved_sms', 'nvls_one_kernel'])
 def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
     """'nccl' mode on a net with 2048- and 4096-wide layers: several all-reduce buckets with the optimizer applied bucket by
     bucket (TSB200_DP_BUCKETS=1), or (TSB200_DP_OVERLAP=1) each layer's gradient all-reduced on the side stream while the
@@ -118,7 +118,8 @@ def test_two_gpu_nccl_wide_layers(tmp_path, monkeypatch, overlap):
     monkeypatch.setenv('TSB200_DP_BUCKETS', '1' if overlap == 'buckets' else '0')
     # 'nvls': each layer's in-switch reduce + update on a side stream under the rest of the backward pass (TSB200_NVLS_OVERLAP_SMS,
     # for nets on the layer-by-layer path); 'nvls_one_kernel': the whole buffer in one kernel after the backward pass
-    monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', '0' if overlap == 'nvls_one_kernel' else '20')
+    # ('nvls': the exchange CTAs co-resident with the GEMM CTAs; 'nvls_reserved_sms': on 20 SMs the GEMMs leave free)
+    monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', {'nvls_one_kernel': '0', 'nvls_reserved_sms': '20'}.get(overlap, '-1'))
     import torch.multiprocessing as mp
     from oracle import mlp_numpy as onp
     from tests.test_gpu_parity import synthetic, seeded_init
@@ -144,14 +145,15 @@ def test_two_gpu_nvls_overlap_is_bit_identical_to_one_kernel_adam(tmp_path, monk
     import torch.multiprocessing as mp
     dims, B = (784, 2048, 2048, 1024, 10), 1024
     outs = []
-    for sms in ('20', '0'):
+    for sms in ('-1', '20', '0'):
         monkeypatch.setenv('TSB200_NVLS_OVERLAP_SMS', sms)
-        out = str(tmp_path / f'sms{sms}_rank0.npz')
+        out = str(tmp_path / f'sms{sms.replace("-", "m")}_rank0.npz')
         mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'nvls', out, dims, B, 'adam'), nprocs=2, join=True)
         outs.append([np.load(out.replace('rank0', f'rank{r}')) for r in range(2)])
     for r in range(2):
         for i in range(8):
-            assert np.array_equal(outs[0][r][f'arr_{i}'], outs[1][r][f'arr_{i}']), f'rank {r} tensor {i}: overlap != one kernel'
+            for k in (1, 2):
+                assert np.array_equal(outs[0][r][f'arr_{i}'], outs[k][r][f'arr_{i}']), f'rank {r} tensor {i}: schedule {k} differs'
             assert np.array_equal(outs[0][0][f'arr_{i}'], outs[0][1][f'arr_{i}']), f'tensor {i}: replicas differ'
-        assert np.array_equal(outs[0][r]['exp_avg_0'], outs[1][r]['exp_avg_0'])
+        assert np.array_equal(outs[0][r]['exp_avg_0'], outs[1][r]['exp_avg_0']) and np.array_equal(outs[0][r]['exp_avg_0'], outs[2][r]['exp_avg_0'])
     assert np.array_equal(outs[0][0]['exp_avg_0'], outs[0][1]['exp_avg_0']), 'gathered moments differ between ranks'

@@ -122,6 +122,7 @@ struct ts_mlp {
     cudaStream_t dp_stream = nullptr;
     cudaEvent_t dp_ev_layer[kMaxLayers] = {nullptr}, dp_ev_done = nullptr;
     int nvls_overlap_ctas = 0;            // 0: one whole-buffer kernel after the backward pass
+    bool nvls_coresident = false;         // the exchange CTAs share SMs with the backward GEMM CTAs instead of owning reserved SMs
     uint32_t dp_seq = 0;                  // launch counter of the nvls kernels: the rank barriers count in it
     uint32_t *status_host = nullptr, *status_dev = nullptr;   // mapped pinned words: [0] = row + 1 of a target outside [0, C)
     uint32_t *dp_err_host = nullptr, *dp_err_dev = nullptr;   // mapped pinned word the DP kernels set when a peer never arrives
@@ -571,7 +572,7 @@ int exchange_layer(ts_mlp *m, int l, const int *nsplit, bool first_of_step, cuda
     o.params_mc = m->params_mc;
     o.shadow_mc = m->prec == TS_PREC_BF16 ? m->shadow_mc : nullptr;
     if (m->shadow_alt) { o.shadow = m->shadow_alt; o.shadow_mc = m->shadow_mc_alt; }   // the set the NEXT step reads
-    o.partial_depth = 4;
+    o.partial_depth = m->nvls_coresident ? 0 : 4;
     o.chunk_begin = (int)(m->off[2 * l] / kChunk);
     const int64_t chunk_end = (m->off[2 * l + 1] + round_up(m->cnt[2 * l + 1], kChunk)) / kChunk;
     DpArgs dp{};
@@ -1011,9 +1012,14 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
     // (128 = 148 - 20 GEMM CTAs walk the 1024 tiles of a 8192 x 4096 layer in exactly 8 waves, as many as 132 would)
     // Measured on 8 B200s (L model, 8,192 rows per GPU): 2.78 ms per step with 20 SMs against 2.99 ms for the one-kernel
     // exchange; on 2 GPUs, where every rank owns half of the update, the side kernel outlasts the backward pass (3.34 vs 3.05 ms).
-    int ov_sms = world >= 4 ? 20 : 0;
+    // TSB200_NVLS_OVERLAP_SMS = n > 0: n fat exchange CTAs on n SMs taken from the backward GEMMs (2.78 ms); = -1 (the default
+    // from 4 ranks up): co-resident -- the GEMM kernels are capped at 128 registers per thread, so a 256-thread exchange CTA
+    // fits on the same SM next to a GEMM CTA and no SM is reserved; 0: off.
+    int ov_sms = world >= 4 ? -1 : 0;
     if (const char *e = getenv("TSB200_NVLS_OVERLAP_SMS")) ov_sms = atoi(e);
-    if (world > 1 && ov_sms > 0 && ov_sms < m->sm_count / 2 && m->tc_head && !m->fused && m->n_layers > 2) {
+    m->nvls_coresident = ov_sms < 0;
+    if (ov_sms < 0) ov_sms = m->sm_count - 16;
+    if (world > 1 && ov_sms > 0 && (m->nvls_coresident || ov_sms < m->sm_count / 2) && m->tc_head && !m->fused && m->n_layers > 2) {
         TS_CUDA_CHECK(cudaSetDevice(m->device));
         if (m->dp_stream == nullptr) {
             int lo = 0, hi = 0;
@@ -1023,7 +1029,7 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
             TS_CUDA_CHECK(cudaEventCreateWithFlags(&m->dp_ev_done, cudaEventDisableTiming));
         }
         m->nvls_overlap_ctas = ov_sms;
-        m->bwd_sms = m->sm_count - ov_sms;
+        m->bwd_sms = m->nvls_coresident ? m->sm_count : m->sm_count - ov_sms;
     }
     return ensure_dp_error_word(m);
 }

@@ -904,7 +904,8 @@ __global__ void __launch_bounds__(kLayerThreads, 1) nvls_layer_kernel(OptArgs p,
     extern __shared__ float4 slots[];
     uint32_t *own = dp.flags[dp.rank];
     const int tid = threadIdx.x & 255, grp = threadIdx.x >> 8;
-    const int vblock = blockIdx.x * kLayerGroups + grp, vgrid = gridDim.x * kLayerGroups;
+    const int groups = (int)blockDim.x >> 8;                 // 4 (fat CTAs on reserved SMs) or 1 (co-resident with the GEMM CTAs)
+    const int vblock = blockIdx.x * groups + grp, vgrid = gridDim.x * groups;
     // 1. this rank's split partials of the range (hidden-layer bias gradients in bf16 mode) into its gradient buffer
     for (int c = vblock; c < n_chunks; c += vgrid) {
         const int chunk = p.chunk_begin + c;
@@ -916,7 +917,15 @@ __global__ void __launch_bounds__(kLayerThreads, 1) nvls_layer_kernel(OptArgs p,
         if (j0 >= d.count || d.nsplit <= 0) continue;
         const int n = (int)min((int64_t)4, d.count - j0);
         float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-        sum_partials(p.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, p.partial_depth, kLayerThreads);
+        if (p.partial_depth > 0) {
+            sum_partials(p.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, p.partial_depth, blockDim.x);
+        } else {    // co-resident launch: no shared memory to stage through; these are the bias tensors, a few thousand elements
+            const float *q = p.partials + d.partial_off + j0;
+            for (int sp = 0; sp < d.nsplit; ++sp) {
+                const float4 t = *reinterpret_cast<const float4 *>(q + (int64_t)sp * d.partial_stride);
+                g[0] += t.x; g[1] += t.y; g[2] += t.z; g[3] += t.w;
+            }
+        }
         *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], n > 1 ? g[1] : 0.0f, n > 2 ? g[2] : 0.0f, n > 3 ? g[3] : 0.0f);
     }
     if (!rank_barrier(own, dp, 8, 2u * dp.step, false)) return;
@@ -962,6 +971,14 @@ int launch_nvls_layer(const OptArgs &a, const DpArgs &dp, const float *grads_mc,
         done[dev & 63] = true;
     }
     TS_REQUIRE(a.partial_depth <= 4, TS_E_INVALID, "nvls layer exchange runs at partial depth <= 4");
+    if (a.partial_depth == 0) {
+        // co-resident form: 256 threads x 64 registers and no dynamic shared memory per CTA, so a CTA fits on an SM NEXT TO a
+        // persistent GEMM CTA (352 threads x <= 128 registers, 225 KiB): no SM has to be taken from the backward pass
+        int64_t grid = n_chunks < n_ctas ? n_chunks : n_ctas;
+        nvls_layer_kernel<<<dim3((unsigned)grid), dim3(256), 0, st>>>(a, dp, grads_mc, (int)n_chunks);
+        TS_LAUNCH_CHECK();
+        return TS_OK;
+    }
     int64_t grid = (n_chunks + kLayerGroups - 1) / kLayerGroups;
     if (grid > n_ctas) grid = n_ctas;
     nvls_layer_kernel<<<dim3((unsigned)grid), dim3(kLayerThreads), smem, st>>>(a, dp, grads_mc, (int)n_chunks);

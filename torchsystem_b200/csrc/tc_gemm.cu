@@ -57,8 +57,10 @@ struct TcParams {
 // TMEM buffers, so the epilogue of tile i (TMEM -> registers -> bias/dropout/ReLU or ReLU' -> global) runs while the
 // producers and the MMA issuer are already in the main loop of tile i+1. With one tile per CTA the epilogue was fully
 // exposed: 333 us instead of 241 us for the forward layer of the L model, 411 us for its dX layer.
+// At most 128 registers per thread (352 x 128 = 45 K of the SM's 64 K): a small second kernel -- the per-layer NVLS exchange of
+// data-parallel training, 256 threads x 64 registers -- can then be resident on the same SM next to a GEMM CTA.
 template <int EPI>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __maxnreg__(128)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcParams p) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kMaxStages];
