@@ -215,9 +215,9 @@ int64_t ts_mlp_shadow_elems(const ts_mlp *m);
 int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_local, const float *grads_mc, float *params_local,
                         float *params_mc, void *shadow_local, void *shadow_mc, uint32_t *const *flag_bufs /*HOST*/);
 /* Optional second set of bf16 shadows (symmetric memory + its multicast mapping, ts_mlp_shadow_elems() elements; no
- * counterpart in the reference). With TSB200_NVLS_OVERLAP_SMS=n when ts_dp_bind_nvls runs (default 20 from 4 ranks up, else 0 = off), nets on the layer-by-layer path
- * exchange every layer on a side stream, on n SMs the backward GEMMs leave free, while the backward pass of the layers below
- * is still running. With ONE shadow set a layer's exchange has to wait for the dX GEMM that still reads its weights; with
+ * counterpart in the reference). Nets on the layer-by-layer path exchange every layer on a side stream while the backward pass
+ * of the layers below is still running (TSB200_NVLS_OVERLAP_SMS when ts_dp_bind_nvls runs: -1, the default, = exchange CTAs
+ * co-resident with the GEMM CTAs; n > 0 = on n SMs the backward GEMMs leave free; 0 = off, one kernel after the backward pass). With ONE shadow set a layer's exchange has to wait for the dX GEMM that still reads its weights; with
  * two, step s writes the set step s+1 reads and the exchange starts as soon as the layer's dW is enqueued. Call
  * ts_mlp_sync_weights afterwards. */
 int32_t ts_dp_nvls_second_shadow(ts_mlp *m, void *shadow2_local, void *shadow2_mc);

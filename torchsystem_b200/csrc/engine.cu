@@ -1010,12 +1010,11 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
     // Wide nets (layer-by-layer tensor-core path): exchange each layer on a side stream while the backward pass of the
     // layers below is still running, on TSB200_NVLS_OVERLAP_SMS SMs (default: 20 from 4 ranks up, 0 = off below) that the backward GEMMs leave free.
     // (128 = 148 - 20 GEMM CTAs walk the 1024 tiles of a 8192 x 4096 layer in exactly 8 waves, as many as 132 would)
-    // Measured on 8 B200s (L model, 8,192 rows per GPU): 2.78 ms per step with 20 SMs against 2.99 ms for the one-kernel
-    // exchange; on 2 GPUs, where every rank owns half of the update, the side kernel outlasts the backward pass (3.34 vs 3.05 ms).
-    // TSB200_NVLS_OVERLAP_SMS = n > 0: n fat exchange CTAs on n SMs taken from the backward GEMMs (2.78 ms); = -1 (the default
-    // from 4 ranks up): co-resident -- the GEMM kernels are capped at 128 registers per thread, so a 256-thread exchange CTA
-    // fits on the same SM next to a GEMM CTA and no SM is reserved; 0: off.
-    int ov_sms = world >= 4 ? -1 : 0;
+    // TSB200_NVLS_OVERLAP_SMS = -1 (the default): co-resident -- the GEMM kernels are capped at 128 registers per thread, so a
+    // 256-thread exchange CTA fits on the same SM next to a GEMM CTA and no SM is reserved (L model, 8,192 rows per GPU: 2.50 ms
+    // per step on 8 B200s, 2.51 ms on 2); = n > 0: n fat exchange CTAs on n SMs taken from the backward GEMMs (2.79 ms on 8 GPUs,
+    // 3.34 ms on 2); 0: off, one whole-buffer kernel after the backward pass (3.02 / 3.05 ms).
+    int ov_sms = world >= 2 ? -1 : 0;
     if (const char *e = getenv("TSB200_NVLS_OVERLAP_SMS")) ov_sms = atoi(e);
     m->nvls_coresident = ov_sms < 0;
     if (ov_sms < 0) ov_sms = m->sm_count - 16;
