@@ -122,7 +122,9 @@ struct ts_mlp {
     cudaStream_t dp_stream = nullptr;
     cudaEvent_t dp_ev_layer[kMaxLayers] = {nullptr}, dp_ev_done = nullptr;
     int nvls_overlap_ctas = 0;            // 0: one whole-buffer kernel after the backward pass
-    bool nvls_coresident = false;         // the exchange CTAs share SMs with the backward GEMM CTAs instead of owning reserved SMs
+    bool nvls_coresident = false;
+    int local_overlap = 1;                // single GPU, layer-by-layer path: each layer's optimizer update on the side stream under the
+                                          // rest of the backward pass (TSB200_OPT_OVERLAP=0: one optimizer launch at the end)         // the exchange CTAs share SMs with the backward GEMM CTAs instead of owning reserved SMs
     uint32_t dp_seq = 0;                  // launch counter of the nvls kernels: the rank barriers count in it
     uint32_t *status_host = nullptr, *status_dev = nullptr;   // mapped pinned words: [0] = row + 1 of a target outside [0, C)
     uint32_t *dp_err_host = nullptr, *dp_err_dev = nullptr;   // mapped pinned word the DP kernels set when a peer never arrives
@@ -183,7 +185,10 @@ int64_t carve(ts_mlp *m, void *base, int64_t Bm) {
         m->x_bf16 = (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2);
         m->x_bf16_alt = m->fused ? (__nv_bfloat16 *)c.take(Bm * m->dims[0] * 2) : nullptr;
         __nv_bfloat16 *ws_shadow = (__nv_bfloat16 *)c.take(m->shadow_total * 2);
-        if (!m->shadow_ext) m->shadow = ws_shadow;         // NVLS data parallel keeps the shadows in symmetric memory (m->shadow set at bind)
+        // nets on the layer-by-layer path keep a second set: a layer's update (side stream) writes the set the NEXT step reads
+        // while this step's dX GEMM still reads the current one
+        __nv_bfloat16 *ws_shadow2 = (!m->fused && m->n_layers > 2) ? (__nv_bfloat16 *)c.take(m->shadow_total * 2) : nullptr;
+        if (!m->shadow_ext) { m->shadow = ws_shadow; m->shadow_alt = ws_shadow2; }   // NVLS data parallel keeps its own sets in symmetric memory
     }
     if (m->tc_head) {
         m->zbuf = (float *)c.take(Bm * 16 * 4);
@@ -560,6 +565,35 @@ int ensure_dp_error_word(ts_mlp *m) {
     return TS_OK;
 }
 
+int ensure_side_stream(ts_mlp *m) {
+    if (m->dp_stream != nullptr) return TS_OK;
+    TS_CUDA_CHECK(cudaSetDevice(m->device));
+    int lo = 0, hi = 0;
+    TS_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    TS_CUDA_CHECK(cudaStreamCreateWithPriority(&m->dp_stream, cudaStreamNonBlocking, hi));   // its small CTAs go first
+    for (int l = 0; l < m->n_layers; ++l) TS_CUDA_CHECK(cudaEventCreateWithFlags(&m->dp_ev_layer[l], cudaEventDisableTiming));
+    TS_CUDA_CHECK(cudaEventCreateWithFlags(&m->dp_ev_done, cudaEventDisableTiming));
+    return TS_OK;
+}
+
+// Single GPU, layer-by-layer path: the optimizer update of layer l's tensors on the side stream, ordered behind everything
+// enqueued on `st` so far, by CTAs small enough to share SMs with the backward GEMMs that are still running.
+int update_layer(ts_mlp *m, int l, const int *nsplit, bool first_of_step, cudaStream_t st) {
+    OptArgs o{};
+    bool any_partial = false;
+    int rc = fill_tensor_table(m, nsplit, o, &any_partial, st, 2 * l, 2 * l + 2);
+    if (rc) return rc;
+    o.update = 1; o.grad_scale = 1.0f;
+    fill_update(m, o, first_of_step);
+    o.shadow = m->shadow_alt;                            // the set the NEXT step reads
+    o.partial_depth = 0;
+    o.chunk_begin = (int)(m->off[2 * l] / kChunk);
+    const int64_t chunk_end = (m->off[2 * l + 1] + round_up(m->cnt[2 * l + 1], kChunk)) / kChunk;
+    TS_CUDA_CHECK(cudaEventRecord(m->dp_ev_layer[l], st));
+    TS_CUDA_CHECK(cudaStreamWaitEvent(m->dp_stream, m->dp_ev_layer[l], 0));
+    return launch_layer_optimizer(o, chunk_end - o.chunk_begin, m->sm_count - 16, m->dp_stream);
+}
+
 // nvls overlap: reduce + update of layer l's tensors (weight and bias) on the side stream, ordered behind everything
 // enqueued on `st` so far. Called once the layer's gradients are enqueued AND nothing enqueued later reads its weights.
 int exchange_layer(ts_mlp *m, int l, const int *nsplit, bool first_of_step, cudaStream_t st) {
@@ -709,8 +743,17 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
     if (rc) return rc;
     // nvls overlap (wide nets, tensor-core last layer): W_last was last read by tc_head_backward, already enqueued
     const bool ov = dp && m->nvls && m->nvls_overlap_ctas > 0 && tc_head;
+    // single GPU: the same schedule with a plain per-layer optimizer kernel (needs the second shadow set of the workspace)
+    const bool ov_local = !dp && update && tc_head && m->local_overlap && m->shadow_alt != nullptr && !m->shadow_ext &&
+                          m->ov_events == nullptr;
     if (ov) {
         rc = exchange_layer(m, L - 1, nsplit, true, st);
+        if (rc) return rc;
+    }
+    if (ov_local) {
+        rc = ensure_side_stream(m);
+        if (rc) return rc;
+        rc = update_layer(m, L - 1, nsplit, true, st);
         if (rc) return rc;
     }
     int cur = 0;
@@ -760,6 +803,10 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
             rc = exchange_layer(m, l, nsplit, false, st);
             if (rc) return rc;
         }
+        if (ov_local) {
+            rc = update_layer(m, l, nsplit, false, st);
+            if (rc) return rc;
+        }
         if (l > 0) {   // dH_{l-1} = (dH_l W_l) * act'(layer l-1) * keep/(1-p)
             const DropoutSpec ds = drop_spec(m, masks, seed, l - 1, true);
             ProfScope ps(K_DX_GEMM, st);
@@ -796,7 +843,7 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
             if (rc) return rc;
         }
     }
-    if (ov) {       // the next forward pass reads every parameter: the compute stream waits for the last exchange
+    if (ov || ov_local) {       // the next forward pass reads every parameter: the compute stream waits for the last exchange / update
         TS_CUDA_CHECK(cudaEventRecord(m->dp_ev_done, m->dp_stream));
         TS_CUDA_CHECK(cudaStreamWaitEvent(st, m->dp_ev_done, 0));
         if (m->shadow_alt) {   // the set just written becomes the one the next step reads
@@ -854,6 +901,7 @@ int32_t ts_mlp_create(ts_mlp **out, const int32_t *dims, int32_t n_dims, int32_t
     if (const char *e = getenv("TSB200_STEP_KERNEL")) m->step_kernel = atoi(e) != 0 ? 1 : 0;
     if (const char *e = getenv("TSB200_WGRAD_UPDATE")) m->wgrad_update = atoi(e) != 0 ? 1 : 0;
     if (const char *e = getenv("TSB200_EVAL_STREAM")) m->eval_stream = atoi(e) != 0 ? 1 : 0;
+    if (const char *e = getenv("TSB200_OPT_OVERLAP")) m->local_overlap = atoi(e) != 0 ? 1 : 0;
     m->n_tensors = 2 * m->n_layers;
     int64_t o = 0, so = 0;
     for (int l = 0; l < m->n_layers; ++l) {
@@ -1006,6 +1054,7 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
     m->grads_mc = grads_mc; m->params_mc = params_mc;
     m->shadow_ext = (__nv_bfloat16 *)shadow_local; m->shadow_mc = (__nv_bfloat16 *)shadow_mc;
     if (m->shadow_ext) m->shadow = m->shadow_ext;
+    m->shadow_alt = nullptr; m->shadow_mc_alt = nullptr;     // the workspace's second set is not symmetric memory (ts_dp_nvls_second_shadow)
     m->dp_world = world; m->dp_rank = rank; m->nvls = true;
     // Wide nets (layer-by-layer tensor-core path): exchange each layer on a side stream while the backward pass of the
     // layers below is still running, on TSB200_NVLS_OVERLAP_SMS SMs (default: 20 from 4 ranks up, 0 = off below) that the backward GEMMs leave free.
@@ -1019,14 +1068,8 @@ int32_t ts_dp_bind_nvls(ts_mlp *m, int32_t rank, int32_t world, float *grads_loc
     m->nvls_coresident = ov_sms < 0;
     if (ov_sms < 0) ov_sms = m->sm_count - 16;
     if (world > 1 && ov_sms > 0 && (m->nvls_coresident || ov_sms < m->sm_count / 2) && m->tc_head && !m->fused && m->n_layers > 2) {
-        TS_CUDA_CHECK(cudaSetDevice(m->device));
-        if (m->dp_stream == nullptr) {
-            int lo = 0, hi = 0;
-            TS_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-            TS_CUDA_CHECK(cudaStreamCreateWithPriority(&m->dp_stream, cudaStreamNonBlocking, hi));   // its few CTAs go first
-            for (int l = 0; l < m->n_layers; ++l) TS_CUDA_CHECK(cudaEventCreateWithFlags(&m->dp_ev_layer[l], cudaEventDisableTiming));
-            TS_CUDA_CHECK(cudaEventCreateWithFlags(&m->dp_ev_done, cudaEventDisableTiming));
-        }
+        int rc = ensure_side_stream(m);
+        if (rc) return rc;
         m->nvls_overlap_ctas = ov_sms;
         m->bwd_sms = m->nvls_coresident ? m->sm_count : m->sm_count - ov_sms;
     }

@@ -142,6 +142,8 @@ int launch_nvls_optimizer(const OptArgs &a, const DpArgs &dp, const float *grads
 
 // one layer's chunk range [a.chunk_begin, a.chunk_begin + n_chunks) of the same exchange, on `n_ctas` CTAs (side stream, overlap)
 int launch_nvls_layer(const OptArgs &a, const DpArgs &dp, const float *grads_mc, int64_t n_chunks, int n_ctas, cudaStream_t st);
+// the single-GPU counterpart: one layer's chunk range updated by CTAs that share SMs with the backward GEMMs (side stream)
+int launch_layer_optimizer(const OptArgs &a, int64_t n_chunks, int n_ctas, cudaStream_t st);
 
 int launch_cast_bf16(const float *src, __nv_bfloat16 *dst, int64_t n, cudaStream_t st, bool wait_at_end = false);
 // uint8 -> lut[byte], written as bf16 (dst_bf16) or fp32 (dst_f32); exactly one destination is non-null

@@ -959,6 +959,46 @@ __global__ void __launch_bounds__(kLayerThreads, 1) nvls_layer_kernel(OptArgs p,
     (void)rank_barrier(own, dp, 9, 2u * dp.step + 1u, true);
 }
 
+// =====================================================================================
+// One layer's optimizer update on a single GPU, co-resident with the backward GEMMs of the layers below (side stream): the
+// chunk range [chunk_begin, chunk_begin + n_chunks) of the flat buffers, 256 threads and at most 64 registers per thread, no
+// dynamic shared memory, so a CTA fits on an SM next to a persistent GEMM CTA (which is capped at 128 registers).
+// =====================================================================================
+__global__ void __maxnreg__(64) layer_optimizer_kernel(OptArgs p, int n_chunks) {
+    for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+        const int chunk = p.chunk_begin + c;
+        const int tix = p.chunk_tensor[chunk];
+        if (tix < 0) continue;
+        const TensorDesc d = p.t[tix];
+        const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+        const int64_t j0 = i0 - d.offset;
+        if (j0 >= d.count) continue;
+        const int n = (int)min((int64_t)4, d.count - j0);
+        float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (d.nsplit > 0) {      // split partials (bias tensors; small weight matrices): summed in order, straight from global memory
+            const float *q = p.partials + d.partial_off + j0;
+            for (int sp = 0; sp < d.nsplit; ++sp) {
+                const float4 t = *reinterpret_cast<const float4 *>(q + (int64_t)sp * d.partial_stride);
+                g[0] += t.x; g[1] += t.y; g[2] += t.z; g[3] += t.w;
+            }
+            if (n == 4) *reinterpret_cast<float4 *>(p.grads + i0) = make_float4(g[0], g[1], g[2], g[3]);
+            else for (int e = 0; e < n; ++e) p.grads[i0 + e] = g[e];
+        } else {
+            const float4 t = *reinterpret_cast<const float4 *>(p.grads + i0);
+            g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
+        }
+        apply_update(p, d, i0, j0, n, g);
+    }
+}
+
+int launch_layer_optimizer(const OptArgs &a, int64_t n_chunks, int n_ctas, cudaStream_t st) {
+    TS_REQUIRE(n_chunks >= 1 && n_ctas >= 1, TS_E_INVALID, "layer optimizer: %lld chunks, %d CTAs", (long long)n_chunks, n_ctas);
+    const int64_t grid = n_chunks < n_ctas ? n_chunks : n_ctas;
+    layer_optimizer_kernel<<<dim3((unsigned)grid), dim3(256), 0, st>>>(a, (int)n_chunks);
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
 int launch_nvls_layer(const OptArgs &a, const DpArgs &dp, const float *grads_mc, int64_t n_chunks, int n_ctas, cudaStream_t st) {
     TS_REQUIRE(grads_mc != nullptr && a.params_mc != nullptr, TS_E_INVALID, "nvls optimizer: multicast mappings missing");
     TS_REQUIRE(n_ctas >= 1 && n_chunks >= 1, TS_E_INVALID, "nvls layer exchange: %d CTAs, %lld chunks", n_ctas, (long long)n_chunks);
