@@ -652,11 +652,13 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
         if (rc) return rc;
         f.opt.update = 1; f.opt.grad_scale = 1.0f;
         fill_update(m, f.opt);
-        m->step_flag += (unsigned int)(m->dims[1] / 64);       // every CTA of the compute cluster adds one
-        f.flag = m->ticket + 16; f.flag_target = m->step_flag;
+        const unsigned int target = m->step_flag + (unsigned int)(m->dims[1] / 64);   // every CTA of the compute cluster adds one
+        f.flag = m->ticket + 16; f.flag_target = target;
         f.n_chunks = (int)m->n_chunks; f.sm_count = m->sm_count;
         ProfScope ps(K_STEP, st);
-        return launch_fit_step(f, st);
+        rc = launch_fit_step(f, st);
+        if (rc == TS_OK) m->step_flag = target;                // a launch that did not happen must not move the counter's target
+        return rc;
     }
     if (m->fused) {
         rc = fused_forward(m, x, x_dtype, y, B, masks, seed, true, pred, rec, &a0, st);
