@@ -157,3 +157,51 @@ def test_two_gpu_nvls_overlap_is_bit_identical_to_one_kernel_adam(tmp_path, monk
             assert np.array_equal(outs[0][0][f'arr_{i}'], outs[0][1][f'arr_{i}']), f'tensor {i}: replicas differ'
         assert np.array_equal(outs[0][r]['exp_avg_0'], outs[1][r]['exp_avg_0']) and np.array_equal(outs[0][r]['exp_avg_0'], outs[2][r]['exp_avg_0'])
     assert np.array_equal(outs[0][0]['exp_avg_0'], outs[0][1]['exp_avg_0']), 'gathered moments differ between ranks'
+
+
+def _late_peer_worker(rank, world, port, precision, out):
+    import torch.distributed as dist
+    from torch import nn
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), TSB200_DP_TIMEOUT_S='1.5')
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+    from torchsystem_b200 import B200Classifier, MLP, TsError
+    from tests.test_gpu_parity import synthetic
+    B = 1024
+    x, y = synthetic(B)
+    torch.manual_seed(0)
+    net = MLP(784, 256, 10, dropout=0.0, activation=nn.ReLU())
+    model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.SGD(net.parameters(), lr=0.05), precision=precision,
+                           device=f'cuda:{rank}', max_batch=B, dp_mode='p2p')
+    xb, yb = x.cuda(), y.cuda()
+    model.fit(xb, yb)                                   # step 1: both ranks
+    torch.cuda.synchronize()
+    w1 = net.linears()[0].weight.detach().clone()
+    result = 'none'
+    if rank == 0:
+        model.fit(xb, yb)                               # step 2: rank 1 never comes
+        torch.cuda.synchronize()                        # returns: the kernel gave up after 1.5 s, it did not trap
+        unchanged = torch.equal(w1, net.linears()[0].weight.detach())
+        try:
+            model.fit(xb, yb)
+            result = 'no error'
+        except TsError as e:
+            result = f'{"timeout" if "did not arrive" in str(e) and "-6" in str(e) else "other"}|unchanged={unchanged}|{str(e)[:160]}'
+        torch.zeros(1, device='cuda').sum().item()      # the context is still usable
+        with open(out, 'w') as f:
+            f.write(result)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
+@pytest.mark.parametrize('precision', ['bf16', 'f32'])
+def test_a_peer_that_never_arrives_is_a_status_not_a_trap(tmp_path, precision):
+    """A rank whose peer does not reach the step within the configured time (TSB200_DP_TIMEOUT_S) skips that step's update
+    and reports TS_E_TIMEOUT at its next call; nothing traps, the CUDA context survives (bf16: the dW1 + update kernel's
+    in-kernel exchange; f32: dp_optimizer_kernel)."""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / 'result.txt')
+    mp.spawn(_late_peer_worker, args=(2, _free_port(), precision, out), nprocs=2, join=True)
+    result = open(out).read()
+    assert result.startswith('timeout|unchanged=True'), result
