@@ -104,6 +104,7 @@ class B200Classifier(Aggregate):
         # optimizer.state_dict() must show the live step count (the moments alias the engine's buffers already)
         optimizer.register_state_dict_pre_hook(self._before_state_dict)
         self._state_gathered_at = -1
+        self._last_phase = None
         self._dp = parallel.DataParallel(process_group)
         self._p2p = None
         self._overlap = False
@@ -139,10 +140,13 @@ class B200Classifier(Aggregate):
     def onphase(self) -> None:
         # weights may have been replaced between phases (repository.restore -> load_state_dict)
         self.engine.sync_weights()
-        # data parallel: line the ranks up on the host at every phase boundary. Rank 0 may come out of an I/O consumer
-        # (storage.py:84-86 saves on every Iterated) seconds after the others; they then wait here, in the process group's
-        # barrier, not inside a spinning optimizer kernel.
-        self._dp.barrier()
+        # data parallel: line the ranks up on the host whenever the phase CHANGES (train -> evaluation -> train ...). Rank 0 may
+        # come out of an I/O consumer (storage.py:84-86 saves on every Iterated) seconds after the others; they then wait
+        # here, in the process group's barrier, not inside a spinning optimizer kernel. Setting the same phase again (a handler
+        # called twice in a row) costs nothing.
+        if self.phase != self._last_phase:
+            self._last_phase = self.phase
+            self._dp.barrier()
 
     def sync(self) -> None:
         """Call after editing `nn`'s weights by hand; re-derives the bf16 operand copies."""
