@@ -35,6 +35,15 @@ CASES = [
     (0, 0, 1000, 16, 512, 1),          # tensor-core head: logits against the [16, K] padded last-layer weights
     (0, 1, 1000, 384, 16, 1),          # tensor-core head: dA = dZ W_last, contraction over the 16 padded classes
     (1, 1, 384, 16, 1000, 3),          # tensor-core head: dW_last^T = A^T dZ, batch split
+    # 256-wide tiles with M >= 256: the CTA-pair (cta_group::2) kernel, every operand-major combination, ragged tails
+    (0, 0, 2048, 4096, 1024, 1),       # L-model forward
+    (0, 1, 2048, 4096, 1024, 1),       # L-model dX
+    (1, 1, 4096, 4096, 2048, 1),       # L-model dW
+    (1, 0, 2048, 4096, 512, 1),
+    (0, 0, 2000, 4000, 1000, 1),       # ragged M (the peer CTA's rows run out), N and K
+    (1, 1, 2040, 4000, 1000, 1),
+    (0, 0, 300, 37888, 64, 1),         # second CTA of the last pair mostly out of range; many column tiles per pair
+    (1, 1, 4096, 4096, 2048, 2),       # pairs with split-K
 ]
 
 

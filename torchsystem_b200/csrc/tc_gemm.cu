@@ -32,6 +32,7 @@ constexpr int kMaxStages = 8;
 
 struct TcParams {
     int M, N, K, BN;
+    int BNh;                   // columns of B this CTA holds: BN, or BN / 2 in a CTA pair
     int BK;                    // K elements per pipeline stage: 64 or 128
     int num_kblocks, kblocks_per_split;
     int tiles_m, tiles_n, splits;
@@ -59,7 +60,12 @@ struct TcParams {
 // exposed: 333 us instead of 241 us for the forward layer of the L model, 411 us for its dX layer.
 // At most 128 registers per thread (352 x 128 = 45 K of the SM's 64 K): a small second kernel -- the per-layer NVLS exchange of
 // data-parallel training, 256 threads x 64 registers -- can then be resident on the same SM next to a GEMM CTA.
-template <int EPI>
+// TWO: a CTA pair (cluster of 2) works on a 256 x BN tile with tcgen05.mma.cta_group::2 -- each CTA stages its own 128 rows
+// of A and HALF of B (BN / 2 columns), so the shared-memory traffic per FLOP of the B operand halves (one CTA alone moves
+// 96 KB through shared memory per 64-wide K block of a 128 x 256 tile, ~750 cycles at 128 B/cycle against 512 cycles of tensor
+// time; a pair moves 64 KB per CTA). The leader (cluster rank 0) owns the full barriers and issues every MMA; completion is
+// committed to the barriers of both CTAs; each CTA drains its own rows of the accumulator from its own tensor memory.
+template <int EPI, bool TWO>
 __global__ void __maxnreg__(128)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -74,6 +80,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role id
     const int katoms = p.BK / KATOM;
     const int tiles_mn = p.tiles_m * p.tiles_n, total_tiles = tiles_mn * p.splits;
+    const uint32_t cta_rank = TWO ? cluster_ctarank() : 0u;
+    const int unit = TWO ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;          // which CTA (pair) of the persistent grid
+    const int n_units = TWO ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    constexpr int BMT = TWO ? 2 * BM : BM;                                    // rows of a tile
     unsigned long long *dbg = (p.dbg && blockIdx.x == 0) ? p.dbg : nullptr;     // CTA 0, first tile only
     unsigned long long cta_t0 = 0;
     if (dbg && threadIdx.x == 0) dbg[0] = clock64();
@@ -85,12 +95,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }   // A + B producers arrive
-        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full_bar[b], 1); mbar_init(&tmem_empty_bar[b], kEpiWarps); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full_bar[b], 1); mbar_init(&tmem_empty_bar[b], TWO ? 2 * kEpiWarps : kEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_a)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_b)) : "memory");
     }
-    if (warp == 1) tmem_alloc(&tmem_base_slot, p.tmem_cols);
+    if (TWO) cluster_sync_all();      // the peer's barriers exist before anything can signal them
+    if (warp == 1) { if (TWO) tmem_alloc2(&tmem_base_slot, p.tmem_cols); else tmem_alloc(&tmem_base_slot, p.tmem_cols); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -103,7 +114,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #define TS_TILE_COORDS(t)                                                       \
     const int z_ = (t) / tiles_mn, r_ = (t) - z_ * tiles_mn;                    \
     const int tm_ = r_ / p.tiles_n, tn_ = r_ - tm_ * p.tiles_n;                 \
-    const int m0 = tm_ * BM, n0 = tn_ * p.BN;                                   \
+    const int m0 = tm_ * BMT + (int)cta_rank * BM, n0 = tn_ * p.BN;             \
     const int kb_begin = z_ * p.kblocks_per_split;                              \
     const int kb_end = min(p.num_kblocks, kb_begin + p.kblocks_per_split);      \
     (void)m0; (void)n0;
@@ -112,20 +123,25 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         // ===================== TMA producer, operand A (whole warp loops; one elected lane issues) =====================
         int s = 0;
         uint32_t phase = 0;
-        for (int t = blockIdx.x, it = 0; t < total_tiles; t += gridDim.x, ++it) {
+        for (int t = unit, it = 0; t < total_tiles; t += n_units, ++it) {
             TS_TILE_COORDS(t)
             for (int kb = kb_begin; kb < kb_end; ++kb) {
                 if (elect_one()) {
                     mbar_wait(&empty_bar[s], phase ^ 1);
                     uint8_t *sa = tiles + (size_t)s * stage_bytes;
-                    mbar_expect_tx(&full_bar[s], p.a_bytes);
+                    // pair: the leader arms its barrier for both CTAs' bytes; the peer's loads are counted there too
+                    if (!TWO) mbar_expect_tx(&full_bar[s], p.a_bytes);
+                    else if (cta_rank == 0) mbar_expect_tx(&full_bar[s], 2u * p.a_bytes);
                     const int k0 = kb * p.BK;
+                    auto load = [&](void *dst, int c0, int c1) {
+                        if (TWO) tma_load_2d_pair(&tma_a, &full_bar[s], dst, c0, c1); else tma_load_2d(&tma_a, &full_bar[s], dst, c0, c1);
+                    };
                     if (p.a_major == TC_MAJOR_K) {
                         for (int a = 0; a < katoms; ++a)                                   // boxes 64(K) x 128(M), one per K atom
-                            tma_load_2d(&tma_a, &full_bar[s], sa + (size_t)a * BM * 128, k0 + a * KATOM, m0);
+                            load(sa + (size_t)a * BM * 128, k0 + a * KATOM, m0);
                     } else {
-                        tma_load_2d(&tma_a, &full_bar[s], sa, m0, k0);                     // two boxes 64(M) x BK(K)
-                        tma_load_2d(&tma_a, &full_bar[s], sa + (size_t)p.BK * 128, m0 + 64, k0);
+                        load(sa, m0, k0);                                                  // two boxes 64(M) x BK(K)
+                        load(sa + (size_t)p.BK * 128, m0 + 64, k0);
                     }
                     if (dbg && it == 0 && kb - kb_begin < 8) dbg[40 + (kb - kb_begin)] = clock64();
                 }
@@ -137,38 +153,43 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         // ===================== TMA producer, operand B =====================
         int s = 0;
         uint32_t phase = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        for (int t = unit; t < total_tiles; t += n_units) {
             TS_TILE_COORDS(t)
+            const int nb = n0 + (int)cta_rank * p.BNh;                                     // pair: this CTA's half of the tile's columns
             for (int kb = kb_begin; kb < kb_end; ++kb) {
                 if (elect_one()) {
                     mbar_wait(&empty_bar[s], phase ^ 1);
                     uint8_t *sb = tiles + (size_t)s * stage_bytes + p.a_bytes;
-                    mbar_expect_tx(&full_bar[s], p.b_bytes);
+                    if (!TWO) mbar_expect_tx(&full_bar[s], p.b_bytes);
+                    else if (cta_rank == 0) mbar_expect_tx(&full_bar[s], 2u * p.b_bytes);
                     const int k0 = kb * p.BK;
+                    auto load = [&](void *dst, int c0, int c1) {
+                        if (TWO) tma_load_2d_pair(&tma_b, &full_bar[s], dst, c0, c1); else tma_load_2d(&tma_b, &full_bar[s], dst, c0, c1);
+                    };
                     if (p.b_major == TC_MAJOR_K) {
-                        for (int a = 0; a < katoms; ++a)                                   // boxes 64(K) x BN(N), one per K atom
-                            tma_load_2d(&tma_b, &full_bar[s], sb + (size_t)a * p.BN * 128, k0 + a * KATOM, n0);
+                        for (int a = 0; a < katoms; ++a)                                   // boxes 64(K) x BNh(N), one per K atom
+                            load(sb + (size_t)a * p.BNh * 128, k0 + a * KATOM, nb);
                     } else {
-                        for (int j = 0; j * 64 < p.BN; ++j)                                // boxes 64(N) x BK(K)
-                            tma_load_2d(&tma_b, &full_bar[s], sb + (size_t)j * p.BK * 128, n0 + j * 64, k0);
+                        for (int j = 0; j * 64 < p.BNh; ++j)                               // boxes 64(N) x BK(K)
+                            load(sb + (size_t)j * p.BK * 128, nb + j * 64, k0);
                     }
                 }
                 __syncwarp();
                 if (++s == p.stages) { s = 0; phase ^= 1; }
             }
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer =====================
+    } else if (warp == 1 && cta_rank == 0) {
+        // ===================== MMA issuer (pair: the leader CTA only) =====================
         int s = 0;
         uint32_t phase = 0;
-        for (int t = blockIdx.x, it = 0; t < total_tiles; t += gridDim.x, ++it) {
+        for (int t = unit, it = 0; t < total_tiles; t += n_units, ++it) {
             TS_TILE_COORDS(t)
             const int buf = it & 1;
             const uint32_t tmem_d = tmem_base + (uint32_t)buf * p.acc_stride;
             if (elect_one()) {
                 mbar_wait(&tmem_empty_bar[buf], ((uint32_t)(it >> 1) & 1u) ^ 1u);   // the epilogue has drained this accumulator
                 tc_fence_after();
-                if (kb_begin >= kb_end) umma_commit(&tmem_full_bar[buf]);           // empty split range: nothing to wait for
+                if (kb_begin >= kb_end) { if (TWO) umma2_commit(&tmem_full_bar[buf]); else umma_commit(&tmem_full_bar[buf]); }   // empty split range
             }
             __syncwarp();
             for (int kb = kb_begin; kb < kb_end; ++kb) {
@@ -180,17 +201,25 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     for (int a = 0; a < katoms; ++a) {
                         // K-major: K atom `a` is its own [rows x 128 B] block; MN-major: 64 more K rows further down
                         const uint32_t a_at = (p.a_major == TC_MAJOR_K) ? sa + a * (BM * 128) : sa + a * (KATOM * 128);
-                        const uint32_t b_at = (p.b_major == TC_MAJOR_K) ? sb + a * (p.BN * 128) : sb + a * (KATOM * 128);
+                        const uint32_t b_at = (p.b_major == TC_MAJOR_K) ? sb + a * (p.BNh * 128) : sb + a * (KATOM * 128);
                         const uint64_t adesc = make_desc(a_at, p.a_major, p.BK), bdesc = make_desc(b_at, p.b_major, p.BK);
                         const uint32_t a_step = (p.a_major == TC_MAJOR_K) ? (UMMA_K * 2) >> 4 : (UMMA_K * 128) >> 4;
                         const uint32_t b_step = (p.b_major == TC_MAJOR_K) ? (UMMA_K * 2) >> 4 : (UMMA_K * 128) >> 4;
 #pragma unroll
-                        for (int k = 0; k < KATOM / UMMA_K; ++k)
-                            umma_bf16(tmem_d, adesc + (uint64_t)(k * a_step), bdesc + (uint64_t)(k * b_step), p.idesc,
-                                      (kb > kb_begin || a > 0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < KATOM / UMMA_K; ++k) {
+                            if (TWO) umma2_bf16(tmem_d, adesc + (uint64_t)(k * a_step), bdesc + (uint64_t)(k * b_step), p.idesc,
+                                                (kb > kb_begin || a > 0 || k > 0) ? 1u : 0u);
+                            else umma_bf16(tmem_d, adesc + (uint64_t)(k * a_step), bdesc + (uint64_t)(k * b_step), p.idesc,
+                                           (kb > kb_begin || a > 0 || k > 0) ? 1u : 0u);
+                        }
                     }
-                    umma_commit(&empty_bar[s]);                               // frees the smem stage when these MMAs retire
-                    if (kb == kb_end - 1) umma_commit(&tmem_full_bar[buf]);   // accumulator complete
+                    if (TWO) {      // frees the stage / publishes the accumulator in BOTH CTAs when these MMAs retire
+                        umma2_commit(&empty_bar[s]);
+                        if (kb == kb_end - 1) umma2_commit(&tmem_full_bar[buf]);
+                    } else {
+                        umma_commit(&empty_bar[s]);                               // frees the smem stage when these MMAs retire
+                        if (kb == kb_end - 1) umma_commit(&tmem_full_bar[buf]);   // accumulator complete
+                    }
                     if (dbg && it == 0 && kb - kb_begin < 16) dbg[24 + (kb - kb_begin)] = clock64();
                 }
                 __syncwarp();
@@ -203,7 +232,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         const int half = (warp - 3) >> 2;        // which of the two warps of that quarter: chunks half, half + 2, ...
         float4 *stage = reinterpret_cast<float4 *>(staging + (size_t)(warp - 3) * 4096);
         const int sub_row = lane >> 3, piece = lane & 7;     // phase-2 mapping: 4 rows x 8 float4 per instruction
-        for (int t = blockIdx.x, it = 0; t < total_tiles; t += gridDim.x, ++it) {
+        auto release_acc = [&](int buf) {      // this warp's reads of the accumulator are done; the pair's barrier lives in the leader
+            if (TWO && cta_rank != 0) mbar_arrive_remote(&tmem_empty_bar[buf], 0u); else mbar_arrive(&tmem_empty_bar[buf]);
+        };
+        for (int t = unit, it = 0; t < total_tiles; t += n_units, ++it) {
             TS_TILE_COORDS(t)
             const int buf = it & 1;
             const uint32_t tmem_acc = tmem_base + (uint32_t)buf * p.acc_stride + ((uint32_t)(q * 32) << 16);
@@ -227,7 +259,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             if (half * 32 >= p.BN) {             // narrow tile: nothing for the second warp of the quarter
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+                if (lane == 0) release_acc(buf);
             }
             if (EPI == TC_EPI_ACTGRAD) fetch_prev(half * 32);
             for (int c = half * 32; c < p.BN; c += 64) {
@@ -249,7 +281,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     // this warp's last TMEM read of the tile is in registers: hand the accumulator back to the MMA issuer
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+                    if (lane == 0) release_acc(buf);
                 }
                 // phase 1: lane = row; 16-byte pieces XOR-swizzled by row so both phases are bank-conflict free
 #pragma unroll
@@ -352,7 +384,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     }
                     const int n = n0 + c + piece * 4;
                     if (sub_row == 0 && c + piece * 4 < p.BN) {
-                        float *o = p.colsum_out + (int64_t)(tm_ * 4 + q) * p.colsum_stride + n;
+                        float *o = p.colsum_out + (int64_t)((m0 / BM) * 4 + q) * p.colsum_stride + n;
                         for (int j = 0; j < 4; ++j)
                             if (n + j < p.N) o[j] = cs[j];
                     }
@@ -366,9 +398,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     __syncwarp();
     tc_fence_before();
     __syncthreads();
+    if (TWO) cluster_sync_all();      // neither CTA leaves (or frees tensor memory) while the other may still use its shared memory
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, p.tmem_cols);
+        if (TWO) tmem_dealloc2(tmem_base, p.tmem_cols); else tmem_dealloc(tmem_base, p.tmem_cols);
     }
     if (p.dbg && threadIdx.x == 0) {
         const unsigned long long t = global_ns();
@@ -483,6 +516,11 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     p.a_major = a.a_major; p.b_major = a.b_major;
     const int splits = a.splits;
     p.BN = pick_bn(a.M, a.N, a.K, splits, sm_count);
+    // CTA pairs for the widest tile: there one CTA alone is bound by shared-memory bandwidth, not by the tensor pipe
+    static const int pair_mode = [] { const char *e = getenv("TSB200_GEMM_PAIR"); return e ? atoi(e) : 1; }();
+    const bool two = pair_mode != 0 && p.BN == 256 && a.M >= 2 * BM && sm_count >= 2;
+    p.BNh = two ? p.BN / 2 : p.BN;
+    const int BMT = two ? 2 * BM : BM;
     // K range per split in elements (a multiple of 64), then K per pipeline stage: 128 for narrow tiles, where the
     // per-stage issue overhead (~300 cycles of barrier + TMA issue) dominates, 64 for wide ones (MMA-bound)
     const int k_atoms = (a.K + KATOM - 1) / KATOM;
@@ -493,15 +531,17 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     p.num_kblocks = (a.K + p.BK - 1) / p.BK;
     p.kblocks_per_split = (atoms_per_split * KATOM + p.BK - 1) / p.BK;   // split boundaries stay stage-aligned
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.a_major << 15) | ((uint32_t)a.b_major << 16) |
-              ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-    p.a_bytes = (uint32_t)BM * (uint32_t)p.BK * 2u;
-    p.b_bytes = (a.b_major == TC_MAJOR_K) ? (uint32_t)p.BN * (uint32_t)p.BK * 2u
-                                          : (uint32_t)((p.BN + 63) / 64) * (uint32_t)(p.BK * 128);
+              ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BMT >> 4) << 24);
+    p.a_bytes = (uint32_t)BM * (uint32_t)p.BK * 2u;                       // per CTA
+    p.b_bytes = (a.b_major == TC_MAJOR_K) ? (uint32_t)p.BNh * (uint32_t)p.BK * 2u
+                                          : (uint32_t)((p.BNh + 63) / 64) * (uint32_t)(p.BK * 128);
     const uint32_t stage = p.a_bytes + p.b_bytes;     // always a multiple of 1024
-    p.tiles_m = (a.M + BM - 1) / BM; p.tiles_n = (a.N + p.BN - 1) / p.BN; p.splits = splits;
+    p.tiles_m = (a.M + BMT - 1) / BMT; p.tiles_n = (a.N + p.BN - 1) / p.BN; p.splits = splits;
     const long total_tiles = (long)p.tiles_m * p.tiles_n * splits;
-    const int grid_x = (int)(total_tiles < sm_count ? total_tiles : sm_count);
-    const long tiles_per_cta = (total_tiles + grid_x - 1) / grid_x;
+    const int units = two ? sm_count / 2 : sm_count;                      // CTAs, or CTA pairs
+    const int grid_units = (int)(total_tiles < units ? total_tiles : units);
+    const int grid_x = two ? 2 * grid_units : grid_units;
+    const long tiles_per_cta = (total_tiles + grid_units - 1) / grid_units;
     // pipeline stages + 32 KiB of epilogue staging (the pipeline stays live while a tile's epilogue runs) + alignment
     p.stages = (int)((226u * 1024u - 1024u - (uint32_t)kEpiWarps * 4096u) / stage);
     if (p.stages > kMaxStages) p.stages = kMaxStages;
@@ -520,27 +560,32 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     if (a.a_major == TC_MAJOR_K) rc = get_map(a.A, (uint64_t)a.K, (uint64_t)a.M, (uint64_t)a.lda, KATOM, BM, &ma);
     else rc = get_map(a.A, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, 64, (uint32_t)p.BK, &ma);
     if (rc) return rc;
-    if (a.b_major == TC_MAJOR_K) rc = get_map(a.B, (uint64_t)a.K, (uint64_t)a.N, (uint64_t)a.ldb, KATOM, (uint32_t)p.BN, &mb);
+    if (a.b_major == TC_MAJOR_K) rc = get_map(a.B, (uint64_t)a.K, (uint64_t)a.N, (uint64_t)a.ldb, KATOM, (uint32_t)p.BNh, &mb);
     else rc = get_map(a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb, 64, (uint32_t)p.BK, &mb);
     if (rc) return rc;
 
     const size_t smem = (size_t)p.stages * stage + kEpiWarps * 4096 + 1024;
     dim3 grid((unsigned)grid_x);
-#define TS_TC_LAUNCH(E)                                                                                             \
+#define TS_TC_LAUNCH_K(KERNEL, CLUSTER)                                                                              \
     do {                                                                                                            \
         static bool attr_set[64] = {false};                                                                         \
         int dev_ = 0;                                                                                               \
         TS_CUDA_CHECK(cudaGetDevice(&dev_));                                                                        \
         if (!attr_set[dev_ & 63]) {                                                                                 \
-            TS_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024)); \
+            TS_CUDA_CHECK(cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));   \
             attr_set[dev_ & 63] = true;                                                                             \
         }                                                                                                           \
-        TS_CUDA_CHECK(launch_pdl(tc_gemm_kernel<E>, grid, dim3(kThreads), smem, st, 1, ma, mb, p));                 \
+        TS_CUDA_CHECK(launch_pdl(KERNEL, grid, dim3(kThreads), smem, st, CLUSTER, ma, mb, p));                      \
+    } while (0)
+#define TS_TC_LAUNCH(E)                                                                                             \
+    do {                                                                                                            \
+        if (two) TS_TC_LAUNCH_K((tc_gemm_kernel<E, true>), 2); else TS_TC_LAUNCH_K((tc_gemm_kernel<E, false>), 1);  \
     } while (0)
     if (a.epi == TC_EPI_STORE_F32) TS_TC_LAUNCH(TC_EPI_STORE_F32);
     else if (a.epi == TC_EPI_FWD) TS_TC_LAUNCH(TC_EPI_FWD);
     else TS_TC_LAUNCH(TC_EPI_ACTGRAD);
 #undef TS_TC_LAUNCH
+#undef TS_TC_LAUNCH_K
     TS_LAUNCH_CHECK();
     return TS_OK;
 }
