@@ -44,6 +44,8 @@ CASES = [
     (1, 1, 2040, 4000, 1000, 1),
     (0, 0, 300, 37888, 64, 1),         # second CTA of the last pair mostly out of range; many column tiles per pair
     (1, 1, 4096, 4096, 2048, 2),       # pairs with split-K
+    (1, 1, 4096, 784, 2048, 1),        # L-model dW1: 4 x 256 columns in one wave of pairs, the last peer half entirely out of range
+    (0, 0, 65536, 256, 784, 1),        # tall and one tile wide
 ]
 
 

@@ -500,7 +500,18 @@ int tc_head_forward(ts_mlp *m, const void *a_last, const int64_t *y, int64_t B, 
 int tc_head_backward(ts_mlp *m, const void *a_last, int64_t B, const uint8_t *const *masks, uint64_t seed, int *nsplit, cudaStream_t st) {
     const int L = m->n_layers, K = m->dims[L - 1], C = m->dims[L];
     int rc;
-    {
+    const int tb_ = 2 * (L - 2) + 1;
+    static const bool dh_gemm = [] { const char *e = getenv("TSB200_HEAD_DH_GEMM"); return e && atoi(e) != 0; }();
+    if (!dh_gemm && head_dh_supported(K, C, m->partial_stride[tb_])) {
+        const int rows32 = (int)((B + 31) / 32);
+        float *cs = nullptr;
+        if (rows32 <= kMaxRowBlocks) { cs = m->partials + m->partial_off[tb_]; nsplit[tb_] = rows32; }
+        ProfScope ps(K_HEAD, st);
+        rc = launch_head_dh(m->dzb, m->shadow + m->shadow_off[L - 1],
+                            m->act == TS_ACT_RELU ? (const __nv_bfloat16 *)a_last : (const __nv_bfloat16 *)m->upre[L - 2], B, K, C, m->act,
+                            drop_spec(m, masks, seed, L - 2, true), m->p > 0.0f, (__nv_bfloat16 *)m->dh[0], cs, m->partial_stride[tb_], st);
+        if (rc) return rc;
+    } else {
         TcGemmArgs g{};
         g.A = m->dzb; g.a_major = TC_MAJOR_K; g.lda = 16;
         g.B = m->shadow + m->shadow_off[L - 1]; g.b_major = TC_MAJOR_MN; g.ldb = K;

@@ -72,6 +72,11 @@ int launch_logits_head(const float *Z, const float *bias, const int64_t *y, int6
                        cudaStream_t st);
 int launch_wlast_finish(const float *wt, int64_t split_stride, int splits, int K, int C, const float *dz, int64_t B, float *gw,
                         float *gb, cudaStream_t st);
+// dH of the last hidden layer from dZ (bf16, [B,16]) and the zero-padded [16,K] last-layer shadow: an HBM-bound SIMT pass with the
+// activation gradient, the dropout factor and the 32-row bias-gradient partials (same layout as the ACTGRAD GEMM epilogue's)
+bool head_dh_supported(int K, int C, int64_t colsum_stride);
+int launch_head_dh(const __nv_bfloat16 *dzb, const __nv_bfloat16 *Wp, const __nv_bfloat16 *prev, int64_t B, int K, int C, int act,
+                   const DropoutSpec &drop, int training, __nv_bfloat16 *dH, float *colsum, int64_t colsum_stride, cudaStream_t st);
 
 // dW_last[c,k] = sum_r dz[r,c] * A[r,k], db_last[c] = sum_r dz[r,c]; `splits` row ranges -> partials
 int launch_head_wgrad(const void *A, int a_is_bf16, const float *dz, int64_t B, int K, int C, float *w_partial,

@@ -491,6 +491,232 @@ int launch_wlast_finish(const float *wt, int64_t split_stride, int splits, int K
     return TS_OK;
 }
 
+// dH of the last hidden layer (bf16 mode, wide nets): dH[r,k] = (sum_c dz[r,c] W_last[c,k]) * act'(.) * keep / (1 - p), with the
+// bias gradient of that layer (column sums of the ROUNDED dH, one partial per 32 rows) taken on the way. The contraction is only
+// C <= 16 long, so this is an HBM-bound elementwise pass (read A_prev, write dH: 4 B per element), not a GEMM: as a tcgen05 tile
+// loop it ran with 8 epilogue warps per SM in flight and took 129 us at 8192 x 4096; here every SM holds 2048 threads.
+// Thread = 4 neighbouring columns, its W_last column quad in registers; CTA = 32 rows x 1024 columns.
+template <int CP>
+__global__ void __launch_bounds__(256) head_dh_kernel(const __nv_bfloat16 *__restrict__ dzb, const __nv_bfloat16 *__restrict__ Wp,
+                                                      const __nv_bfloat16 *__restrict__ prev, int64_t B, int K, int act, DropoutSpec drop,
+                                                      int training, __nv_bfloat16 *__restrict__ dH, float *__restrict__ colsum,
+                                                      int64_t colsum_stride) {
+    __shared__ __align__(16) float sdz[32][CP];
+    const int64_t r0 = (int64_t)blockIdx.y * 32;
+    const int nr = (int)min((int64_t)32, B - r0);
+    const int k = (blockIdx.x * 256 + threadIdx.x) * 4;
+    pdl_wait();
+    pdl_launch_dependents();
+    float w[CP][4];
+    if (k < K) {
+#pragma unroll
+        for (int c = 0; c < CP; ++c) {
+            const uint2 pk = *reinterpret_cast<const uint2 *>(Wp + (int64_t)c * K + k);
+            const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162 *>(&pk.x), hi = *reinterpret_cast<const __nv_bfloat162 *>(&pk.y);
+            w[c][0] = __low2float(lo); w[c][1] = __high2float(lo); w[c][2] = __low2float(hi); w[c][3] = __high2float(hi);
+        }
+    }
+    for (int i = threadIdx.x; i < 32 * CP; i += 256) {
+        const int rr = i / CP, c = i % CP;
+        sdz[rr][c] = rr < nr ? __bfloat162float(dzb[(r0 + rr) * 16 + c]) : 0.0f;
+    }
+    __syncthreads();
+    if (k >= K) return;
+    const float sc = training ? drop.scale : 1.0f;
+    float cs[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    constexpr int U = 8;       // rows whose loads are in flight together
+    for (int rb = 0; rb < nr; rb += U) {
+        uint2 pv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            pv[u] = rb + u < nr ? __ldcs(reinterpret_cast<const uint2 *>(prev + (r0 + rb + u) * K + k)) : make_uint2(0u, 0u);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (rb + u >= nr) break;
+            const int rr = rb + u;
+            float a[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+            for (int c4 = 0; c4 < CP; c4 += 4) {
+                const float4 d = *reinterpret_cast<const float4 *>(&sdz[rr][c4]);
+                const float dv[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) a[e] = fmaf(dv[j], w[c4 + j][e], a[e]);
+            }
+            const __nv_bfloat162 plo = *reinterpret_cast<const __nv_bfloat162 *>(&pv[u].x), phi = *reinterpret_cast<const __nv_bfloat162 *>(&pv[u].y);
+            const float pf[4] = {__low2float(plo), __high2float(plo), __low2float(phi), __high2float(phi)};
+            if (act == TS_ACT_RELU) {      // A_prev > 0 implies the unit was kept
+#pragma unroll
+                for (int e = 0; e < 4; ++e) a[e] = pf[e] > 0.0f ? a[e] * sc : 0.0f;
+            } else {                       // prev = the stored pre-activation u; a dropped unit has u = 0, gelu'(0) = 1/2: keep factor explicit
+                float keep[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+                if (training) drop.factor4(r0 + rr, k, K, keep);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) a[e] = a[e] * gelu_grad_f(pf[e]) * keep[e];
+            }
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(a[0], a[1]), hi = __floats2bfloat162_rn(a[2], a[3]);
+            cs[0] += __low2float(lo); cs[1] += __high2float(lo); cs[2] += __low2float(hi); cs[3] += __high2float(hi);
+            uint2 pk;
+            pk.x = *reinterpret_cast<const uint32_t *>(&lo);
+            pk.y = *reinterpret_cast<const uint32_t *>(&hi);
+            *reinterpret_cast<uint2 *>(dH + (r0 + rr) * K + k) = pk;
+        }
+    }
+    if (colsum != nullptr) *reinterpret_cast<float4 *>(colsum + (int64_t)blockIdx.y * colsum_stride + k) = make_float4(cs[0], cs[1], cs[2], cs[3]);
+}
+
+// The same pass for widths that are multiples of 64, with the 16-long contraction on warp-level MMAs (m16n8k16, one k-step):
+// the FMA form above spends as long on its 12-16 FMAs per element as on the memory traffic. Warp = 64 rows x 64 columns in
+// four 16-row blocks; the 8 column tiles of a block are PERMUTED columns of W_last, chosen so that the accumulator fragment
+// of a thread is 2 x 8 contiguous columns of its row (tile j, fragment column 2q+e  <->  column 8q + 2(j&3) + e + 32(j>>2)):
+// A_prev is read and dH written as 16-byte pieces, four neighbouring lanes covering 64 contiguous bytes.
+__device__ __forceinline__ void mma_bf16_16x8x16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(256, 2) head_dh_mma_kernel(const __nv_bfloat16 *__restrict__ dzb, const __nv_bfloat16 *__restrict__ Wp,
+                                                             const __nv_bfloat16 *__restrict__ prev, int64_t B, int K, int act,
+                                                             DropoutSpec drop, int training, __nv_bfloat16 *__restrict__ dH,
+                                                             float *__restrict__ colsum, int64_t colsum_stride) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, i = lane >> 2, q = lane & 3;
+    const int cb = (blockIdx.x * 8 + warp) * 64;          // this warp's 64 columns
+    const int64_t r0 = (int64_t)blockIdx.y * 64;
+    pdl_wait();
+    pdl_launch_dependents();
+    if (cb >= K) return;
+    // B fragments: tile j, fragment column i = this lane's n; k = 2q, 2q+1 (b0) and 2q+8, 2q+9 (b1)
+    uint32_t wb[8][2];
+    const unsigned short *W16 = reinterpret_cast<const unsigned short *>(Wp);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int n = cb + 8 * (i >> 1) + 2 * (j & 3) + (i & 1) + 32 * (j >> 2);
+        wb[j][0] = (uint32_t)W16[(int64_t)(2 * q) * K + n] | ((uint32_t)W16[(int64_t)(2 * q + 1) * K + n] << 16);
+        wb[j][1] = (uint32_t)W16[(int64_t)(2 * q + 8) * K + n] | ((uint32_t)W16[(int64_t)(2 * q + 9) * K + n] << 16);
+    }
+    const float sc = training ? drop.scale : 1.0f;
+    const int col = cb + 8 * q;                            // this thread's columns: col..col+7 and col+32..col+39
+    auto fetch = [&](int blk, uint4 (&pv)[4]) {            // rows i and i + 8 of the block, two 16-byte pieces each
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t row = r0 + blk * 16 + i + 8 * h;
+#pragma unroll
+            for (int g = 0; g < 2; ++g)
+                pv[h * 2 + g] = (blk < 4 && row < B) ? __ldcs(reinterpret_cast<const uint4 *>(prev + row * K + col + 32 * g)) : make_uint4(0u, 0u, 0u, 0u);
+        }
+    };
+    uint4 pv_next[4];
+    fetch(0, pv_next);
+    float cs[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) cs[e] = 0.0f;
+#pragma unroll 1
+    for (int blk = 0; blk < 4; ++blk) {
+        const int64_t rb = r0 + blk * 16;
+        if (rb < B) {
+            uint4 pv[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) pv[e] = pv_next[e];
+            fetch(blk + 1, pv_next);
+            uint32_t a[4];
+            const uint32_t *dz32 = reinterpret_cast<const uint32_t *>(dzb);
+            const int64_t ra = rb + i, rc = rb + i + 8;
+            a[0] = ra < B ? dz32[ra * 8 + q] : 0u;
+            a[1] = rc < B ? dz32[rc * 8 + q] : 0u;
+            a[2] = ra < B ? dz32[ra * 8 + q + 4] : 0u;
+            a[3] = rc < B ? dz32[rc * 8 + q + 4] : 0u;
+            float acc[8][4];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0f;
+                mma_bf16_16x8x16(acc[j], a, wb[j][0], wb[j][1]);
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {                 // row i (h = 0: c0, c1) and row i + 8 (h = 1: c2, c3)
+                const int64_t row = rb + i + 8 * h;
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {              // columns col + 32 g .. + 7: tiles j = 4g .. 4g + 3
+                    const uint4 pq = pv[h * 2 + g];
+                    const uint32_t pw[4] = {pq.x, pq.y, pq.z, pq.w};
+                    float v[8];
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) { v[2 * jj] = acc[4 * g + jj][2 * h]; v[2 * jj + 1] = acc[4 * g + jj][2 * h + 1]; }
+                    float keep[8] = {1.0f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f};
+                    if (act != TS_ACT_RELU && training && row < B) {
+                        drop.factor4(row, col + 32 * g, K, *reinterpret_cast<float(*)[4]>(&keep[0]));
+                        drop.factor4(row, col + 32 * g + 4, K, *reinterpret_cast<float(*)[4]>(&keep[4]));
+                    }
+                    uint32_t ow[4];
+#pragma unroll
+                    for (int e2 = 0; e2 < 4; ++e2) {
+                        const __nv_bfloat162 pp = *reinterpret_cast<const __nv_bfloat162 *>(&pw[e2]);
+                        const float p0 = __low2float(pp), p1 = __high2float(pp);
+                        float x0 = v[2 * e2], x1 = v[2 * e2 + 1];
+                        if (act == TS_ACT_RELU) {          // A_prev > 0 implies the unit was kept
+                            x0 = p0 > 0.0f ? x0 * sc : 0.0f;
+                            x1 = p1 > 0.0f ? x1 * sc : 0.0f;
+                        } else {                           // prev = the stored pre-activation; gelu'(0) = 1/2, so the keep factor is explicit
+                            x0 = x0 * gelu_grad_f(p0) * keep[2 * e2];
+                            x1 = x1 * gelu_grad_f(p1) * keep[2 * e2 + 1];
+                        }
+                        const __nv_bfloat162 o2 = __floats2bfloat162_rn(x0, x1);
+                        if (row < B) { cs[g * 8 + 2 * e2] += __low2float(o2); cs[g * 8 + 2 * e2 + 1] += __high2float(o2); }
+                        ow[e2] = *reinterpret_cast<const uint32_t *>(&o2);
+                    }
+                    if (row < B) *reinterpret_cast<uint4 *>(dH + row * K + col + 32 * g) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+                }
+            }
+        }
+        if ((blk & 1) && colsum != nullptr) {              // one bias-gradient partial per 32 rows: fold the 8 row lanes
+            const int64_t prow = blockIdx.y * 2 + (blk >> 1);
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                float c = cs[e];
+                c += __shfl_xor_sync(0xffffffffu, c, 4);
+                c += __shfl_xor_sync(0xffffffffu, c, 8);
+                c += __shfl_xor_sync(0xffffffffu, c, 16);
+                cs[e] = c;
+            }
+            if (i == 0 && prow * 32 < B) {
+                float *o = colsum + prow * colsum_stride + col;
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    *reinterpret_cast<float4 *>(o + 32 * g) = make_float4(cs[g * 8], cs[g * 8 + 1], cs[g * 8 + 2], cs[g * 8 + 3]);
+                    *reinterpret_cast<float4 *>(o + 32 * g + 4) = make_float4(cs[g * 8 + 4], cs[g * 8 + 5], cs[g * 8 + 6], cs[g * 8 + 7]);
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < 16; ++e) cs[e] = 0.0f;
+        }
+    }
+}
+
+bool head_dh_supported(int K, int C, int64_t colsum_stride) { return K % 4 == 0 && C >= 1 && C <= 16 && colsum_stride % 4 == 0; }
+
+int launch_head_dh(const __nv_bfloat16 *dzb, const __nv_bfloat16 *Wp, const __nv_bfloat16 *prev, int64_t B, int K, int C, int act,
+                   const DropoutSpec &drop, int training, __nv_bfloat16 *dH, float *colsum, int64_t colsum_stride, cudaStream_t st) {
+    TS_REQUIRE(head_dh_supported(K, C, colsum_stride), TS_E_INVALID, "head dH: width %d / classes %d not supported", K, C);
+    if (K % 64 == 0) {
+        const dim3 grid_mma((unsigned)((K / 64 + 7) / 8), (unsigned)((B + 63) / 64));
+        TS_CUDA_CHECK(launch_pdl(head_dh_mma_kernel, grid_mma, dim3(256), 0, st, 1, dzb, Wp, prev, B, K, act, drop, training, dH, colsum,
+                                 colsum_stride));
+        TS_LAUNCH_CHECK();
+        return TS_OK;
+    }
+    const dim3 grid((unsigned)((K / 4 + 255) / 256), (unsigned)((B + 31) / 32));
+#define TS_HEAD_DH(CP_) \
+    TS_CUDA_CHECK(launch_pdl(head_dh_kernel<CP_>, grid, dim3(256), 0, st, 1, dzb, Wp, prev, B, K, act, drop, training, dH, colsum, colsum_stride))
+    if (C <= 4) TS_HEAD_DH(4);
+    else if (C <= 8) TS_HEAD_DH(8);
+    else if (C <= 12) TS_HEAD_DH(12);
+    else TS_HEAD_DH(16);
+#undef TS_HEAD_DH
+    TS_LAUNCH_CHECK();
+    return TS_OK;
+}
+
 template <typename T, int MAXC>
 __global__ void __launch_bounds__(128) head_wgrad_kernel(const T *__restrict__ A, const float *__restrict__ dz, int64_t B,
                                                          int K, int C, float *__restrict__ w_partial, int64_t w_stride,

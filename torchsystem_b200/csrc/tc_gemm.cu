@@ -483,9 +483,13 @@ namespace {
 //   ~2000 prologue + per 64 K-elements max(2*BN tensor time, issue cadence: ~440 with 128-wide stages, ~684 with
 //   64-wide stages) + ~12 per output column of epilogue; total = waves * per-CTA. Widths that would pad the
 //   problem by more than 12.5 % are not considered.
-int pick_bn(int M, int N, int K, int splits, int sm_count) {
+// A CTA pair on a 256 x 256 tile runs close to the tensor time (~560 cycles per 64 K-elements measured against 684 for one
+// CTA on 128 x 256) and is costed next to the single-CTA widths -- without the padding rule: a padded tile that saves a wave
+// is still a win (dW1 of the 784 -> 4096 layer: N = 784 as 4 x 256 in ONE wave of pairs instead of two waves of 112-wide tiles).
+int pick_bn(int M, int N, int K, int splits, int sm_count, bool pairs_allowed, bool *two) {
     static const int cand[] = {256, 224, 192, 160, 128, 112, 96, 80, 64, 48, 32, 16};
-    if (const char *f = getenv("TSB_FORCE_BN")) return atoi(f);   // experiments
+    *two = false;
+    if (const char *f = getenv("TSB_FORCE_BN")) { *two = pairs_allowed && atoi(f) == 256 && M >= 2 * BM; return atoi(f); }   // experiments
     const int tiles_m = (M + BM - 1) / BM;
     const long k64 = ((K + KATOM - 1) / KATOM + splits - 1) / splits;
     int best = 16;
@@ -501,6 +505,13 @@ int pick_bn(int M, int N, int K, int splits, int sm_count) {
         const double cost = (double)waves * per_cta;
         if (cost < best_cost - 1e-9) { best_cost = cost; best = bn; }
     }
+    if (pairs_allowed && M >= 2 * BM && N > 128 && sm_count >= 2) {
+        const long tiles = (long)((M + 2 * BM - 1) / (2 * BM)) * ((N + 255) / 256) * splits;
+        const long units = sm_count / 2;
+        const long waves = (tiles + units - 1) / units;
+        const double cost = (double)waves * (2000.0 + (double)k64 * 560.0 + 12.0 * 256);
+        if (cost < best_cost) { best_cost = cost; best = 256; *two = true; }
+    }
     return best;
 }
 
@@ -515,10 +526,10 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     p.M = a.M; p.N = a.N; p.K = a.K;
     p.a_major = a.a_major; p.b_major = a.b_major;
     const int splits = a.splits;
-    p.BN = pick_bn(a.M, a.N, a.K, splits, sm_count);
     // CTA pairs for the widest tile: there one CTA alone is bound by shared-memory bandwidth, not by the tensor pipe
     static const int pair_mode = [] { const char *e = getenv("TSB200_GEMM_PAIR"); return e ? atoi(e) : 1; }();
-    const bool two = pair_mode != 0 && p.BN == 256 && a.M >= 2 * BM && sm_count >= 2;
+    bool two = false;
+    p.BN = pick_bn(a.M, a.N, a.K, splits, sm_count, pair_mode != 0, &two);
     p.BNh = two ? p.BN / 2 : p.BN;
     const int BMT = two ? 2 * BM : BM;
     // K range per split in elements (a multiple of 64), then K per pipeline stage: 128 for narrow tiles, where the
