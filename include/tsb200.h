@@ -198,6 +198,15 @@ int32_t ts_dp_reserve_sms(ts_mlp *m, int32_t n_sms);
  * (ts_dp_set_timeout, default 600 s or TSB200_DP_TIMEOUT_S): when it expires the kernel skips its update and sets a
  * host-visible error word instead of trapping; the next ts_fit_step (or ts_dp_status) then returns TS_E_TIMEOUT. */
 int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bufs /*HOST*/, uint32_t *const *flag_bufs /*HOST*/);
+/* Optional low-latency form of that exchange for the one-hidden-layer path at batches of 2,048 rows or more (no counterpart in
+ * the reference): the kernel that computes dW1 sends its share of the gradient as 16-byte packets {three floats, step number}
+ * to the rank that owns the share, which adds the ranks in rank order and sends the sum to everybody; receivers poll their OWN
+ * memory for the step number. No fence, flag or remote read on the critical path. Call after ts_dp_bind, on every rank.
+ *   inbox_bufs   HOST array of world device pointers: rank r's inbox, TS_DP_LL_INBOX_BYTES bytes, zero-initialised, 16-byte
+ *                aligned, mapped on THIS device (e.g. torch symmetric memory)
+ * TSB200_DP_LL=0 (environment, read once) keeps the exchange of ts_dp_bind. */
+#define TS_DP_LL_INBOX_BYTES 28311552
+int32_t ts_dp_bind_ll(ts_mlp *m, void *const *inbox_bufs /*HOST*/, int64_t inbox_bytes);
 /* Bound, in seconds, on how long a data-parallel kernel waits for a peer rank (no counterpart in the reference). */
 int32_t ts_dp_set_timeout(ts_mlp *m, double seconds);
 /* TS_OK, or TS_E_TIMEOUT once a data-parallel kernel has given up waiting for a peer (no counterpart in the reference). */

@@ -23,6 +23,13 @@ if rank == 0: print(f'{mode}: {e0.elapsed_time(e1) / 256 * 1e3:.1f} us per fit (
 if model._p2p is not None:
     tr = model._p2p[1][16:24].cpu().tolist(); tr = [(v - tr[0]) & 0xffffffff for v in tr]
     print(f'rank {rank} dp kernel trace ns: pdl_wait_done {tr[1]}, flags_seen {tr[2]}, peers_read {tr[3]}, updated {tr[4]} | part1_done {tr[5]} last_cta_ticket {tr[6]} flags_sent {tr[7]}', flush=True)
+import ctypes
+from torchsystem_b200 import _lib
+tr = (ctypes.c_uint64 * 16)()
+if _lib.lib.ts_test_wgrad_trace(tr) == 0:
+    t = [int(v) for v in tr]
+    print(f'rank {rank} dW1+update CTA 0 (cycles after griddepcontrol.wait): last MMA issued {t[3]-t[1]}, tile staged {t[5]-t[1]}, cluster barrier {t[6]-t[1]}, '
+          f'remote smem loads issued {t[7]-t[1]}, own gradient summed {t[10]-t[1]}, exchanged+updated {t[8]-t[1]}, end {t[9]-t[1]}', flush=True)
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for i in range(64): step(i)
     torch.cuda.synchronize()

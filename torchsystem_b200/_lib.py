@@ -47,6 +47,7 @@ PROTOTYPES = {
     'ts_opt_bind': (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(OptHyper), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     'ts_opt_step_count': (C.c_int64, [C.c_void_p]),
     'ts_dp_bind': (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
+    'ts_dp_bind_ll': (C.c_int32, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int64]),
     'ts_dp_set_timeout': (C.c_int32, [C.c_void_p, C.c_double]),
     'ts_dp_status': (C.c_int32, [C.c_void_p]),
     'ts_mlp_shadow_elems': (C.c_int64, [C.c_void_p]),

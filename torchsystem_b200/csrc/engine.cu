@@ -117,6 +117,8 @@ struct ts_mlp {
     int dp_world = 1, dp_rank = 0;
     float *dp_grads[2][kMaxRanks] = {{nullptr}};
     uint32_t *dp_flags[kMaxRanks] = {nullptr};
+    char *ll_inbox[kMaxRanks] = {nullptr};         // ts_dp_bind_ll: rank r's inbox of the low-latency exchange (two parities)
+    bool ll_bound = false;
     // NVLS variant (ts_dp_bind_nvls): multicast mappings of the symmetric gradient / parameter / shadow buffers
     // nvls overlap: each layer's reduce + update runs on a side stream, on a few SMs, under the backward pass of the layers below
     cudaStream_t dp_stream = nullptr;
@@ -723,6 +725,12 @@ int fit_impl(ts_mlp *m, const void *x, int x_dtype, const int64_t *y, int64_t B,
                 w.dp.timeout_ns = (unsigned long long)(m->dp_timeout_s * 1e9);
                 w.dp.err = m->dp_err_dev;
                 for (int r = 0; r < m->dp_world; ++r) { w.dp.grads[r] = m->dp_grads[parity][r]; w.dp.flags[r] = m->dp_flags[r]; }
+                if (m->ll_bound) {
+                    for (int r = 0; r < m->dp_world; ++r) w.dp.ll_peer[r] = reinterpret_cast<float4 *>(m->ll_inbox[r] + parity * kLlParityBytes);
+                    w.dp.ll_own = reinterpret_cast<const float4 *>(m->ll_inbox[m->dp_rank] + parity * kLlParityBytes);
+                    static const bool two_hops = [] { const char *e = getenv("TSB200_DP_LL"); return e && atoi(e) == 2; }();   // A/B runs
+                    w.dp.ll_direct = m->dp_world == 2 && !two_hops;
+                }
             }
             ProfScope ps(K_WGRAD_UPD, st);
             return launch_wgrad_update(w, st);
@@ -1032,6 +1040,20 @@ int32_t ts_dp_bind(ts_mlp *m, int32_t rank, int32_t world, float *const *grad_bu
     m->dp_world = world;
     m->dp_rank = rank;
     return ensure_dp_error_word(m);
+}
+
+int32_t ts_dp_bind_ll(ts_mlp *m, void *const *inbox_bufs, int64_t inbox_bytes) {
+    TS_REQUIRE(m && inbox_bufs, TS_E_INVALID, "null argument");
+    TS_REQUIRE(m->dp_world >= 2 && !m->nvls, TS_E_STATE, "ts_dp_bind_ll follows ts_dp_bind on a world of at least 2 ranks");
+    TS_REQUIRE(inbox_bytes >= 2 * kLlParityBytes, TS_E_INVALID, "inbox of %lld bytes, TS_DP_LL_INBOX_BYTES = %lld", (long long)inbox_bytes,
+               (long long)(2 * kLlParityBytes));
+    for (int r = 0; r < m->dp_world; ++r) {
+        TS_REQUIRE(inbox_bufs[r] != nullptr && ((uintptr_t)inbox_bufs[r] % 16) == 0, TS_E_INVALID, "inbox of rank %d null or not 16-byte aligned", r);
+        m->ll_inbox[r] = static_cast<char *>(inbox_bufs[r]);
+    }
+    static const bool off = [] { const char *e = getenv("TSB200_DP_LL"); return e && atoi(e) == 0; }();
+    m->ll_bound = !off;
+    return TS_OK;
 }
 
 int32_t ts_dp_set_timeout(ts_mlp *m, double seconds) {

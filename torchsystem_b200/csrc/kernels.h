@@ -132,9 +132,19 @@ int launch_reduce_partials(float *partials, const ReduceArgs &r, cudaStream_t st
 
 // data parallel: peer-mapped gradient buffers and flag arrays of every rank (this step's parity)
 constexpr int kMaxRanks = 8;
+// Inbox of the low-latency exchange: per step parity, kMaxRanks regions for what the peers send to the owner of a CTA's share
+// plus one region for the sums the owners send back; a region holds, per CTA of the kernel, kLlQuads x 256 sixteen-byte
+// packets {three floats, step number}.   2 * kLlParityBytes = TS_DP_LL_INBOX_BYTES (include/tsb200.h)
+constexpr int kLlCtas = 128, kLlQuads = 3;
+constexpr int64_t kLlParityBytes = (int64_t)(kMaxRanks + 1) * kLlCtas * kLlQuads * 256 * 16;
+__host__ __device__ inline int64_t ll_index(int region, int cta, int tid) { return ((int64_t)(region * kLlCtas + cta) * kLlQuads) * 256 + tid; }
 struct DpArgs {
     const float *grads[kMaxRanks];   // rank r's reduced gradient (flat layout), readable from this GPU
     uint32_t *flags[kMaxRanks];      // rank r's flag array: entry q = last step whose gradient rank q has published; [8] arrival ticket
+    // low-latency exchange of the dW1 + update kernel (ts_dp_bind_ll; ll_own == nullptr: the pull exchange above)
+    float4 *ll_peer[kMaxRanks];      // rank r's inbox (this step's parity), writable from this GPU
+    const float4 *ll_own;            // this rank's inbox (this step's parity)
+    int ll_direct;                   // two ranks: each sends its share straight to the other and both add in rank order (one hop)
     int world, rank;
     uint32_t step;
     unsigned long long timeout_ns;   // how long a wait for a peer may last before the kernel gives up (no trap)

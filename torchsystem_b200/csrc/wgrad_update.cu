@@ -71,6 +71,132 @@ __device__ __forceinline__ bool dp_publish_and_wait(const DpArgs &dp, int tid, i
     return !*s_timed_out;
 }
 
+// ---- low-latency exchange (ts_dp_bind_ll). The pull exchange above crosses NVLink three times on the critical path (publish,
+// remote load request, reply) behind a grid-wide ticket. Here the data carries its own validity, as in a collective library's
+// low-latency protocol: a 16-byte packet {three floats, step number} written with ONE store; the receiver polls its own memory
+// until the fourth word shows this step (a 16-byte aligned store or load is a single transaction, so a packet is seen whole
+// or not at all). No fence, no separate flag, no ticket, and a late CTA delays only its own share. Two hops keep the wire
+// volume flat in the world size: CTA c's share of the gradient is owned by rank c % world; the other ranks send their share
+// to the owner's inbox, the owner adds them in rank order (its own term in its place) and sends the sum to everybody -- all
+// replicas apply bit-identical gradients. (A world of two skips the second hop: each rank sends its share to the other and both
+// add the same two terms in the same order.) Slots alternate with the step parity: a rank can be one step ahead of a peer's
+// reads, never two (to finish a step it needs every peer's packets of that step, sent after they had read the step before).
+__device__ __forceinline__ void ll_store(float4 *dst, float a, float b, float c, uint32_t step) {
+    asm volatile("st.volatile.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(a), "f"(b), "f"(c), "f"(__uint_as_float(step)) : "memory");
+}
+__device__ __forceinline__ float4 ll_load(const float4 *src) {
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src) : "memory");
+    return v;
+}
+// packets k = 0..NQ-1 of up to NB sources (nullptr: skip), all loads in flight together; polls until every packet shows `step`
+template <int NB, int NQ>
+__device__ __forceinline__ bool ll_recv(const float4 *const (&src)[NB], float4 (&v)[NB][NQ], uint32_t step, const DpArgs &dp) {
+    uint32_t pending = 0;
+#pragma unroll
+    for (int b = 0; b < NB; ++b)
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) {
+            v[b][k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (src[b] != nullptr) pending |= 1u << (b * NQ + k);
+        }
+    unsigned long long t0 = 0;
+    for (uint32_t spins = 0; pending != 0u; ++spins) {
+#pragma unroll
+        for (int b = 0; b < NB; ++b)
+#pragma unroll
+            for (int k = 0; k < NQ; ++k)
+                if ((pending >> (b * NQ + k)) & 1u) v[b][k] = ll_load(src[b] + k * 256);
+#pragma unroll
+        for (int b = 0; b < NB; ++b)
+#pragma unroll
+            for (int k = 0; k < NQ; ++k)
+                if (((pending >> (b * NQ + k)) & 1u) && __float_as_uint(v[b][k].w) == step) pending &= ~(1u << (b * NQ + k));
+        if (pending != 0u && spins > 64u) __nanosleep(32);
+        if ((spins & 1023u) == 1023u) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > dp.timeout_ns) {
+                if (dp.err != nullptr) *reinterpret_cast<volatile uint32_t *>(dp.err) = dp.step ? dp.step : 1u;
+                return false;
+            }
+        }
+    }
+    return true;
+}
+// One 256-thread group (tid, named barrier `bar`) exchanges NF floats per thread; tot = sum over the ranks, identical everywhere.
+// Inactive threads (nothing to send: out-of-range quads) only take part in the barriers. False after a timeout, for the whole group.
+template <int NF>
+__device__ __forceinline__ bool ll_exchange(const DpArgs &dp, int cta, int tid, bool active, const float (&mine)[NF], float (&tot)[NF],
+                                            int bar, bool *s_timed_out) {
+    constexpr int NQ = (NF + 2) / 3;
+    static_assert(NQ <= kLlQuads, "packets per thread");
+    const int W = dp.world, R = dp.rank, owner = cta % W;
+    if (tid == 0) *s_timed_out = false;
+    named_bar_sync(bar, 256);
+    bool ok = true;
+    auto send = [&](float4 *dst, const float (&val)[NF]) {
+#pragma unroll
+        for (int k = 0; k < NQ; ++k)
+            ll_store(dst + k * 256, val[3 * k], 3 * k + 1 < NF ? val[3 * k + 1] : 0.0f, 3 * k + 2 < NF ? val[3 * k + 2] : 0.0f, dp.step);
+    };
+    auto unpack = [&](const float4 (&v)[NQ], float (&val)[NF]) {
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) {
+            val[3 * k] = v[k].x;
+            if (3 * k + 1 < NF) val[3 * k + 1] = v[k].y;
+            if (3 * k + 2 < NF) val[3 * k + 2] = v[k].z;
+        }
+    };
+    if (active) {
+        if (dp.ll_direct) {          // world of two
+            send(dp.ll_peer[R ^ 1] + ll_index(R, cta, tid), mine);
+            const float4 *src[1] = {dp.ll_own + ll_index(R ^ 1, cta, tid)};
+            float4 v[1][NQ];
+            ok = ll_recv<1, NQ>(src, v, dp.step, dp);
+            float val[NF];
+            unpack(v[0], val);
+#pragma unroll
+            for (int e = 0; e < NF; ++e) tot[e] = R == 0 ? (0.0f + mine[e]) + val[e] : (0.0f + val[e]) + mine[e];
+        } else if (owner != R) {
+            send(dp.ll_peer[owner] + ll_index(R, cta, tid), mine);
+            const float4 *src[1] = {dp.ll_own + ll_index(kMaxRanks, cta, tid)};
+            float4 v[1][NQ];
+            ok = ll_recv<1, NQ>(src, v, dp.step, dp);
+            unpack(v[0], tot);
+        } else {
+#pragma unroll
+            for (int e = 0; e < NF; ++e) tot[e] = 0.0f;
+#pragma unroll
+            for (int rb = 0; rb < kMaxRanks; rb += 4) {       // four sources' packets in flight together; the sum stays in rank order
+                if (rb >= W) break;
+                const float4 *src[4];
+#pragma unroll
+                for (int b = 0; b < 4; ++b) src[b] = (rb + b < W && rb + b != R) ? dp.ll_own + ll_index(rb + b, cta, tid) : nullptr;
+                float4 v[4][NQ];
+                ok = ll_recv<4, NQ>(src, v, dp.step, dp) && ok;
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    if (rb + b >= W) continue;
+                    float val[NF];
+                    unpack(v[b], val);
+#pragma unroll
+                    for (int e = 0; e < NF; ++e) tot[e] += (rb + b == R) ? mine[e] : val[e];
+                }
+            }
+            if (ok) {
+#pragma unroll
+                for (int r = 0; r < kMaxRanks; ++r)
+                    if (r < W && r != R) send(dp.ll_peer[r] + ll_index(kMaxRanks, cta, tid), tot);
+            }
+        }
+    }
+    if (!ok) *s_timed_out = true;
+    named_bar_sync(bar, 256);
+    return !*s_timed_out;
+}
+
 // clock64 trace of CTA 0 of the most recent launch (read back by the ts_test_wgrad_trace hook)
 __device__ unsigned long long g_wgrad_trace[16];
 #define WTRACE(i) do { if (blockIdx.x == 0) g_wgrad_trace[(i)] = clock64(); } while (0)
@@ -103,6 +229,7 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     const int cluster_id = (int)blockIdx.x / S;
     const uint32_t rank = cluster_rank();
     const OptArgs &o = p.opt;
+    const bool ll = DP && p.dp.ll_own != nullptr;     // low-latency packets instead of publish + remote reads
 
     if (cluster_id >= p.n_tiles) {
         // ===================== the other tensors: per-slab partials from the fused kernel -> sum -> update =====================
@@ -110,6 +237,33 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         pdl_launch_dependents();
         pdl_wait();
         if (threadIdx.x >= 256) return;
+        if (DP && ll) {
+            // low-latency exchange: at most one chunk per CTA (the launcher checks small_chunks <= S); every thread joins the barriers
+            const int c = (int)rank;
+            const int chunk = p.small_chunk_begin + c;
+            const int tix = c < p.small_chunks ? o.chunk_tensor[chunk] : -1;
+            TensorDesc d{};
+            if (tix >= 0) d = o.t[tix];
+            const int64_t i0 = (int64_t)chunk * kChunk + threadIdx.x * 4;
+            const int64_t j0 = i0 - d.offset;
+            const bool active = tix >= 0 && j0 < d.count;
+            const int n = active ? (int)min((int64_t)4, d.count - j0) : 0;
+            float g[4] = {0.0f, 0.0f, 0.0f, 0.0f}, tot[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            if (active) {
+                if (d.nsplit > 0) {
+                    sum_partials(o.partials + d.partial_off + j0, d.partial_stride, d.nsplit, g, slots, o.partial_depth);
+                    if (n < 2) g[1] = 0.0f;
+                    if (n < 3) g[2] = 0.0f;
+                    if (n < 4) g[3] = 0.0f;
+                    *reinterpret_cast<float4 *>(o.grads + i0) = make_float4(g[0], g[1], g[2], g[3]);
+                } else {
+                    const float4 t = *reinterpret_cast<const float4 *>(o.grads + i0);
+                    g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
+                }
+            }
+            if (ll_exchange<4>(p.dp, (int)blockIdx.x, (int)threadIdx.x, active, g, tot, 2, &s_timed_out) && active) apply_update(o, d, i0, j0, n, tot);
+            return;
+        }
         for (int pass = 0; pass < (DP ? 2 : 1); ++pass) {
             // DP: pass 0 folds the partials into this rank's peer-visible gradient buffer, then the handshake, pass 1 sums the
             // ranks and updates; single GPU: one pass does both
@@ -316,16 +470,33 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             pk.y = *reinterpret_cast<const uint32_t *>(&hi);
             *reinterpret_cast<uint2 *>(o.shadow + p.sh_w1 + idx[i]) = pk;
         };
+        float4 own[n_own];      // DP: this rank's gradient quads
 #pragma unroll
         for (int i = 0; i < n_own; ++i) {
+            own[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
             float g[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
             for (int r = 0; r < S; ++r) { g[0] += part[i][r].x; g[1] += part[i][r].y; g[2] += part[i][r].z; g[3] += part[i][r].w; }
             if (idx[i] < 0) continue;
-            if (DP) *reinterpret_cast<float4 *>(o.grads + p.off_w1 + idx[i]) = make_float4(g[0], g[1], g[2], g[3]);   // peer-visible buffer
-            else update_quad(i, g);
+            if (DP) {
+                own[i] = make_float4(g[0], g[1], g[2], g[3]);
+                *reinterpret_cast<float4 *>(o.grads + p.off_w1 + idx[i]) = own[i];   // peer-visible buffer (and param.grad)
+            } else {
+                update_quad(i, g);
+            }
         }
-        if (DP) {
+        if (et == 0) WTRACE(10);
+        if (DP && ll) {
+            if constexpr (S == 8) {      // n_own = 2: eight floats per thread in three packets
+                const float mine[8] = {own[0].x, own[0].y, own[0].z, own[0].w, own[1].x, own[1].y, own[1].z, own[1].w};
+                float tot[8];
+                if (ll_exchange<8>(p.dp, (int)blockIdx.x, et, idx[0] >= 0 || idx[1] >= 0, mine, tot, 1, &s_timed_out)) {
+                    const float g0[4] = {tot[0], tot[1], tot[2], tot[3]}, g1[4] = {tot[4], tot[5], tot[6], tot[7]};
+                    if (idx[0] >= 0) update_quad(0, g0);
+                    if (idx[1] >= 0) update_quad(1, g1);
+                }
+            }
+        } else if (DP) {
             // ---- every rank's gradient is complete once the handshake returns: this thread's quads from all of them, rank order
             if (dp_publish_and_wait(p.dp, et, 1, &s_last, &s_timed_out)) {
                 float4 rv[n_own][8];
@@ -347,7 +518,7 @@ wgrad_update_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             }
         }
     }
-    if (threadIdx.x == 96) WTRACE(8);
+    if (threadIdx.x == 96) WTRACE(8);   // et == 0
     // the cluster barriers are cluster-wide: the producer / issuer warps take part too. Second barrier: nobody leaves while a
     // peer may still be reading its tile.
     __syncwarp();
@@ -409,6 +580,8 @@ int launch_wgrad_update(const WgradUpdateArgs &a, cudaStream_t st) {
     const unsigned grid = (unsigned)((p.n_tiles + 1) * p.S);
     const bool dp = a.dp.world > 1;
     p.dp = a.dp;
+    // low-latency exchange: clusters of 8 (two quads per thread), one small-tensor chunk per CTA, a slot per CTA in the inbox
+    if (p.S != 8 || p.small_chunks > p.S || (int)grid > kLlCtas) p.dp.ll_own = nullptr;
     // DP: every CTA waits for the peers, so the whole grid must be resident: one CTA per SM (160 KiB of shared memory each)
     TS_REQUIRE(!dp || (int)grid <= a.sm_count, TS_E_UNSUPPORTED, "dW1 + update kernel: %u CTAs do not fit on %d SMs at once", grid, a.sm_count);
     if (p.S == 8 && dp) TS_CUDA_CHECK(launch_pdl(wgrad_update_kernel<8, true>, dim3(grid), dim3(kThreads), smem, st, 8u, ma, mb, p));

@@ -6,9 +6,14 @@ step, metric counters are summed once per `compute()`.
 Everything here is device-agnostic on purpose, so the world_size-2 gloo tests exercise the same code."""
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 from torch import Tensor
+
+LL_INBOX_BYTES = 28311552              # TS_DP_LL_INBOX_BYTES (include/tsb200.h)
+LL_MAX_MODEL_BYTES = 16 << 20          # flat gradient size up to which the low-latency inbox is allocated (one-hidden-layer models)
 
 
 def shard_bounds(n: int, rank: int, world: int, granule: int = 1) -> tuple[int, int]:
@@ -94,7 +99,19 @@ def bind_peer_gradients(engine, params, dp: DataParallel):
     for i, p in enumerate(params):
         o, n = engine.offsets[i], p.numel()
         p.grad = engine.grads[o:o + n].view(p.shape)
-    return gbuf, flags, hg, hf
+    keep = [gbuf, flags, hg, hf]
+    # small models (the one-hidden-layer path): inbox of the low-latency exchange inside the dW1 kernel (ts_dp_bind_ll)
+    if total * 4 <= LL_MAX_MODEL_BYTES and os.environ.get('TSB200_DP_LL', '1') != '0':
+        with torch.cuda.device(engine.index):
+            inbox = symm.empty(LL_INBOX_BYTES // 4, dtype=torch.float32, device=dev)
+            inbox.zero_()
+            hi = symm.rendezvous(inbox, group)
+            torch.cuda.synchronize(engine.index)
+        dist.barrier(group=dp.group)
+        iptrs = (C.c_void_p * world)(*[hi.buffer_ptrs[r] for r in range(world)])
+        check(lib.ts_dp_bind_ll(engine.handle, iptrs, LL_INBOX_BYTES), 'ts_dp_bind_ll')
+        keep += [inbox, hi]
+    return tuple(keep)
 
 
 def bind_nvls(engine, params, dp: DataParallel):
