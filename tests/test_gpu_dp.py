@@ -159,7 +159,40 @@ def test_two_gpu_nvls_overlap_is_bit_identical_to_one_kernel_adam(tmp_path, monk
     assert np.array_equal(outs[0][0]['exp_avg_0'], outs[0][1]['exp_avg_0']), 'gathered moments differ between ranks'
 
 
-def _late_peer_worker(rank, world, port, precision, out):
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
+@pytest.mark.parametrize('optimizer', ['sgd', 'adam'])
+def test_two_gpu_low_latency_exchange_is_bit_identical_to_publish_and_read(tmp_path, monkeypatch, optimizer):
+    """2,048 rows per rank: the dW1 + update kernel exchanges gradients as 16-byte packets {three floats, step} that the receivers
+    poll in their own memory (ts_dp_bind_ll). Same terms, same order as the publish + remote-read exchange: the weights after three
+    steps must be bit-identical between the two exchanges and between the replicas, and within 1e-2 of the full-batch oracle."""
+    import torch.multiprocessing as mp
+    from oracle import mlp_numpy as onp
+    from tests.test_gpu_parity import synthetic, seeded_init
+    from tests.golden_util import assert_params_close
+    dims, B = [784, 256, 10], 4096
+    runs = {}
+    for name, env in (('packets', '1'), ('two_hops', '2'), ('publish_read', '0')) if optimizer == 'sgd' else (('packets', '1'), ('publish_read', '0')):
+        monkeypatch.setenv('TSB200_DP_LL', env)
+        out = str(tmp_path / f'{name}_rank0.npz')
+        mp.spawn(_worker, args=(2, _free_port(), 'bf16', 'p2p', out, tuple(dims), B, optimizer), nprocs=2, join=True)
+        runs[name] = [np.load(out.replace('rank0', f'rank{r}')) for r in range(2)]
+    for name, got in runs.items():
+        for i in range(4):
+            assert np.array_equal(got[0][f'arr_{i}'], got[1][f'arr_{i}']), f'{name}: replicas differ in tensor {i}'
+            assert np.array_equal(got[0][f'arr_{i}'], runs['publish_read'][0][f'arr_{i}']), f'{name} differs from publish + read in tensor {i}'
+    if optimizer == 'adam':
+        assert np.array_equal(runs['packets'][0]['exp_avg_0'], runs['publish_read'][0]['exp_avg_0'])
+    x, y = synthetic(B * 3)
+    x = x.bfloat16().float()
+    init = seeded_init(dims, seed=0, bf16=True)
+    oracle = onp.OracleMLP(weights=init[0::2], biases=init[1::2], opt_kind=onp.OPT_SGD if optimizer == 'sgd' else onp.OPT_ADAM,
+                           lr=0.05 if optimizer == 'sgd' else 1e-3, emulate_bf16=True)
+    for s in range(3):
+        oracle.fit(x[s * B:(s + 1) * B].numpy(), y[s * B:(s + 1) * B].numpy(), None)
+    assert_params_close([runs['packets'][0][f'arr_{i}'] for i in range(4)], oracle.parameters(), 1e-2, lr=1e-3, steps=3, adam=optimizer == 'adam')
+
+
+def _late_peer_worker(rank, world, port, precision, out, B=1024):
     import torch.distributed as dist
     from torch import nn
     os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), TSB200_DP_TIMEOUT_S='1.5')
@@ -167,7 +200,6 @@ def _late_peer_worker(rank, world, port, precision, out):
     dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
     from torchsystem_b200 import B200Classifier, MLP, TsError
     from tests.test_gpu_parity import synthetic
-    B = 1024
     x, y = synthetic(B)
     torch.manual_seed(0)
     net = MLP(784, 256, 10, dropout=0.0, activation=nn.ReLU())
@@ -195,13 +227,13 @@ def _late_peer_worker(rank, world, port, precision, out):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
-@pytest.mark.parametrize('precision', ['bf16', 'f32'])
-def test_a_peer_that_never_arrives_is_a_status_not_a_trap(tmp_path, precision):
+@pytest.mark.parametrize('precision,rows', [('bf16', 1024), ('bf16', 2048), ('f32', 1024)])
+def test_a_peer_that_never_arrives_is_a_status_not_a_trap(tmp_path, precision, rows):
     """A rank whose peer does not reach the step within the configured time (TSB200_DP_TIMEOUT_S) skips that step's update
     and reports TS_E_TIMEOUT at its next call; nothing traps, the CUDA context survives (bf16: the dW1 + update kernel's
-    in-kernel exchange; f32: dp_optimizer_kernel)."""
+    in-kernel exchange -- publish + remote reads at 1,024 rows, low-latency packets at 2,048; f32: dp_optimizer_kernel)."""
     import torch.multiprocessing as mp
     out = str(tmp_path / 'result.txt')
-    mp.spawn(_late_peer_worker, args=(2, _free_port(), precision, out), nprocs=2, join=True)
+    mp.spawn(_late_peer_worker, args=(2, _free_port(), precision, out, rows), nprocs=2, join=True)
     result = open(out).read()
     assert result.startswith('timeout|unchanged=True'), result

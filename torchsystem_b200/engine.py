@@ -15,6 +15,16 @@ from .modules import MLPSpec
 
 RING = 1024  # per-batch records kept alive; a returned loss tensor is overwritten RING batches later
 
+# handle of the current stream of a device: torch's raw accessor when this build has it (what its own inductor uses),
+# else through torch.cuda.Stream. Per-batch host time is what bounds the handlers once the kernels take ~30 us.
+_get_raw = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+
+
+def _raw_stream(index: int) -> int:
+    if _get_raw is not None:
+        return _get_raw(index)
+    return torch.cuda.current_stream(index).cuda_stream
+
 
 class Engine:
     def __init__(self, spec: MLPSpec, precision: str, device: torch.device, max_batch: int = 4096):
@@ -130,7 +140,7 @@ class Engine:
 
     # ------------------------------------------------------------------ hot path
     def _stream(self):
-        return torch.cuda.current_stream(self.index).cuda_stream
+        return _raw_stream(self.index)       # the current stream's handle, without building a torch.cuda.Stream per call
 
     def _next_slot(self) -> int:
         s = self._slot

@@ -15,7 +15,7 @@ from torch import Tensor
 
 from . import _lib
 from ._lib import lib, check
-from .engine import RING
+from .engine import RING, _raw_stream
 from .parallel import DataParallel
 
 logger = getLogger(__name__)
@@ -36,7 +36,7 @@ class B200Metrics:
         self._dp = DataParallel(process_group)
 
     def _stream(self):
-        return torch.cuda.current_stream(self.device.index).cuda_stream
+        return _raw_stream(self.device.index)
 
     def _flush(self) -> None:
         if self._run is not None:
