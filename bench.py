@@ -116,8 +116,8 @@ def reference_arm(args):
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
     """SM clock and throttle reasons sampled DURING the timed region. The region is tens of milliseconds long, shorter than
-    one `nvidia-smi -lms` period, so the samples come from NVML in a thread (every ~2 ms, and always at least one taken
-    while the GPU is busy); nvidia-smi is only the fallback when the NVML binding is missing."""
+    one `nvidia-smi -lms` period, so the samples come from NVML in a thread (every ~8 ms: an NVML query takes driver locks the
+    kernel launches of the same process also need, so it is kept rare; always at least one sample taken while the GPU is busy); nvidia-smi is only the fallback when the NVML binding is missing."""
     Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,'
          'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
 
@@ -166,7 +166,7 @@ class ClockSampler:
                 self._sample()
             except Exception:
                 break
-            time.sleep(0.002)
+            time.sleep(0.008)
 
     def sample_now(self):
         """One sample from the calling thread (called right after the timed launches are enqueued: the GPU is busy)."""

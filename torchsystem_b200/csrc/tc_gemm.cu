@@ -489,7 +489,11 @@ namespace {
 int pick_bn(int M, int N, int K, int splits, int sm_count, bool pairs_allowed, bool *two) {
     static const int cand[] = {256, 224, 192, 160, 128, 112, 96, 80, 64, 48, 32, 16};
     *two = false;
-    if (const char *f = getenv("TSB_FORCE_BN")) { *two = pairs_allowed && atoi(f) == 256 && M >= 2 * BM; return atoi(f); }   // experiments
+    if (const char *f = getenv("TSB_FORCE_BN")) {   // experiments; TSB_FORCE_PAIR=1: CTA pairs at that width
+        const char *fp = getenv("TSB_FORCE_PAIR");
+        *two = pairs_allowed && M >= 2 * BM && (atoi(f) == 256 || (fp && atoi(fp) != 0));
+        return atoi(f);
+    }
     const int tiles_m = (M + BM - 1) / BM;
     const long k64 = ((K + KATOM - 1) / KATOM + splits - 1) / splits;
     int best = 16;
