@@ -256,6 +256,13 @@ def test_device_loader_batches_shuffle_and_shards():
     sizes = [xb.shape[0] for xb, _ in DeviceLoader(x, y, 32, device='cpu')]
     assert sizes == [32, 32, 32, 7] and len(DeviceLoader(x, y, 32, device='cpu')) == 4
     assert [xb.shape[0] for xb, _ in DeviceLoader(x, y, 32, device='cpu', drop_last=True)] == [32, 32, 32]
+    # unshuffled: the batch views are made once and handed out again every epoch (same storage, same order, still views)
+    plain = DeviceLoader(x.clone(), y, 32, device='cpu')
+    e1, e2 = list(plain), list(plain)
+    assert all(a is b and c is d for (a, c), (b, d) in zip(e1, e2)) and len(e1) == 4
+    assert e1[1][0].data_ptr() == plain.inputs[32:64].data_ptr() and torch.equal(e1[3][1], plain.targets[96:])
+    plain.inputs[40] = 7.0                                   # a view: sees later writes to the dataset
+    assert float(e1[1][0][8].flatten()[0]) == 7.0
     a = [(xb, yb) for xb, yb in DeviceLoader(x, y, 32, device='cpu', shuffle=True, seed=7)]
     b = [(xb, yb) for xb, yb in DeviceLoader(x, y, 32, device='cpu', shuffle=True, seed=7)]
     assert all(torch.equal(p[0], q[0]) and torch.equal(p[1], q[1]) for p, q in zip(a, b))
