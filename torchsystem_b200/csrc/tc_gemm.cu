@@ -52,6 +52,8 @@ struct TcParams {
     DropoutSpec drop;
     int training;
     unsigned long long *dbg;   // optional trace buffer (test hook), or nullptr
+    int wide_epi;              // bf16 epilogues: 64-column chunks (16-byte stores, whole 128-byte lines per row); staging 8 KiB per warp
+    uint32_t epi_stage_bytes;  // staging per epilogue warp: 4096, or 8192 with wide_epi
 };
 
 // Persistent: one CTA per SM walks the tiles t = blockIdx.x, + gridDim.x, ...; the accumulator alternates between two
@@ -60,6 +62,11 @@ struct TcParams {
 // exposed: 333 us instead of 241 us for the forward layer of the L model, 411 us for its dX layer.
 // At most 128 registers per thread (352 x 128 = 45 K of the SM's 64 K): a small second kernel -- the per-layer NVLS exchange of
 // data-parallel training, 256 threads x 64 registers -- can then be resident on the same SM next to a GEMM CTA.
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    const __nv_bfloat162 b = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&b);
+}
+
 // TWO: a CTA pair (cluster of 2) works on a 256 x BN tile with tcgen05.mma.cta_group::2 -- each CTA stages its own 128 rows
 // of A and HALF of B (BN / 2 columns), so the shared-memory traffic per FLOP of the B operand halves (one CTA alone moves
 // 96 KB through shared memory per 64-wide K block of a 128 x 256 tile, ~750 cycles at 128 B/cycle against 512 cycles of tensor
@@ -230,11 +237,176 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         // ===================== epilogue: TMEM -> registers -> smem (transpose) -> coalesced global =====================
         const int q = warp & 3;                  // TMEM lane quarter this warp may read
         const int half = (warp - 3) >> 2;        // which of the two warps of that quarter: chunks half, half + 2, ...
-        float4 *stage = reinterpret_cast<float4 *>(staging + (size_t)(warp - 3) * 4096);
+        float4 *stage = reinterpret_cast<float4 *>(staging + (size_t)(warp - 3) * p.epi_stage_bytes);
         const int sub_row = lane >> 3, piece = lane & 7;     // phase-2 mapping: 4 rows x 8 float4 per instruction
         auto release_acc = [&](int buf) {      // this warp's reads of the accumulator are done; the pair's barrier lives in the leader
             if (TWO && cta_rank != 0) mbar_arrive_remote(&tmem_empty_bar[buf], 0u); else mbar_arrive(&tmem_empty_bar[buf]);
         };
+        // ---- bf16 outputs (FWD, ACTGRAD): 64-column chunks. A 32-column chunk is 64 bytes of a bf16 row: every store and every
+        //      A_prev load touched half a 128-byte line, and the kernel runs at the L2's throughput -- the epilogue's
+        //      half-line requests were paid at the bottleneck. Here 8 lanes cover one whole line of a row (16 bytes each); the
+        //      accumulator chunk goes through an 8 KiB staging tile [32 rows][16 float4] in two TMEM rounds of 32 columns. The
+        //      two halves of a row are XOR-swizzled differently so that the 32-byte reads of phase 2 stay bank-conflict free.
+        if (EPI != TC_EPI_STORE_F32 && p.wide_epi) {
+            for (int t = unit, it = 0; t < total_tiles; t += n_units, ++it) {
+                TS_TILE_COORDS(t)
+                const int buf = it & 1;
+                const uint32_t tmem_acc = tmem_base + (uint32_t)buf * p.acc_stride + ((uint32_t)(q * 32) << 16);
+                const bool has_k = kb_begin < kb_end;
+                mbar_wait(&tmem_full_bar[buf], (uint32_t)(it >> 1) & 1u);
+                tc_fence_after();
+                if (half * 64 >= p.BN) {             // narrow tile: nothing for the second warp of the quarter
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) release_acc(buf);
+                }
+                for (int c = half * 64; c < p.BN; c += 128) {
+                    const int n = n0 + c + piece * 8;                      // this lane's 8 columns in phase 2
+                    const bool col_in = c + piece * 8 < p.BN && n < p.N;   // BN and the piece are multiples of 8
+                    const int nv = col_in ? min(8, p.N - n) : 0;
+                    const bool vec = nv == 8 && (p.ldo & 7) == 0;
+                    uint4 prev[8];
+                    if (EPI == TC_EPI_ACTGRAD) {      // the layer's own output (ReLU') / stored pre-activation (GELU'): issued before the TMEM rounds
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int row = m0 + q * 32 + i * 4 + sub_row;
+                            prev[i] = make_uint4(0u, 0u, 0u, 0u);
+                            if (vec && row < p.M) prev[i] = *reinterpret_cast<const uint4 *>(p.A_prev + (int64_t)row * p.ldo + n);
+                        }
+                    }
+                    float bias8[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) bias8[j] = (EPI == TC_EPI_FWD && j < nv) ? p.bias[n + j] : 0.0f;
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int cc = c + 32 * hh;
+                        float v[32];
+                        if (has_k && cc < p.BN) {
+                            tmem_ld16(tmem_acc + (uint32_t)cc, *reinterpret_cast<float(*)[16]>(&v[0]));
+                            if (cc + 16 < p.BN) tmem_ld16(tmem_acc + (uint32_t)(cc + 16), *reinterpret_cast<float(*)[16]>(&v[16]));
+                            else {
+#pragma unroll
+                                for (int j = 16; j < 32; ++j) v[j] = 0.0f;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] = 0.0f;
+                        }
+                        // phase 1: lane = row; 16-byte pieces XOR-swizzled by row (and by the half)
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            stage[lane * 16 + 8 * hh + ((j ^ (lane & 7)) ^ hh)] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    }
+                    if (c + 128 >= p.BN) {       // this warp's last TMEM read of the tile is in shared memory: hand the accumulator back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) release_acc(buf);
+                    }
+                    __syncwarp();
+                    // phase 2: 8 consecutive lanes cover 128 contiguous bytes (64 bf16 columns) of one output row
+                    float cs[8] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+                    const int hh2 = piece >> 2, j0 = (2 * piece) & 7;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int rr = i * 4 + sub_row;
+                        const int row = m0 + q * 32 + rr;
+                        const float4 t0 = stage[rr * 16 + 8 * hh2 + ((j0 ^ (rr & 7)) ^ hh2)];
+                        const float4 t1 = stage[rr * 16 + 8 * hh2 + (((j0 + 1) ^ (rr & 7)) ^ hh2)];
+                        if (row >= p.M || nv == 0) continue;
+                        float w[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+                        __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(p.out) + (int64_t)row * p.ldo + n;
+                        float pf[8];            // ACTGRAD: A_prev (or the stored pre-activation) of these 8 columns
+                        if (EPI == TC_EPI_ACTGRAD) {
+                            if (vec) {
+                                const uint32_t pw[4] = {prev[i].x, prev[i].y, prev[i].z, prev[i].w};
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {      // bf16 -> fp32 is a shift
+                                    pf[2 * e] = __uint_as_float(pw[e] << 16); pf[2 * e + 1] = __uint_as_float(pw[e] & 0xffff0000u);
+                                }
+                            } else {
+                                const __nv_bfloat16 *ap = p.A_prev + (int64_t)row * p.ldo + n;
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) pf[j] = j < nv ? __bfloat162float(ap[j]) : 0.0f;
+                            }
+                        }
+                        if (EPI == TC_EPI_FWD) {
+                            // Linear bias, Dropout, ReLU (mlp.py:14-16), all in fp32 on the accumulator
+                            float k0[4] = {1.0f, 1.0f, 1.0f, 1.0f}, k1[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+                            if (p.training) {
+                                p.drop.factor4((int64_t)row, n, p.N, k0);
+                                p.drop.factor4((int64_t)row, n + 4, p.N, k1);
+                            }
+                            const float keep[8] = {k0[0], k0[1], k0[2], k0[3], k1[0], k1[1], k1[2], k1[3]};
+                            if (p.act == TS_ACT_RELU) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) w[j] = fmaxf((w[j] + bias8[j]) * keep[j], 0.0f);
+                            } else {
+                                // GELU: the post-dropout pre-activation is kept (bf16) for the backward pass
+                                float u[8];
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) { u[j] = (w[j] + bias8[j]) * keep[j]; w[j] = gelu_f(u[j]); }
+                                __nv_bfloat16 *uo = p.U_out + (int64_t)row * p.ldo + n;
+                                if (vec) {
+                                    *reinterpret_cast<uint4 *>(uo) = make_uint4(pack_bf16x2(u[0], u[1]), pack_bf16x2(u[2], u[3]),
+                                                                                pack_bf16x2(u[4], u[5]), pack_bf16x2(u[6], u[7]));
+                                } else {
+                                    #pragma unroll
+                                    for (int j = 0; j < 8; ++j)
+                                        if (j < nv) uo[j] = __float2bfloat16_rn(u[j]);
+                                }
+                            }
+                        } else if (p.act != TS_ACT_RELU) {
+                            // dH = dA * gelu'(u) * keep/(1-p), u = the stored pre-activation (a dropped unit has u = 0 and
+                            // gelu'(0) = 1/2, so the keep factor is applied explicitly)
+                            float k0[4] = {1.0f, 1.0f, 1.0f, 1.0f}, k1[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+                            if (p.training) {
+                                p.drop.factor4((int64_t)row, n, p.N, k0);
+                                p.drop.factor4((int64_t)row, n + 4, p.N, k1);
+                            }
+                            const float keep[8] = {k0[0], k0[1], k0[2], k0[3], k1[0], k1[1], k1[2], k1[3]};
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) w[j] = w[j] * gelu_grad_f(pf[j]) * keep[j];
+                        } else {
+                            // dH = dA * relu'(A_prev) / (1-p): A_prev > 0 implies the unit was kept
+                            const float sc = p.training ? p.drop.scale : 1.0f;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) w[j] = (pf[j] > 0.0f) ? w[j] * sc : 0.0f;
+                        }
+                        uint32_t pk[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            pk[e] = pack_bf16x2(w[2 * e], w[2 * e + 1]);
+                            if (EPI == TC_EPI_ACTGRAD) {   // sums of the ROUNDED values: what a column sum of the stored dH gives
+                                if (2 * e < nv) cs[2 * e] += __uint_as_float(pk[e] << 16);
+                                if (2 * e + 1 < nv) cs[2 * e + 1] += __uint_as_float(pk[e] & 0xffff0000u);
+                            }
+                        }
+                        if (vec) {
+                            *reinterpret_cast<uint4 *>(o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        } else {
+                            #pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (j < nv) o[j] = __float2bfloat16_rn(w[j]);
+                        }
+                    }
+                    if (EPI == TC_EPI_ACTGRAD && p.colsum_out != nullptr) {
+                        // the 4 lanes that share a column group (sub_row 0..3) fold their 8 rows each: 32 rows per warp
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
+                            cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
+                        }
+                        if (sub_row == 0 && nv > 0) {
+                            float *o = p.colsum_out + (int64_t)((m0 / BM) * 4 + q) * p.colsum_stride + n;
+                            #pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (j < nv) o[j] = cs[j];
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        } else
         for (int t = unit, it = 0; t < total_tiles; t += n_units, ++it) {
             TS_TILE_COORDS(t)
             const int buf = it & 1;
@@ -557,8 +729,12 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     const int grid_units = (int)(total_tiles < units ? total_tiles : units);
     const int grid_x = two ? 2 * grid_units : grid_units;
     const long tiles_per_cta = (total_tiles + grid_units - 1) / grid_units;
-    // pipeline stages + 32 KiB of epilogue staging (the pipeline stays live while a tile's epilogue runs) + alignment
-    p.stages = (int)((226u * 1024u - 1024u - (uint32_t)kEpiWarps * 4096u) / stage);
+    // pipeline stages + 32 (64: bf16 epilogues with 64-column chunks) KiB of epilogue staging (the pipeline stays live while a
+    // tile's epilogue runs) + alignment
+    static const int wide_mode = [] { const char *e = getenv("TSB200_GEMM_WIDE_EPI"); return e ? atoi(e) : 1; }();
+    p.wide_epi = (wide_mode != 0 && a.epi != TC_EPI_STORE_F32 && two) ? 1 : 0;   // pairs: 32 KiB stages, five of them still fit
+    p.epi_stage_bytes = p.wide_epi ? 8192u : 4096u;
+    p.stages = (int)((226u * 1024u - 1024u - (uint32_t)kEpiWarps * p.epi_stage_bytes) / stage);
     if (p.stages > kMaxStages) p.stages = kMaxStages;
     const long kblocks_per_cta = (long)p.kblocks_per_split * tiles_per_cta;
     if (p.stages > kblocks_per_cta) p.stages = kblocks_per_cta < 2 ? 2 : (int)kblocks_per_cta;
@@ -579,7 +755,7 @@ int launch_tc_gemm(const TcGemmArgs &a, int sm_count, cudaStream_t st) {
     else rc = get_map(a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb, 64, (uint32_t)p.BK, &mb);
     if (rc) return rc;
 
-    const size_t smem = (size_t)p.stages * stage + kEpiWarps * 4096 + 1024;
+    const size_t smem = (size_t)p.stages * stage + (size_t)kEpiWarps * p.epi_stage_bytes + 1024;
     dim3 grid((unsigned)grid_x);
 #define TS_TC_LAUNCH_K(KERNEL, CLUSTER)                                                                              \
     do {                                                                                                            \
