@@ -6,7 +6,8 @@ from torch import nn
 from torchsystem_b200 import B200Classifier, MLP, _lib
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 torch.manual_seed(0)
-net = MLP(784, [4096] * 4, 10, dropout=0.1, activation=nn.ReLU())
+DROP = float(os.environ.get("LPROF_DROPOUT", "0.1"))
+net = MLP(784, [4096] * 4, 10, dropout=DROP, activation=nn.ReLU())
 model = B200Classifier(net, nn.CrossEntropyLoss(), torch.optim.Adam(net.parameters(), lr=1e-3), precision='bf16', device='cuda:0', max_batch=B)
 x = torch.randn(B, 784, device='cuda'); y = torch.randint(0, 10, (B,), device='cuda')
 for _ in range(3): model.fit(x, y)
