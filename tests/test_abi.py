@@ -45,6 +45,19 @@ def test_abi_version_and_error_string(built):
         built.check(rc, 'ts_mlp_create')
 
 
+def test_inbox_size_agrees_between_header_kernels_and_python():
+    """TS_DP_LL_INBOX_BYTES (include/tsb200.h) = 2 parities x kLlParityBytes (csrc/kernels.h) = parallel.LL_INBOX_BYTES: the inbox
+    of the low-latency exchange is allocated in Python, checked in the C ABI and indexed in the kernel."""
+    header = int(re.search(r'#define\s+TS_DP_LL_INBOX_BYTES\s+(\d+)', open(HEADER).read()).group(1))
+    kh = open(os.path.join(ROOT, 'torchsystem_b200', 'csrc', 'kernels.h')).read()
+    ranks = int(re.search(r'constexpr int kMaxRanks = (\d+);', kh).group(1))
+    ctas, quads = map(int, re.search(r'constexpr int kLlCtas = (\d+), kLlQuads = (\d+);', kh).groups())
+    assert '(kMaxRanks + 1) * kLlCtas * kLlQuads * 256 * 16' in kh
+    assert header == 2 * (ranks + 1) * ctas * quads * 256 * 16
+    from torchsystem_b200 import parallel
+    assert parallel.LL_INBOX_BYTES == header and header % 16 == 0
+
+
 def test_no_torch_types_in_the_abi():
     text = open(HEADER).read()
     assert 'torch' not in re.sub(r'/\*.*?\*/', '', text, flags=re.S).lower()
