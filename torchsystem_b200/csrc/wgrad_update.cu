@@ -75,7 +75,8 @@ __device__ __forceinline__ bool dp_publish_and_wait(const DpArgs &dp, int tid, i
 // remote load request, reply) behind a grid-wide ticket. Here the data carries its own validity, as in a collective library's
 // low-latency protocol: a 16-byte packet {three floats, step number} written with ONE store; the receiver polls its own memory
 // until the fourth word shows this step (a 16-byte aligned store or load is a single transaction, so a packet is seen whole
-// or not at all). No fence, no separate flag, no ticket, and a late CTA delays only its own share. Two hops keep the wire
+// or not at all: a hardware property -- the PTX memory model only promises it per scalar -- of the kind the 128-byte
+// low-latency protocols of collective libraries rely on; the replicas are compared bit for bit by tests and bench). No fence, no separate flag, no ticket, and a late CTA delays only its own share. Two hops keep the wire
 // volume flat in the world size: CTA c's share of the gradient is owned by rank c % world; the other ranks send their share
 // to the owner's inbox, the owner adds them in rank order (its own term in its place) and sends the sum to everybody -- all
 // replicas apply bit-identical gradients. (A world of two skips the second hop: each rank sends its share to the other and both
