@@ -3,7 +3,7 @@ tile or CTA pairs; TSB_FORCE_BN overrides the tile width. python scratch/gemm_pa
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from torchsystem_b200 import _lib
-SHAPES = [('fwd', 0, 0, 8192, 4096, 4096), ('dX', 0, 1, 8192, 4096, 4096), ('dW', 1, 1, 4096, 4096, 8192), ('fwd1', 0, 0, 8192, 4096, 784)]
+SHAPES = [('cube (the shape of MEASURED_PEAKS.json bf16_tflops)', 0, 0, 8192, 8192, 8192), ('fwd', 0, 0, 8192, 4096, 4096), ('dX', 0, 1, 8192, 4096, 4096), ('dW', 1, 1, 4096, 4096, 8192), ('fwd1', 0, 0, 8192, 4096, 784)]
 st = torch.cuda.current_stream().cuda_stream
 flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
 for name, am, bm, M, N, K in SHAPES:
